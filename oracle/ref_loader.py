@@ -1,0 +1,115 @@
+"""Load the UNMODIFIED reference hot-path modules on CPU.  TEST INFRASTRUCTURE.
+
+Only usable where /root/reference exists (the build container).  Nothing under
+`-m gpu`, `smoke()` or `bench.py` may import this module: the GPU box has no
+/root/reference.  It is used (a) by `-m "not gpu"` tests to validate
+`oracle/restated.py` against the real reference code and (b) by
+`oracle/make_golden.py` to generate the fixtures under tests/golden/.
+
+The reference imports three packages that are not installed (no network):
+optree, torchopt, torchtyping -> `oracle/shims/`.  `big_sweep.py` and
+`standard_metrics.py` import matplotlib / transformer_lens / wandb / baukit at
+module level, so single `def`s are AST-extracted from them and executed in a
+namespace that only holds what those functions touch.
+"""
+import ast
+import importlib
+import os
+import sys
+
+REFERENCE_ROOT = os.environ.get("SC_REFERENCE_ROOT", "/root/reference")
+_SHIMS = os.path.join(os.path.dirname(os.path.abspath(__file__)), "shims")
+
+
+def available() -> bool:
+    return os.path.isfile(os.path.join(REFERENCE_ROOT, "autoencoders", "ensemble.py"))
+
+
+_loaded = {}
+
+
+def load():
+    """Returns a namespace object with the reference modules / functions."""
+    if "ns" in _loaded:
+        return _loaded["ns"]
+    if not available():
+        raise RuntimeError(f"reference not found at {REFERENCE_ROOT}")
+    # our own package also has a sub-package called `autoencoders`, but it lives
+    # under sparse_coding__b200.*, so the top-level name is free for the reference.
+    for p in (_SHIMS, REFERENCE_ROOT):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+
+    class NS:
+        pass
+
+    ns = NS()
+    ns.torchopt = importlib.import_module("torchopt")
+    ns.optree = importlib.import_module("optree")
+    ns.ensemble = importlib.import_module("autoencoders.ensemble")
+    ns.sae_ensemble = importlib.import_module("autoencoders.sae_ensemble")
+    ns.learned_dict = importlib.import_module("autoencoders.learned_dict")
+    ns.fista = importlib.import_module("autoencoders.fista")
+    assert ns.ensemble.__file__.startswith(REFERENCE_ROOT), ns.ensemble.__file__
+
+    ns.FunctionalEnsemble = ns.ensemble.FunctionalEnsemble
+    ns.FunctionalSAE = ns.sae_ensemble.FunctionalSAE
+    ns.FunctionalTiedSAE = ns.sae_ensemble.FunctionalTiedSAE
+    ns.FunctionalFista = ns.fista.FunctionalFista
+    ns.UntiedSAE = ns.learned_dict.UntiedSAE
+    ns.TiedSAE = ns.learned_dict.TiedSAE
+
+    import numpy as np
+    import torch
+
+    def extract(path, names, extra_globals):
+        with open(os.path.join(REFERENCE_ROOT, path)) as f:
+            tree = ast.parse(f.read())
+        body = [n for n in tree.body if isinstance(n, ast.FunctionDef) and n.name in names]
+        found = {n.name for n in body}
+        missing = set(names) - found
+        if missing:
+            raise RuntimeError(f"{path}: functions not found: {sorted(missing)}")
+        mod = ast.Module(body=body, type_ignores=[])
+        g = {"torch": torch, "np": np, "__builtins__": __builtins__}
+        g.update(extra_globals)
+        exec(compile(mod, os.path.join(REFERENCE_ROOT, path), "exec"), g)
+        return {n: g[n] for n in names}
+
+    class _Any:
+        def __class_getitem__(cls, item):
+            return cls
+
+    def make_hyperparam_name(hv):
+        return "_".join(f"{k}_{v}" for k, v in hv.items())
+
+    bs = extract(
+        "big_sweep.py",
+        ["ensemble_train_loop", "separate_tensors", "unstacked_to_learned_dicts"],
+        {"FunctionalFista": ns.FunctionalFista, "make_hyperparam_name": make_hyperparam_name},
+    )
+    # the extracted functions call each other through their module globals
+    for fn in bs.values():
+        fn.__globals__.update(bs)
+    ns.ensemble_train_loop = bs["ensemble_train_loop"]
+    ns.separate_tensors = bs["separate_tensors"]
+    ns.unstacked_to_learned_dicts = bs["unstacked_to_learned_dicts"]
+
+    sm_names = [
+        "mean_nonzero_activations", "fraction_variance_unexplained",
+        "fraction_variance_unexplained_top_activating", "r_squared",
+        "calc_feature_n_active", "batched_calc_feature_n_ever_active",
+        "calc_feature_mean", "calc_feature_variance", "calc_feature_skew",
+        "calc_feature_kurtosis", "calc_moments_streaming",
+    ]
+    sm = extract(
+        "standard_metrics.py", sm_names,
+        {"LearnedDict": ns.learned_dict.LearnedDict, "TensorType": _Any},
+    )
+    for fn in sm.values():
+        fn.__globals__.update(sm)
+    for k, v in sm.items():
+        setattr(ns, k, v)
+
+    _loaded["ns"] = ns
+    return ns

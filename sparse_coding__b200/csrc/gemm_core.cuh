@@ -1,0 +1,253 @@
+// Persistent, warp-specialised tcgen05 GEMM core for sm_100a with pluggable fused epilogues.
+//
+//   ACC[g][m][n] = sum_seg sum_k A_seg[g][m][k] * B_seg[g][n][k]        (TF32 in, fp32 accumulate)
+//
+// * one CTA per SM, 256 threads: warp 0 = TMA producer, warp 1 = MMA issuer, warp 2 = TMEM
+//   allocator, warps 4..7 = epilogue (thread t of the four owns accumulator row t = TMEM lane t)
+// * operand tiles [128 x 32] / [BN x 32] fp32 arrive by TMA into 128-byte-swizzled shared memory,
+//   a ring of kStages stages guarded by full/empty mbarriers
+// * one elected thread issues tcgen05.mma.kind::tf32 128 x BN x 8; accumulators live in TMEM,
+//   double buffered (2 x BN columns) so the epilogue of tile i overlaps the MMAs of tile i+1
+// * up to three (A,B) operand pairs ("segments") accumulate into the same tile: used for the tied
+//   SAE gradient (c^T R + dz^T x) and for the 3xTF32 split products of FISTA
+// * either operand may be K-major (k contiguous) or MN-major (m/n contiguous); MN-major fp32 tiles
+//   use the 128-byte swizzle with 32-byte atoms, the only MN-major layout tcgen05 takes for 32-bit
+// * the epilogue is a functor that sees its accumulator row 32 columns at a time
+//
+// Group (member) index g lets one launch cover every SAE of the ensemble; an operand that all
+// members share (the activation batch) has gmul = 0 and is fetched from the same address by all.
+#pragma once
+#include "sm100_ptx.cuh"
+
+namespace sc {
+
+constexpr int kBlockM = 128;
+constexpr int kBlockK = 32;  // fp32 elements: 128 bytes, one swizzle span
+constexpr int kUmmaK = 8;    // tf32: 32 bytes of K per instruction
+constexpr int kMaxSeg = 3;
+constexpr int kGemmThreads = 256;
+constexpr int kATileBytes = kBlockM * kBlockK * 4;
+
+struct alignas(64) GemmMaps {
+    CUtensorMap a[kMaxSeg];
+    CUtensorMap b[kMaxSeg];
+};
+
+struct GemmShape {
+    int M, N, G;
+    int nseg;
+    int K[kMaxSeg];
+    int a_gmul[kMaxSeg], b_gmul[kMaxSeg];
+    int tiles_m, tiles_n;
+};
+
+template <int BN>
+struct GemmCfg {
+    static constexpr int kBTileBytes = BN * kBlockK * 4;
+    static constexpr int kStageBytes = kATileBytes + kBTileBytes;
+    static constexpr int kStagesRaw = (227 * 1024 - 2048) / kStageBytes;
+    static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
+    static constexpr int kTmemCols = (2 * BN <= 32) ? 32 : (2 * BN <= 64) ? 64 : (2 * BN <= 128) ? 128 : (2 * BN <= 256) ? 256 : 512;
+    static constexpr int kBarrierBytes = (2 * kStages + 4) * 8 + 16;
+    static constexpr int kSmemBytes = kStages * kStageBytes + kBarrierBytes + 1024;  // + alignment slack
+    static_assert(BN % 32 == 0 && BN >= 32 && BN <= 256, "BN must be a multiple of 32 in [32,256]");
+};
+
+// Context handed to an epilogue functor for one accumulator row of one tile.
+struct RowCtx {
+    int g;       // group / ensemble member
+    int row;     // global accumulator row (may be >= M on the ragged last tile)
+    int col0;    // first global column of the tile
+    int M, N;    // logical extents
+    int tile_m, tile_n;
+    int warp_q;  // which 32-row quarter of the tile this warp owns (0..3)
+};
+
+template <int BN, bool A_MN, bool B_MN, class Epi>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_tf32_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
+                 const __grid_constant__ typename Epi::Params ep) {
+    using Cfg = GemmCfg<BN>;
+    constexpr int kStages = Cfg::kStages;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kStages * Cfg::kStageBytes);
+    uint64_t* empty_bar = full_bar + kStages;
+    uint64_t* tmem_full = empty_bar + kStages;
+    uint64_t* tmem_empty = tmem_full + 2;
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    if (warp == 0 && lane == 0) {
+        for (int s = 0; s < shape.nseg; ++s) {
+            tma_prefetch_desc(&maps.a[s]);
+            tma_prefetch_desc(&maps.b[s]);
+        }
+    }
+    if (warp == 1 && lane == 0) {
+        for (int i = 0; i < kStages; ++i) {
+            mbar_init(&full_bar[i], 1);
+            mbar_init(&empty_bar[i], 1);
+        }
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&tmem_full[i], 1);
+            mbar_init(&tmem_empty[i], 128);
+        }
+        fence_mbar_init();
+    }
+    if (warp == 2) {
+        tmem_alloc(tmem_ptr, Cfg::kTmemCols);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr;
+
+    const int tiles_per_group = shape.tiles_m * shape.tiles_n;
+    const int total_tiles = tiles_per_group * shape.G;
+
+    if (warp == 0) {
+        // ------------------------------------------------------------------ TMA producer
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+                const int g = tile / tiles_per_group;
+                const int rem = tile - g * tiles_per_group;
+                const int tn = rem / shape.tiles_m;
+                const int tm = rem - tn * shape.tiles_m;
+                const int m0 = tm * kBlockM, n0 = tn * BN;
+                for (int seg = 0; seg < shape.nseg; ++seg) {
+                    const int kblocks = (shape.K[seg] + kBlockK - 1) / kBlockK;
+                    const int ga = g * shape.a_gmul[seg], gb = g * shape.b_gmul[seg];
+                    for (int kb = 0; kb < kblocks; ++kb) {
+                        mbar_wait(&empty_bar[stage], phase ^ 1);
+                        mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+                        uint8_t* sa = smem + stage * Cfg::kStageBytes;
+                        uint8_t* sb = sa + kATileBytes;
+                        const int k0 = kb * kBlockK;
+                        if (!A_MN) {
+                            tma_load_3d(&maps.a[seg], &full_bar[stage], sa, k0, m0, ga);
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < kBlockM / 32; ++i)
+                                tma_load_3d(&maps.a[seg], &full_bar[stage], sa + i * 4096, m0 + 32 * i, k0, ga);
+                        }
+                        if (!B_MN) {
+                            tma_load_3d(&maps.b[seg], &full_bar[stage], sb, k0, n0, gb);
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < BN / 32; ++i)
+                                tma_load_3d(&maps.b[seg], &full_bar[stage], sb + i * 4096, n0 + 32 * i, k0, gb);
+                        }
+                        if (++stage == kStages) { stage = 0; phase ^= 1; }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ------------------------------------------------------------------ MMA issuer
+        if (lane == 0) {
+            constexpr uint32_t idesc = make_idesc_tf32(kBlockM, BN, A_MN, B_MN);
+            int stage = 0;
+            uint32_t phase = 0;
+            int it = 0;
+            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+                const int as = it & 1;
+                const uint32_t aph = (it >> 1) & 1;
+                mbar_wait(&tmem_empty[as], aph ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + as * BN;
+                uint32_t accumulate = 0;
+                for (int seg = 0; seg < shape.nseg; ++seg) {
+                    const int kblocks = (shape.K[seg] + kBlockK - 1) / kBlockK;
+                    for (int kb = 0; kb < kblocks; ++kb) {
+                        mbar_wait(&full_bar[stage], phase);
+                        tc_fence_after();
+                        const uint32_t a_base = smem_u32(smem + stage * Cfg::kStageBytes);
+                        const uint32_t b_base = a_base + kATileBytes;
+#pragma unroll
+                        for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+                            // K-major : 8-row groups 1024 B apart (SBO); K advances 32 B inside the swizzle span
+                            // MN-major: 32-wide MN chunks 4096 B apart (LBO); 4-k-row groups 512 B apart (SBO);
+                            //           K advances 8 rows = 1024 B
+                            const uint64_t da = A_MN ? make_smem_desc(a_base + k * 1024, 4096, 512, kLayoutSw128Base32)
+                                                     : make_smem_desc(a_base + k * 32, 16, 1024, kLayoutSw128);
+                            const uint64_t db = B_MN ? make_smem_desc(b_base + k * 1024, 4096, 512, kLayoutSw128Base32)
+                                                     : make_smem_desc(b_base + k * 32, 16, 1024, kLayoutSw128);
+                            umma_tf32(d_tmem, da, db, idesc, accumulate);
+                            accumulate = 1;
+                        }
+                        umma_commit(&empty_bar[stage]);  // frees the smem stage once these MMAs retire
+                        if (++stage == kStages) { stage = 0; phase ^= 1; }
+                    }
+                }
+                umma_commit(&tmem_full[as]);  // accumulator ready for the epilogue
+            }
+        }
+    } else if (warp >= 4) {
+        // ------------------------------------------------------------------ epilogue
+        const int q = warp & 3;
+        int it = 0;
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+            const int g = tile / tiles_per_group;
+            const int rem = tile - g * tiles_per_group;
+            const int tn = rem / shape.tiles_m;
+            const int tm = rem - tn * shape.tiles_m;
+            const int as = it & 1;
+            const uint32_t aph = (it >> 1) & 1;
+            RowCtx ctx;
+            ctx.g = g; ctx.row = tm * kBlockM + q * 32 + lane; ctx.col0 = tn * BN;
+            ctx.M = shape.M; ctx.N = shape.N; ctx.tile_m = tm; ctx.tile_n = tn; ctx.warp_q = q;
+            Epi epi(ep, ctx);
+            mbar_wait(&tmem_full[as], aph);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
+#pragma unroll 1
+            for (int c = 0; c < BN / 32; ++c) {
+                float v[32];
+                tmem_ld32(taddr + c * 32, v);
+                tmem_ld_wait();
+                epi.chunk(c * 32, v);
+            }
+            tc_fence_before();
+            mbar_arrive(&tmem_empty[as]);
+            epi.finish();
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, Cfg::kTmemCols);
+    }
+}
+
+// Host-side launcher: grid = min(#tiles, #SMs) persistent CTAs.
+template <int BN, bool A_MN, bool B_MN, class Epi>
+cudaError_t launch_gemm(const GemmMaps& maps, GemmShape shape, const typename Epi::Params& ep, int num_sms,
+                        cudaStream_t stream) {
+    using Cfg = GemmCfg<BN>;
+    auto kern = gemm_tf32_kernel<BN, A_MN, B_MN, Epi>;
+    static bool attr_set[64] = {};  // per template instantiation, per device
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (!attr_set[dev & 63]) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
+        if (e != cudaSuccess) return e;
+        attr_set[dev & 63] = true;
+    }
+    shape.tiles_m = (shape.M + kBlockM - 1) / kBlockM;
+    shape.tiles_n = (shape.N + BN - 1) / BN;
+    const long long total = 1LL * shape.tiles_m * shape.tiles_n * shape.G;
+    if (total <= 0) return cudaSuccess;
+    const int grid = static_cast<int>(total < num_sms ? total : num_sms);
+    kern<<<grid, kGemmThreads, Cfg::kSmemBytes, stream>>>(maps, shape, ep);
+    return cudaGetLastError();
+}
+
+}  // namespace sc

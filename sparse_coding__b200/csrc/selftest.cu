@@ -1,0 +1,134 @@
+// Stand-alone check of the tcgen05 GEMM core against a double-precision CPU product.
+//   sc_selftest M N K G a_mn b_mn BN nseg
+// Inputs are pre-rounded to TF32 on the host, so the only error left is fp32 accumulation order.
+// One configuration per process: a trapped kernel poisons the context, the shell loop moves on.
+#include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <vector>
+
+#include "epi_store.cuh"
+#include "tmap.h"
+
+using namespace sc;
+
+static float host_rn_tf32(float x) {
+    uint32_t u;
+    memcpy(&u, &x, 4);
+    u = (u + 0x0fffu + ((u >> 13) & 1u)) & 0xffffe000u;
+    memcpy(&x, &u, 4);
+    return x;
+}
+
+#define CK(x)                                                                          \
+    do {                                                                               \
+        cudaError_t e_ = (x);                                                          \
+        if (e_ != cudaSuccess) {                                                       \
+            printf("CUDA error %s at %s:%d\n", cudaGetErrorString(e_), __FILE__, __LINE__); \
+            return 2;                                                                  \
+        }                                                                              \
+    } while (0)
+
+template <int BN, bool A_MN, bool B_MN>
+static cudaError_t run(const GemmMaps& maps, const GemmShape& sh, const EpiStore::Params& ep, int sms) {
+    return launch_gemm<BN, A_MN, B_MN, EpiStore>(maps, sh, ep, sms, 0);
+}
+
+int main(int argc, char** argv) {
+    if (argc < 9) {
+        printf("usage: %s M N K G a_mn b_mn BN nseg\n", argv[0]);
+        return 1;
+    }
+    const int M = atoi(argv[1]), N = atoi(argv[2]), K = atoi(argv[3]), G = atoi(argv[4]);
+    const int a_mn = atoi(argv[5]), b_mn = atoi(argv[6]), BN = atoi(argv[7]), nseg = atoi(argv[8]);
+    const int ldA = a_mn ? ((M + 3) & ~3) : ((K + 3) & ~3);
+    const int ldB = b_mn ? ((N + 3) & ~3) : ((K + 3) & ~3);
+    const size_t szA = (size_t)(a_mn ? K : M) * ldA, szB = (size_t)(b_mn ? K : N) * ldB;
+    std::vector<std::vector<float>> hA(nseg), hB(nseg);
+    srand(1234);
+    for (int s = 0; s < nseg; ++s) {
+        hA[s].resize(szA * G);
+        hB[s].resize(szB * G);
+        for (auto& v : hA[s]) v = host_rn_tf32((rand() / (float)RAND_MAX) * 2.f - 1.f);
+        for (auto& v : hB[s]) v = host_rn_tf32((rand() / (float)RAND_MAX) * 2.f - 1.f);
+    }
+    auto A = [&](int s, int g, int m, int k) { return hA[s][g * szA + (a_mn ? (size_t)k * ldA + m : (size_t)m * ldA + k)]; };
+    auto B = [&](int s, int g, int n, int k) { return hB[s][g * szB + (b_mn ? (size_t)k * ldB + n : (size_t)n * ldB + k)]; };
+
+    int dev = 0, sms = 0;
+    CK(cudaSetDevice(dev));
+    CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    float *dA[kMaxSeg] = {}, *dB[kMaxSeg] = {}, *dC = nullptr;
+    GemmMaps maps;
+    memset(&maps, 0, sizeof maps);
+    GemmShape sh;
+    memset(&sh, 0, sizeof sh);
+    sh.M = M; sh.N = N; sh.G = G; sh.nseg = nseg;
+    const char* err = nullptr;
+    for (int s = 0; s < nseg; ++s) {
+        CK(cudaMalloc(&dA[s], hA[s].size() * 4));
+        CK(cudaMalloc(&dB[s], hB[s].size() * 4));
+        CK(cudaMemcpy(dA[s], hA[s].data(), hA[s].size() * 4, cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(dB[s], hB[s].data(), hB[s].size() * 4, cudaMemcpyHostToDevice));
+        Operand oa{dA[s], M, K, G, ldA, (int64_t)szA, a_mn != 0};
+        Operand ob{dB[s], N, K, G, ldB, (int64_t)szB, b_mn != 0};
+        if (make_operand_map(&maps.a[s], oa, 128, &err) || make_operand_map(&maps.b[s], ob, BN, &err)) {
+            printf("tensor map error: %s\n", err ? err : "?");
+            return 2;
+        }
+        sh.K[s] = K; sh.a_gmul[s] = G > 1; sh.b_gmul[s] = G > 1;
+    }
+    const int ldC = (N + 3) & ~3;
+    CK(cudaMalloc(&dC, (size_t)G * M * ldC * 4));
+    CK(cudaMemset(dC, 0xff, (size_t)G * M * ldC * 4));
+    EpiStore::Params ep{dC, ldC, (long long)M * ldC};
+
+    cudaError_t le = cudaErrorInvalidValue;
+#define DISPATCH(bn)                                                    \
+    if (BN == bn) {                                                     \
+        if (!a_mn && !b_mn) le = run<bn, false, false>(maps, sh, ep, sms); \
+        if (a_mn && !b_mn) le = run<bn, true, false>(maps, sh, ep, sms);   \
+        if (!a_mn && b_mn) le = run<bn, false, true>(maps, sh, ep, sms);   \
+        if (a_mn && b_mn) le = run<bn, true, true>(maps, sh, ep, sms);     \
+    }
+    DISPATCH(64) DISPATCH(128) DISPATCH(256)
+    CK(le);
+    CK(cudaDeviceSynchronize());
+
+    // timing (only meaningful for big shapes)
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    const int reps = 5;
+    CK(cudaEventRecord(e0));
+    for (int r = 0; r < reps; ++r) { DISPATCH(64) DISPATCH(128) DISPATCH(256) }
+    CK(cudaEventRecord(e1));
+    CK(cudaDeviceSynchronize());
+    float ms = 0;
+    CK(cudaEventElapsedTime(&ms, e0, e1));
+    ms /= reps;
+
+    std::vector<float> hC((size_t)G * M * ldC);
+    CK(cudaMemcpy(hC.data(), dC, hC.size() * 4, cudaMemcpyDeviceToHost));
+    double max_err = 0, max_ref = 0;
+    long long bad = 0;
+    // full check for small problems, sampled rows/cols for large ones
+    const int mstep = (long long)M * N * K * G > (1LL << 31) ? 37 : 1;
+    for (int g = 0; g < G; ++g)
+        for (int m = 0; m < M; m += mstep)
+            for (int n = 0; n < N; n += mstep) {
+                double acc = 0;
+                for (int s = 0; s < nseg; ++s)
+                    for (int k = 0; k < K; ++k) acc += (double)A(s, g, m, k) * (double)B(s, g, n, k);
+                const double got = hC[((size_t)g * M + m) * ldC + n];
+                const double e = fabs(got - acc);
+                if (!(e <= 1e-4 * sqrt((double)K * nseg) + 1e-5 * fabs(acc))) ++bad;
+                if (e > max_err || e != e) max_err = e;
+                if (fabs(acc) > max_ref) max_ref = fabs(acc);
+            }
+    const double flops = 2.0 * M * N * (double)K * G * nseg;
+    printf("M=%d N=%d K=%d G=%d a_mn=%d b_mn=%d BN=%d nseg=%d : max_err=%.3e (max |ref| %.3e) bad=%lld  %.3f ms  %.1f TFLOP/s  %s\n",
+           M, N, K, G, a_mn, b_mn, BN, nseg, max_err, max_ref, bad, ms, flops / ms * 1e-9, bad == 0 ? "PASS" : "FAIL");
+    return bad == 0 ? 0 : 3;
+}

@@ -1,0 +1,310 @@
+#!/usr/bin/env python
+"""Headline benchmark: ensemble-SAE train throughput (BASELINE.json configs[1]).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--batch B] [--impl reference]
+
+Workload (config.workload "pythia70m_l2_untied_sae"): M = 8 untied SAEs (L1 sweep
+np.logspace(-4,-2,8)), d = 512, 4096 features, Adam lr 1e-3, one FunctionalEnsemble.step_batch per
+step on a synthetic activation batch of B rows.  Multi-GPU: the ensemble shards naturally, one
+8-member group per GPU, no data-path collective ("weak" scaling), same per-GPU work.
+
+metric = member-activations per second = B * M_total / step_time.
+  value : inputs resident in HBM (a chunk larger than L2, a different batch slice each step)
+  e2e   : through the public API with the batch in pinned HOST memory, H2D copy of the batch and
+          D2H read of the loss scalars inside the timed region
+  roofline    : dominant kernel's algorithmic flops / its CUDA-event time vs the measured TF32 dense peak
+  cpu_baseline: the CPU oracle (oracle/restated.py, a port of the reference's torch path) on the host cores
+--impl reference times that same CPU port with all host threads and prints the same line shape.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+D_ACT, N_FEATS, M_PER_GPU = 512, 4096, 8
+METRIC = "sae_train_member_activations_per_sec"
+UNIT = "member-activations/s"
+
+
+def l1_values(m):
+    return np.logspace(-4, -2, m)
+
+
+def make_chunk(rows, d, seed, device):
+    """Synthetic sparse-feature activations of the named shape (sc_datasets/random_dataset.py style)."""
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    n_gt = 1024
+    feats = torch.randn(n_gt, d, generator=g)
+    feats /= feats.norm(dim=1, keepdim=True)
+    out = torch.empty(rows, d)
+    for i in range(0, rows, 16384):
+        n = min(16384, rows - i)
+        codes = torch.rand(n, n_gt, generator=g)
+        codes = codes * (torch.rand(n, n_gt, generator=g) < 10.0 / n_gt)
+        out[i:i + n] = codes @ feats
+    return out.to(device)
+
+
+# ------------------------------------------------------------------------------------------ CPU arm
+def cpu_port_steps(batch, steps, warmup, threads):
+    """Time the CPU port of the reference path (oracle/restated.EnsembleOracle) on `batch` rows."""
+    from oracle import restated as R
+    torch.set_num_threads(threads)
+    torch.manual_seed(0)
+    params = {"encoder": torch.stack([R.xavier_uniform(N_FEATS, D_ACT) for _ in range(M_PER_GPU)]),
+              "encoder_bias": torch.zeros(M_PER_GPU, N_FEATS),
+              "decoder": torch.stack([R.xavier_uniform(N_FEATS, D_ACT) for _ in range(M_PER_GPU)])}
+    buffers = {"l1_alpha": torch.tensor(l1_values(M_PER_GPU), dtype=torch.float32),
+               "bias_decay": torch.zeros(M_PER_GPU)}
+    orc = R.EnsembleOracle(params, buffers, tied=False, lr=1e-3)
+    data = make_chunk(batch * 4, D_ACT, 1, "cpu")
+    for i in range(warmup):
+        orc.step_batch(data[(i % 4) * batch:(i % 4 + 1) * batch])
+    t0 = time.perf_counter()
+    for i in range(steps):
+        orc.step_batch(data[(i % 4) * batch:(i % 4 + 1) * batch])
+    dt = time.perf_counter() - t0
+    return batch * M_PER_GPU * steps / dt, dt / steps
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    sample_b = min(args.batch, 512)
+    steps = max(1, min(args.steps, 12))
+    warmup = max(1, min(args.warmup, 2))
+    val, sec = cpu_port_steps(sample_b, steps, warmup, threads)
+    sample = (f"{steps} steps of {sample_b} rows (of the B={args.batch} workload) x {M_PER_GPU} members, "
+              f"oracle/restated.py torch-CPU fp32, {threads} threads")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
+        "warmup": warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "pythia70m_l2_untied_sae", "d": D_ACT, "n_feats": N_FEATS, "members": M_PER_GPU,
+                   "batch": args.batch, "sample_batch": sample_b},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+# ------------------------------------------------------------------------------------------ clocks
+class ClockSampler:
+    def __init__(self, index):
+        self.index, self.samples, self.reasons, self.stop = index, [], set(), False
+        self.max_mhz = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+        self.t = threading.Thread(target=self._run, daemon=True)
+
+    def _run(self):
+        names = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap",
+                 0x80: "hw_power_brake"}
+        while not self.stop and self.nv is not None:
+            try:
+                self.samples.append(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM))
+                r = self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.h) if hasattr(
+                    self.nv, "nvmlDeviceGetCurrentClocksEventReasons") else self.nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, nm in names.items():
+                    if r & bit:
+                        self.reasons.add(nm)
+            except Exception:
+                pass
+            time.sleep(0.05)
+
+    def __enter__(self):
+        self.t.start()
+        return self
+
+    def __exit__(self, *a):
+        self.stop = True
+        self.t.join(timeout=1)
+
+    def summary(self):
+        med = float(np.median(self.samples)) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+def measure_tf32_peak(device):
+    """Dense TF32 cuBLAS peak, same method as MEASURED_PEAKS.json's bf16 figure (8192^3, best of 10)."""
+    n = 8192
+    a = torch.randn(n, n, device=device)
+    b = torch.randn(n, n, device=device)
+    old = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = True
+    best = 1e9
+    for i in range(12):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        torch.matmul(a, b)
+        e1.record()
+        torch.cuda.synchronize()
+        if i >= 2:
+            best = min(best, e0.elapsed_time(e1))
+    torch.backends.cuda.matmul.allow_tf32 = old
+    del a, b
+    return 2.0 * n ** 3 / (best * 1e-3) / 1e12
+
+
+# ------------------------------------------------------------------------------------------ our arm
+def run_ours(args):
+    import torch.distributed as dist
+    import sparse_coding__b200 as sc
+    from sparse_coding__b200 import _native as nat
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+
+    B, M = args.batch, M_PER_GPU
+    torch.manual_seed(rank)  # every GPU trains its own group of members
+    models = [sc.FunctionalSAE.init(D_ACT, N_FEATS, float(l1), device=device) for l1 in l1_values(M)]
+    ens = sc.FunctionalEnsemble(models, sc.FunctionalSAE, sc.torchopt_compat.adam, {"lr": 1e-3}, device=device)
+    n_slices = max(8, (160 << 20) // (B * D_ACT * 4) + 1)  # chunk > L2 (126 MB)
+    chunk = make_chunk(n_slices * B, D_ACT, 1, device)
+    host_chunk = chunk.cpu().pin_memory()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def device_step(i):
+        s = i % n_slices
+        return ens.step_batch(chunk[s * B:(s + 1) * B])
+
+    def e2e_step(i):
+        s = i % n_slices
+        x = host_chunk[s * B:(s + 1) * B].to(device, non_blocking=True)
+        losses, _ = ens.step_batch(x)
+        return losses["loss"].cpu()
+
+    for i in range(args.warmup):
+        device_step(i)
+    barrier()
+    with ClockSampler(local) as clocks:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(args.steps):
+            device_step(i)
+        e1.record()
+        barrier()
+        ms_total = e0.elapsed_time(e1)
+    t = torch.tensor([ms_total], device=device)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_step = float(t.item()) / args.steps
+    value = B * M * world / (ms_step * 1e-3)
+
+    # end to end: pinned host batch -> device, loss scalars -> host, every step
+    for i in range(min(args.warmup, 5)):
+        e2e_step(i)
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        e2e_step(i)
+    barrier()
+    t = torch.tensor([time.perf_counter() - t0], device=device)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_value = B * M * world / (float(t.item()) / args.steps)
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # per-kernel CUDA-event times over profiled steps of the same workload
+    prof_steps = min(args.steps, 20)
+    nat.profile_begin()
+    for i in range(prof_steps):
+        device_step(i)
+    marks = nat.profile_end()
+    per = {}
+    for nm, ms in marks:
+        per.setdefault(nm, []).append(ms)
+    kernel_ms = {k: float(np.mean(v)) for k, v in per.items()}
+    gemm_flops = 2.0 * B * N_FEATS * D_ACT * M  # per GEMM launch (all members)
+    gemms = {k: v for k, v in kernel_ms.items() if k.startswith("G")}
+    dom = max(gemms, key=gemms.get)
+    tf32_peak = measure_tf32_peak(device)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    achieved = gemm_flops / (gemms[dom] * 1e-3) / 1e12
+    step_flops = 10.0 * B * N_FEATS * D_ACT * M
+    roofline = {
+        "bound": "tensor", "kernel": dom, "achieved": achieved, "peak": tf32_peak, "unit": "TFLOP/s",
+        "frac": achieved / tf32_peak, "traffic": None,
+        "peak_source": "measured here: torch.matmul TF32 8192^3 best of 10 (MEASURED_PEAKS.json has bf16 only; "
+                       "the kernels run kind::tf32)",
+        "bf16_peak_measured": peaks.get("bf16_tflops"),
+        "step_tflops": step_flops / (ms_step * 1e-3) / 1e12,
+        "step_frac_of_tf32_peak": step_flops / (ms_step * 1e-3) / 1e12 / tf32_peak,
+        "kernel_ms": kernel_ms,
+    }
+
+    threads = os.cpu_count() or 1
+    cpu_b = min(B, 512)
+    cpu_val, cpu_sec = cpu_port_steps(cpu_b, 3, 1, threads)
+    cpu_baseline = {"value": cpu_val, "unit": UNIT, "cores": threads, "kind": "port",
+                    "sample": f"3 steps of {cpu_b} rows x {M} members after 1 warm-up, oracle/restated.py torch-CPU fp32"}
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "tf32",
+        "data": "synthetic",
+        "config": {"workload": "pythia70m_l2_untied_sae", "d": D_ACT, "n_feats": N_FEATS, "members_per_gpu": M,
+                   "batch": B, "optimizer": "adam lr=1e-3 (reference-faithful t=1)", "parallelism": f"ensemble-shard x{world}",
+                   "l2_policy": f"inputs larger than L2: {n_slices} batch slices = {n_slices * B * D_ACT * 4 >> 20} MiB chunk, "
+                                "working set per step > 1 GB"},
+        "activations_per_sec": value / (M * world) ,
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": B * D_ACT * 4, "d2h_bytes_per_step": M * 4},
+        "gpu_launches": 8 * args.steps,
+        "roofline": roofline, "cpu_baseline": cpu_baseline, "clocks": clocks.summary(),
+    }
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--batch", type=int, default=2048)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

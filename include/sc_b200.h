@@ -1,0 +1,165 @@
+/* sc_b200.h - C ABI of the B200 (sm_100a) engine for ensemble sparse-autoencoder training.
+ *
+ * The reference (johnathan217/sparse_coding_) is pure Python/PyTorch and has no FFI of its own;
+ * the "operator API" of this path is the Python duck type consumed by
+ * autoencoders/ensemble.py:68-193.  Each entry point below replaces the torch.vmap / torchopt /
+ * cuBLAS call chain of the cited reference lines.  The Python mirror in sparse_coding__b200/
+ * binds these with ctypes (see INTEGRATION.md for the stub a reference maintainer would add).
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer to contiguous row-major fp32 unless stated otherwise,
+ *     16-byte aligned; d and N must be multiples of 4 (TMA strides are multiples of 16 bytes)
+ *   - the caller owns every buffer, including the workspace; the library allocates nothing on
+ *     the device and only caches immutable per-process state (function attributes)
+ *   - calls enqueue work on `stream` (a cudaStream_t) and return without synchronising
+ *   - return 0 = ok, < 0 = argument error caught before any launch, > 0 = cudaError_t;
+ *     sc_last_error() gives the message for the calling thread
+ *   - M = ensemble members, B = batch rows, d = activation width, N = dictionary size
+ */
+#ifndef SC_B200_H
+#define SC_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+int sc_version(void);
+const char* sc_last_error(void);
+
+/* Adam hyper-parameters as torchopt 0.7.1 `adam(lr, betas, eps, eps_root)` takes them
+ * (reference call sites ensemble.py:94-95,123,182).  bc1 = 1 - b1^t and bc2 = 1 - b2^t are the
+ * bias-correction denominators: the reference never advances its stored step count
+ * (ensemble.py:185-189 copies into a clone), so reference-faithful callers pass t = 1 forever. */
+typedef struct {
+    float lr, b1, b2, eps, eps_root;
+    float bc1, bc2;
+} ScAdam;
+
+/* One FunctionalEnsemble.step_batch (ensemble.py:175-193) for sig in
+ * {FunctionalSAE (sae_ensemble.py:13-77), FunctionalFista (fista.py:18-84, same loss),
+ *  FunctionalTiedSAE with identity or pre-applied centering (sae_ensemble.py:80-160)}:
+ * forward, loss terms, backward and the in-place Adam update of every member. */
+typedef struct {
+    int32_t M, B, d, N;
+    int32_t tied;           /* 0: encoder + bias + decoder, 1: encoder + bias, D = rownorm(encoder) both ways */
+    int32_t x_per_member;   /* 0: x is [B,d] shared by all members (expand_dims=True), 1: x is [M,B,d] */
+    const float* x;
+    float *enc, *enc_mu, *enc_nu;    /* [M,N,d] params["encoder"] and its Adam moments */
+    float *bias, *bias_mu, *bias_nu; /* [M,N]   params["encoder_bias"] */
+    float *dec, *dec_mu, *dec_nu;    /* [M,N,d] params["decoder"] (ignored when tied) */
+    const float* l1_alpha;           /* [M] buffers["l1_alpha"] */
+    const float* bias_decay;         /* [M] buffers["bias_decay"] */
+    ScAdam adam;
+    float* out_losses;      /* [4,M]: loss, l_reconstruction, l_l1, l_bias_decay (sae_ensemble.py:66-71) */
+    float* out_c;           /* [M,B,N] aux "c" (sae_ensemble.py:73-75); values are TF32-rounded, an entry
+                               whose pre-activation was negative is -0.0f */
+    void* workspace;        /* >= sc_sae_step_workspace_bytes(...) bytes, 1024-byte aligned */
+    size_t workspace_bytes;
+    void* stream;
+    /* Gradient-only mode (data-parallel training of one large dictionary, reference analogue
+     * experiments/huge_batch_size.py:259-335 DDP): when grad_enc is non-NULL the gradients of the total
+     * loss are WRITTEN to grad_enc / grad_bias / grad_dec (grad_dec ignored when tied) and no Adam
+     * update happens; the caller all-reduces them and calls sc_adam_apply.  B_total > 0 replaces B in
+     * the 1/B and 1/(B d) loss normalisations so that per-rank results add up to the global-batch ones. */
+    float *grad_enc, *grad_bias, *grad_dec;
+    int32_t B_total;
+} ScStepArgs;
+
+size_t sc_sae_step_workspace_bytes(int32_t M, int32_t B, int32_t d, int32_t N, int32_t tied, int32_t x_per_member);
+int sc_sae_step(const ScStepArgs* args);
+
+/* Elementwise Adam exactly as the fused epilogues apply it (torchopt 0.7.1 semantics, see ScAdam):
+ * p, mu, nu updated in place from gradient g, n elements (multiple of 4). */
+int sc_adam_apply(float* p, float* mu, float* nu, const float* g, int64_t n, const ScAdam* adam, void* stream);
+
+/* LearnedDict.encode (learned_dict.py:127-131 untied, :186-196 tied) for G dictionaries at once:
+ * c[g] = relu(x W[g]^T + b[g]).  W is used as given (the tied caller passes the row-normalised
+ * dictionary).  Optionally counts, per feature, the rows with c != 0
+ * (standard_metrics.py:303-306 mean_nonzero_activations, :439-452 n-ever-active). */
+typedef struct {
+    int32_t G, B, d, N;
+    int32_t x_per_group;
+    const float* x;         /* [B,d] or [G,B,d] */
+    const float* W;         /* [G,N,d] */
+    const float* bias;      /* [G,N] or NULL */
+    float* out_c;           /* [G,B,N] or NULL (statistics only) */
+    float* out_nonzero;     /* [G,N] count of rows with c != 0, accumulated (+=) into the buffer, or NULL */
+    float* out_moments;     /* [G,4,N] sums of c, c^2, c^3, c^4 over rows, accumulated, or NULL
+                               (standard_metrics.py:480-509 calc_moments_streaming) */
+    void* workspace;
+    size_t workspace_bytes;
+    void* stream;
+} ScEncodeArgs;
+size_t sc_encode_workspace_bytes(int32_t G, int32_t B, int32_t d, int32_t N, int32_t x_per_group);
+int sc_encode(const ScEncodeArgs* args);
+
+/* LearnedDict.decode (learned_dict.py:29-32): x_hat[g] = c[g] @ rownorm(Wd[g]) (normalise = 1) or
+ * c[g] @ Wd[g] (normalise = 0).  With `target` also returns sum((x_hat - target)^2) per group,
+ * the numerator of fraction_variance_unexplained (standard_metrics.py:308-312). */
+typedef struct {
+    int32_t G, B, d, N;
+    int32_t normalise;
+    int32_t target_per_group;
+    const float* c;         /* [G,B,N] */
+    const float* Wd;        /* [G,N,d] */
+    const float* target;    /* [B,d] or [G,B,d] or NULL */
+    float* out_x_hat;       /* [G,B,d] or NULL */
+    float* out_sq_err;      /* [G] or NULL */
+    void* workspace;
+    size_t workspace_bytes;
+    void* stream;
+} ScDecodeArgs;
+size_t sc_decode_workspace_bytes(int32_t G, int32_t B, int32_t d, int32_t N);
+int sc_decode(const ScDecodeArgs* args);
+
+/* FunctionalFista.fista (fista.py:99-128; method twin :274-301): num_iter FISTA iterations of
+ * min_a 0.5||x - a D||^2 + l1 ||a||_1, a >= 0, from the warm start a0.  Products run as split
+ * 3xTF32 (hi*hi + hi*lo + lo*hi) so the codes agree with the fp32 reference to ~1e-6 relative.
+ * eta <= 0 computes eta = 1/lambda_max(D^T D) by power iteration (fista.py:105-106 takes it from
+ * eigvalsh(D D^T): same value).  momentum[k] = (t_k - 1)/t_{k+1}, computed by the caller in
+ * float64 exactly as fista.py:117-118 does. */
+typedef struct {
+    int32_t B, d, N, num_iter;
+    const float* x;         /* [B,d] */
+    const float* D;         /* [N,d] dictionary, used as given */
+    const float* a0;        /* [B,N] warm start */
+    float l1_coef;
+    float eta;              /* <= 0: compute */
+    const float* momentum;  /* HOST pointer, [num_iter] */
+    float* out_a;           /* [B,N] */
+    float* out_res;         /* [B,d] x - a D */
+    float* out_eta;         /* device scalar, the step size used, or NULL */
+    void* workspace;
+    size_t workspace_bytes;
+    void* stream;
+} ScFistaArgs;
+size_t sc_fista_workspace_bytes(int32_t B, int32_t d, int32_t N);
+int sc_fista(const ScFistaArgs* args);
+
+/* LearnedDict.get_learned_dict (learned_dict.py:118-120, :172-174): out[g][n][:] = W[g][n][:] /
+ * max(||W[g][n]||_2, 1e-8), full fp32. */
+int sc_row_normalise(const float* W, float* out, int32_t G, int32_t N, int32_t d, void* stream);
+
+/* Denominator of fraction_variance_unexplained (standard_metrics.py:311): *out_sum =
+ * sum_{b,j} (x[b][j] - mean_b x[b][j])^2 for x [B,d].  workspace: at least (d + 1) floats. */
+int sc_column_variance(const float* x, float* out_sum, int32_t B, int32_t d, void* workspace, void* stream);
+
+/* Per-launch timing for bench.py: between sc_profile_begin() and sc_profile_end() every kernel the
+ * library launches is bracketed by CUDA events on the caller's stream.  sc_profile_end synchronises and
+ * returns up to `cap` (kernel name, milliseconds) pairs in launch order. */
+int sc_profile_begin(void);
+int sc_profile_end(const char** names, float* ms, int cap);
+
+/* Debug / validation hook: C[g] = A[g] B[g]^T through the tcgen05 core with plain store epilogue.
+ * a_mn / b_mn select MN-major storage ([K,M] / [K,N]) for the operand.  Inputs are used as given
+ * (the tensor core truncates to TF32). */
+int sc_gemm_tf32(const float* A, const float* Bm, float* C, int32_t G, int32_t M, int32_t N, int32_t K,
+                 int32_t a_mn, int32_t b_mn, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SC_B200_H */

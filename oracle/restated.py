@@ -334,3 +334,34 @@ def moments_streaming(c: Tensor, batch_size=1000):
 def xavier_uniform(n, d, generator=None, dtype=torch.float32):
     bound = math.sqrt(6.0 / (n + d))
     return (torch.rand(n, d, generator=generator, dtype=dtype) * 2 - 1) * bound
+
+
+# --------------------------------------------------------------------------- #
+# TF32-operand emulation of the untied step (what the GPU engine is DESIGNED to  #
+# compute: every GEMM operand rounded to TF32 round-to-nearest, fp32 accumulate). #
+# A sharper target than the fp32 reference: differences to it are accumulation    #
+# order only.  Used next to - never instead of - the fp32 parity checks.          #
+# --------------------------------------------------------------------------- #
+def rn_tf32(t: Tensor) -> Tensor:
+    i = t.contiguous().view(torch.int32)
+    return ((i + 0x0FFF + ((i >> 13) & 1)) & ~0x1FFF).view(torch.float32)
+
+
+def sae_grads_tf32(We, b, Wd, lam, beta, x):
+    q = rn_tf32
+    B, d = x.shape
+    z = q(x) @ q(We).T + b
+    c = torch.clamp(z, min=0.0)
+    D, cl = row_normalise(Wd)
+    cr, Dr = q(c), q(D)
+    r = cr @ Dr - x
+    Rm = q(r * (2.0 / (B * d)))
+    qq = Rm @ Dr.T
+    dz = (qq + (lam / B) * (c > 0).to(x.dtype)) * (z >= 0).to(x.dtype)
+    gWe = q(dz).T @ q(x)
+    bn = torch.sqrt((b * b).sum())
+    gb = dz.sum(0) + (beta * b / bn if float(bn) > 0 else 0.0)
+    gD = cr.T @ Rm
+    s = (cr * qq).sum(0)
+    gWd = (gD - s[:, None] * D) / cl[:, None]
+    return gWe, gb, gWd, cr

@@ -1,0 +1,323 @@
+"""FunctionalEnsemble on the B200 engine - host-side mirror of the reference's
+autoencoders/ensemble.py:15-193 (same constructor, attributes, state_dict keys and
+`step_batch` contract).  The vmap(grad(loss)) -> vmap(adam.update) -> apply_updates chain
+(ensemble.py:175-193) is one call into libsc_b200 (`sc_sae_step`).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Dict, List, Optional
+
+import numpy as np
+import torch
+
+from .. import _native as nat
+from ..torchopt_compat import EmptyState, ScaleByAdamState, spec_from
+
+
+class DictSignature:
+    """ensemble.py:15-22."""
+
+    @staticmethod
+    def to_learned_dict(params, buffers):
+        pass
+
+    @staticmethod
+    def loss(params, buffers, batch):
+        pass
+
+
+def optim_str_to_func(optim_str):
+    """ensemble.py:25-31."""
+    from .. import torchopt_compat
+    if optim_str == "adam":
+        return torchopt_compat.adam
+    raise ValueError("Unknown optimizer string: {}".format(optim_str))
+
+
+def stack_dict(models: list, device=None) -> Dict[str, torch.Tensor]:
+    """ensemble.py:50-56: stack the same leaf of every member on a new leading dim."""
+    keys = list(models[0].keys())
+    out = {}
+    for k in keys:
+        ts = [m[k] for m in models]
+        out[k] = torch.stack([t.detach() for t in ts]).to(device=device)
+    return out
+
+
+def unstack_dict(params: Dict[str, torch.Tensor], n_models: int, device=None) -> List[Dict[str, torch.Tensor]]:
+    """ensemble.py:59-65."""
+    return [{k: t[i].to(device=device) for k, t in params.items()} for i in range(n_models)]
+
+
+def _sig_kind(sig) -> str:
+    kind = getattr(sig, "_sc_kind", None)
+    if kind is None:
+        kind = {"FunctionalSAE": "untied", "FunctionalFista": "untied", "FunctionalTiedSAE": "tied"}.get(
+            getattr(sig, "__name__", ""), None)
+    if kind is None:
+        raise NotImplementedError(
+            f"signature {sig!r}: the B200 engine implements FunctionalSAE, FunctionalFista and FunctionalTiedSAE; "
+            "other signatures have no fused path (and there is no generic fallback)")
+    return kind
+
+
+class FunctionalEnsemble:
+    """Drop-in for reference ensemble.py:68-193.
+
+    `reference_faithful` (default True) reproduces the reference's Adam as it actually runs:
+    the stored step count is never advanced (ensemble.py:185-189 writes the new optimizer state
+    into a clone), so bias correction stays at t = 1.  Set it to False for textbook Adam.
+    """
+
+    def __init__(self, models, sig, optimizer_func, optimizer_kwargs, device=None, no_stacking=False):
+        if device is None:
+            self.device = models[0][0]["encoder"].device
+        else:
+            self.device = device
+        if torch.device(self.device).type != "cuda":
+            raise NotImplementedError(f"device {self.device}: this engine runs on CUDA sm_100a only (no CPU path)")
+        self.n_models = len(models)
+        params, buffers = tuple(zip(*models))
+        self.params = stack_dict(list(params), device=self.device)
+        self.buffers = stack_dict(list(buffers), device=self.device)
+        self.sig = sig
+        self.no_stacking = no_stacking
+        self.optimizer_func = optimizer_func
+        self.optimizer_kwargs = optimizer_kwargs
+        self.optim_states = self._init_optim_states()
+        self.reference_faithful = True
+        self.init_functions()
+
+    # ------------------------------------------------------------------ set-up
+    def _init_optim_states(self):
+        mu = {k: torch.zeros_like(v) for k, v in self.params.items()}
+        nu = {k: torch.zeros_like(v) for k, v in self.params.items()}
+        count = {k: torch.zeros(self.n_models, dtype=torch.int64, device=self.device) for k in self.params}
+        return (ScaleByAdamState(mu=mu, nu=nu, count=count), EmptyState())
+
+    def init_functions(self):
+        """ensemble.py:99-123 builds the vmapped closures; here: resolve the fused path."""
+        self._kind = _sig_kind(self.sig)
+        self._adam = spec_from(self.optimizer_func, self.optimizer_kwargs)
+        self._ws = nat.Workspace()
+        self._step = 0
+        if not hasattr(self, "reference_faithful"):
+            self.reference_faithful = True
+        nat.lib()  # fail now, loudly, if the native library is missing
+
+    @staticmethod
+    def from_state(state_dict):
+        """ensemble.py:125-143."""
+        self = FunctionalEnsemble.__new__(FunctionalEnsemble)
+        self.device = state_dict["device"]
+        self.n_models = state_dict["n_models"]
+        self.params = state_dict["params"]
+        self.buffers = state_dict["buffers"]
+        self.sig = state_dict["sig"]
+        self.no_stacking = state_dict["no_stacking"]
+        self.optimizer_func = state_dict["optimizer_func"]
+        self.optimizer_kwargs = state_dict["optimizer_kwargs"]
+        self.optim_states = state_dict["optim_states"]
+        self.reference_faithful = state_dict.get("reference_faithful", True)
+        self.init_functions()
+        return self
+
+    def unstack(self, device=None):
+        """ensemble.py:145-148."""
+        params = unstack_dict(self.params, self.n_models, device=device)
+        buffers = unstack_dict(self.buffers, self.n_models, device=device)
+        return list(zip(params, buffers))
+
+    def state_dict(self):
+        """ensemble.py:150-161 (same nine keys)."""
+        return {
+            "device": self.device,
+            "n_models": self.n_models,
+            "params": self.params,
+            "buffers": self.buffers,
+            "sig": self.sig,
+            "no_stacking": self.no_stacking,
+            "optimizer_func": self.optimizer_func,
+            "optimizer_kwargs": self.optimizer_kwargs,
+            "optim_states": self.optim_states,
+        }
+
+    def _map_state(self, fn):
+        st = self.optim_states[0]
+        self.optim_states = (ScaleByAdamState(mu={k: fn(v) for k, v in st.mu.items()},
+                                              nu={k: fn(v) for k, v in st.nu.items()},
+                                              count={k: fn(v) for k, v in st.count.items()}), EmptyState())
+
+    def to_device(self, device):
+        """ensemble.py:163-168."""
+        self.device = device
+        self.params = {k: v.to(device) for k, v in self.params.items()}
+        self.buffers = {k: v.to(device) for k, v in self.buffers.items()}
+        self._map_state(lambda t: t.to(device))
+
+    def to_shared_memory(self):
+        """ensemble.py:170-173 (CPU tensors only, as in torch)."""
+        for v in self.params.values():
+            v.share_memory_()
+        for v in self.buffers.values():
+            v.share_memory_()
+        st = self.optim_states[0]
+        for group in (st.mu, st.nu, st.count):
+            for v in group.values():
+                v.share_memory_()
+
+    # ------------------------------------------------------------------ the hot path
+    def _contig(self, store: dict, key: str, shape=None) -> torch.Tensor:
+        t = store[key]
+        if not t.is_cuda or t.dtype != torch.float32:
+            nat.require_cuda(t, key)
+        if not t.is_contiguous() or t.data_ptr() % 16:
+            t = t.contiguous().clone() if t.data_ptr() % 16 else t.contiguous()
+            store[key] = t  # callers assign into .params (big_sweep.py:198); keep the rebinding visible
+        if shape is not None and tuple(t.shape) != tuple(shape):
+            raise ValueError(f"{key}: expected shape {tuple(shape)}, got {tuple(t.shape)}")
+        return t
+
+    def _scalar_buffer(self, key: str) -> torch.Tensor:
+        """Per-member scalars as a contiguous float32 [M] device vector.  Recipes often build them from
+        numpy float64 values (basic_l1_sweep.py:71); the stored buffer keeps its dtype, the kernel gets a
+        cached float32 copy."""
+        t = self.buffers[key]
+        if t.is_cuda and t.dtype == torch.float32 and t.is_contiguous() and tuple(t.shape) == (self.n_models,):
+            return t
+        cache = self.__dict__.setdefault("_scalar_cache", {})
+        tag = (t.data_ptr(), t._version, t.dtype)
+        hit = cache.get(key)
+        if hit is None or hit[0] != tag:
+            v = t.detach().to(device=self.device, dtype=torch.float32).reshape(self.n_models).contiguous()
+            cache[key] = (tag, v)
+            hit = cache[key]
+        return hit[1]
+
+    def _centered_batch(self, x: torch.Tensor, expand: bool):
+        """FunctionalTiedSAE.center (sae_ensemble.py:126-127) with per-member buffers.  Identity
+        buffers (the default, :97-108) skip it; otherwise the batch is centred once per step with a
+        plain library GEMM - a constant pre-transform of the input, not part of the trained graph."""
+        b = self.buffers
+        rot, tr, sc = b["center_rot"], b["center_trans"], b["center_scale"]
+        key = (rot.data_ptr(), rot._version, tr.data_ptr(), tr._version, sc.data_ptr(), sc._version)
+        if getattr(self, "_center_key", None) != key:
+            d = rot.shape[-1]
+            eye = torch.eye(d, device=rot.device, dtype=rot.dtype)
+            self._center_identity = bool((rot == eye).all() and (tr == 0).all() and (sc == 1).all())
+            self._center_key = key
+        if self._center_identity:
+            return x, not expand
+        xm = x.unsqueeze(0) if expand else x
+        xc = torch.einsum("mcu,mbu->mbc", rot, xm - tr[:, None, :]) * sc[:, None, :]
+        return xc.contiguous(), True
+
+    def step_batch(self, minibatches, expand_dims=True):
+        """ensemble.py:175-193.  Returns (loss_dict of [M] tensors, {"c": [M,B,N]})."""
+        return self._run(minibatches, expand_dims, grad_only=False)
+
+    def compute_grads(self, minibatches, expand_dims=True, batch_total=0, bias_decay=None):
+        """Gradient-only twin of step_batch: what vmap(grad(sig.loss)) returns at ensemble.py:180,
+        without the Adam update.  `batch_total` (> 0) replaces the local batch size in the loss
+        normalisation (data-parallel shards); `bias_decay` overrides buffers["bias_decay"].
+        Returns (grads dict like .params, loss_dict, {"c": ...})."""
+        return self._run(minibatches, expand_dims, grad_only=True, batch_total=batch_total, bias_decay=bias_decay)
+
+    def adam_constants(self, advance=True):
+        """(ScAdam for this step)."""
+        if advance:
+            self._step += 1
+        t = 1 if self.reference_faithful else max(self._step, 1)
+        a = self._adam
+        # torchopt: mu.div(1 - b1 ** count_inc) with a float32 tensor power
+        bc1 = float(np.float32(1.0) - np.float32(a.b1) ** np.float32(t))
+        bc2 = float(np.float32(1.0) - np.float32(a.b2) ** np.float32(t))
+        if advance and not self.reference_faithful:
+            for cnt in self.optim_states[0].count.values():
+                cnt += 1
+        return nat.ScAdam(a.lr, a.b1, a.b2, a.eps, a.eps_root, bc1, bc2)
+
+    def apply_grads(self, grads):
+        """vmap(optimizer.update) + apply_updates (ensemble.py:182-191) from explicit gradients."""
+        L = nat.lib()
+        adam = self.adam_constants(advance=True)
+        st = self.optim_states[0]
+        for k, g in grads.items():
+            p = self._contig(self.params, k)
+            mu, nu = self._contig(st.mu, k, p.shape), self._contig(st.nu, k, p.shape)
+            g = g.contiguous()
+            with torch.cuda.device(p.device):
+                nat.check(L.sc_adam_apply(nat.ptr(p), nat.ptr(mu), nat.ptr(nu), nat.ptr(g), p.numel(), C.byref(adam),
+                                          nat.stream_ptr(p.device)), "sc_adam_apply")
+
+    def _run(self, minibatches, expand_dims, grad_only, batch_total=0, bias_decay=None):
+        L = nat.lib()
+        M = self.n_models
+        x = minibatches
+        nat.require_cuda(x, "minibatches")
+        if self.no_stacking and expand_dims:
+            # reference ensemble.py:100-116 indexes batch[i] per member in this mode
+            expand_dims = False
+        if expand_dims:
+            if x.dim() != 2:
+                raise ValueError(f"expected a [B, d] batch, got {tuple(x.shape)}")
+        else:
+            if x.dim() != 3 or x.shape[0] != M:
+                raise ValueError(f"expected an [M={M}, B, d] batch, got {tuple(x.shape)}")
+        x = x.contiguous()
+        tied = self._kind == "tied"
+        per_member = not expand_dims
+        if tied:
+            x, per_member = self._centered_batch(x, expand_dims)
+        B, d = x.shape[-2], x.shape[-1]
+        enc = self._contig(self.params, "encoder")
+        N = enc.shape[1]
+        if enc.shape != (M, N, d):
+            raise ValueError(f"encoder shape {tuple(enc.shape)} does not match batch width {d}")
+        bias = self._contig(self.params, "encoder_bias", (M, N))
+        st = self.optim_states[0]
+        enc_mu, enc_nu = self._contig(st.mu, "encoder", enc.shape), self._contig(st.nu, "encoder", enc.shape)
+        b_mu, b_nu = self._contig(st.mu, "encoder_bias", (M, N)), self._contig(st.nu, "encoder_bias", (M, N))
+        if tied:
+            dec = dec_mu = dec_nu = None
+        else:
+            dec = self._contig(self.params, "decoder", enc.shape)
+            dec_mu, dec_nu = self._contig(st.mu, "decoder", enc.shape), self._contig(st.nu, "decoder", enc.shape)
+        l1 = self._scalar_buffer("l1_alpha")
+        bd = self._scalar_buffer("bias_decay") if bias_decay is None else bias_decay.to(torch.float32).contiguous()
+
+        adam = self.adam_constants(advance=not grad_only)
+        grads = None
+        if grad_only:
+            grads = {"encoder": torch.empty_like(enc), "encoder_bias": torch.empty_like(bias)}
+            if not tied:
+                grads["decoder"] = torch.empty_like(dec)
+
+        losses = torch.empty((4, M), dtype=torch.float32, device=x.device)
+        c = torch.empty((M, B, N), dtype=torch.float32, device=x.device)
+        need = L.sc_sae_step_workspace_bytes(M, B, d, N, int(tied), int(per_member))
+        ws_ptr, ws_bytes = self._ws.aligned(need, x.device)
+        args = nat.ScStepArgs(
+            M=M, B=B, d=d, N=N, tied=int(tied), x_per_member=int(per_member),
+            x=nat.ptr(x), enc=nat.ptr(enc), enc_mu=nat.ptr(enc_mu), enc_nu=nat.ptr(enc_nu),
+            bias=nat.ptr(bias), bias_mu=nat.ptr(b_mu), bias_nu=nat.ptr(b_nu),
+            dec=nat.ptr(dec), dec_mu=nat.ptr(dec_mu), dec_nu=nat.ptr(dec_nu),
+            l1_alpha=nat.ptr(l1), bias_decay=nat.ptr(bd), adam=adam,
+            out_losses=nat.ptr(losses), out_c=nat.ptr(c),
+            workspace=ws_ptr, workspace_bytes=ws_bytes, stream=nat.stream_ptr(x.device),
+            grad_enc=nat.ptr(grads["encoder"]) if grad_only else None,
+            grad_bias=nat.ptr(grads["encoder_bias"]) if grad_only else None,
+            grad_dec=nat.ptr(grads.get("decoder")) if grad_only else None,
+            B_total=int(batch_total),
+        )
+        with torch.cuda.device(x.device):
+            nat.check(L.sc_sae_step(C.byref(args)), "sc_sae_step")
+        loss_dict = {"loss": losses[0], "l_reconstruction": losses[1], "l_l1": losses[2]}
+        if not tied:  # FunctionalTiedSAE's loss_data has no l_bias_decay key (sae_ensemble.py:150-154)
+            loss_dict["l_bias_decay"] = losses[3]
+        elif grad_only:
+            loss_dict["l_bias_decay"] = losses[3]
+        if grad_only:
+            return grads, loss_dict, {"c": c}
+        return loss_dict, {"c": c}

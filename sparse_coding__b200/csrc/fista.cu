@@ -1,0 +1,282 @@
+// sc_fista: batched FISTA sparse inference (reference autoencoders/fista.py:99-128, twin :274-301).
+//
+// Per iteration k (fista.py:116-125):
+//   Res = x - y D                      F1: [B x d] GEMM, K = N, epilogue forms the residual
+//   y   = y + eta Res D^T              F2: [B x N] GEMM, K = d, epilogue does the rest:
+//   a   = max(y - eta l1, 0)
+//   y   = a + mom_k (a - a_prev)
+// The reference runs these in fp32 and the parity gate is 1e-4 absolute on the codes after 300
+// iterations, so plain TF32 products are not enough.  Every operand is kept as an exact hi + lo
+// pair of TF32 numbers (hi = rn_tf32(v), lo = rn_tf32(v - hi)) and each product runs as three
+// tensor-core passes hi*hi + hi*lo + lo*hi accumulated in the same TMEM tile ("3xTF32", relative
+// error ~2^-21); the GEMM core's operand segments do this without extra kernels.
+// The tensor core adds each instruction's products into the TMEM accumulator with truncation, a bias of
+// about 3e-8 x |accumulator| per instruction for same-sign sums (measured: -2.7e-5 on a K = 2000 Gram
+// diagonal over 750 instructions).  The two small cross terms therefore run FIRST, while the
+// accumulator is still tiny, and hi*hi last: only K/8 instructions see the full magnitude.
+#include "../../include/sc_b200.h"
+#include "host_common.cuh"
+#include "sae_epilogues.cuh"
+
+namespace sc {
+
+// v -> (hi, lo) TF32 pair, optionally also a plain copy
+__global__ void split_kernel(const float4* __restrict__ in, float4* __restrict__ hi, float4* __restrict__ lo,
+                             float4* __restrict__ copy, long long n4) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+        const float4 v = in[i];
+        float4 h, l;
+        h.x = rn_tf32(v.x); h.y = rn_tf32(v.y); h.z = rn_tf32(v.z); h.w = rn_tf32(v.w);
+        l.x = rn_tf32(v.x - h.x); l.y = rn_tf32(v.y - h.y); l.z = rn_tf32(v.z - h.z); l.w = rn_tf32(v.w - h.w);
+        hi[i] = h;
+        lo[i] = l;
+        if (copy) copy[i] = v;
+    }
+}
+
+// F1 epilogue: res = x - acc -> (res_hi, res_lo) for F2, or the full-precision residual at the end
+struct EpiFistaRes {
+    struct Params {
+        const float* x;
+        float *res_hi, *res_lo, *res_full;
+    };
+    const Params& p;
+    const RowCtx c;
+    SC_DEVICE EpiFistaRes(const Params& p_, const RowCtx& c_) : p(p_), c(c_) {}
+    SC_DEVICE void chunk(int co, float (&v)[32]) {
+        const int col = c.col0 + co;
+        if (c.row >= c.M || col >= c.N) return;
+        const int ncols = c.N - col;
+        const long long off = (long long)c.row * c.N + col;
+        float xv[32];
+        load_row32(p.x + off, xv, ncols);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = xv[j] - v[j];
+        if (p.res_full) store_row32(p.res_full + off, v, ncols);
+        if (p.res_hi) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                xv[j] = rn_tf32(v[j]);
+                v[j] = rn_tf32(v[j] - xv[j]);
+            }
+            store_row32(p.res_hi + off, xv, ncols);
+            store_row32(p.res_lo + off, v, ncols);
+        }
+    }
+    SC_DEVICE void finish() {}
+};
+
+// F2 epilogue: gradient step, shrink + ReLU, momentum (fista.py:121-123)
+struct EpiFistaStep {
+    struct Params {
+        float* y;         // [B][N] in: y_k, out: y_{k+1}
+        float* a;         // [B][N] in: a_{k-1}, out: a_k
+        float *y_hi, *y_lo;
+        const float* eta; // device scalar
+        float l1, mom;
+    };
+    const Params& p;
+    const RowCtx c;
+    float eta, thr;
+    SC_DEVICE EpiFistaStep(const Params& p_, const RowCtx& c_) : p(p_), c(c_) {
+        eta = *p.eta;
+        thr = eta * p.l1;
+    }
+    SC_DEVICE void chunk(int co, float (&v)[32]) {
+        const int col = c.col0 + co;
+        if (c.row >= c.M || col >= c.N) return;
+        const int ncols = c.N - col;
+        const long long off = (long long)c.row * c.N + col;
+        float yv[32], av[32];
+        load_row32(p.y + off, yv, ncols);
+        load_row32(p.a + off, av, ncols);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            const float yn = yv[j] + eta * v[j];         // ahat_y.add(eta * Res D^T)
+            const float an = fmaxf(yn - thr, 0.f);       // .sub(eta*l1).clamp(min=0)
+            yv[j] = an + (an - av[j]) * p.mom;           // ahat.add(ahat.sub(ahat_pre).mul(mom))
+            av[j] = an;
+        }
+        store_row32(p.a + off, av, ncols);
+        store_row32(p.y + off, yv, ncols);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            av[j] = rn_tf32(yv[j]);
+            yv[j] = rn_tf32(yv[j] - av[j]);
+        }
+        store_row32(p.y_hi + off, av, ncols);
+        store_row32(p.y_lo + off, yv, ncols);
+    }
+    SC_DEVICE void finish() {}
+};
+
+// eta = 1 / lambda_max(G), G = D^T D [d x d] symmetric PSD (fista.py:105-106 takes it from
+// eigvalsh(D D^T): same non-zero spectrum).  Plain power iteration stalls when the top eigenvalues
+// are close (random dictionaries: Marchenko-Pastur edge), so the matrix is first squared kSquarings
+// times on the tensor cores (T <- (T/tr T)^2, 3xTF32): T becomes the 2^k-th power of G up to scale and
+// a handful of power steps on it isolate the top eigenvector; lambda is then the Rayleigh quotient of
+// that vector with the ORIGINAL fp32 G, whose error is second order in the vector's.
+constexpr int kSquarings = 14;
+
+__global__ void normalise_split_kernel(const float* __restrict__ T, int d, float* __restrict__ hi, float* __restrict__ lo) {
+    __shared__ float sh[8];
+    float acc = 0.f;
+    for (int i = threadIdx.x; i < d; i += blockDim.x) acc += T[(long long)i * d + i];
+    const float inv = 1.0f / block_sum(acc, sh);
+    const long long n = (long long)d * d;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const float v = T[i] * inv;
+        const float h = rn_tf32(v);
+        hi[i] = h;
+        lo[i] = rn_tf32(v - h);
+    }
+}
+
+// One CTA: v <- T v (iters times, normalised), then eta = (v.v) / (v.G v).
+__global__ void top_eigen_kernel(const float* __restrict__ T, const float* __restrict__ G, int d, float* __restrict__ v0,
+                                 float* __restrict__ v1, float* __restrict__ out_eta, int iters) {
+    __shared__ float sh[8];
+    const int tid = threadIdx.x, nthreads = blockDim.x, warp = tid >> 5, lane = tid & 31, nwarps = nthreads >> 5;
+    for (int i = tid; i < d; i += nthreads) v0[i] = 1.0f + 0.25f * (float)((i * 37) % 101) / 101.f;
+    __syncthreads();
+    float* vin = v0;
+    float* vout = v1;
+    for (int it = 0; it <= iters; ++it) {
+        const float* Mx = it < iters ? T : G;
+        for (int r = warp; r < d; r += nwarps) {
+            float acc = 0.f;
+            for (int j = lane; j < d; j += 32) acc += Mx[(long long)r * d + j] * vin[j];
+            acc = warp_sum(acc);
+            if (lane == 0) vout[r] = acc;
+        }
+        __syncthreads();
+        if (it == iters) {
+            float num = 0.f, den = 0.f;
+            for (int i = tid; i < d; i += nthreads) { num += vin[i] * vout[i]; den += vin[i] * vin[i]; }
+            num = block_sum(num, sh);
+            den = block_sum(den, sh);
+            if (tid == 0) *out_eta = den / num;
+        } else {
+            float nn = 0.f;
+            for (int i = tid; i < d; i += nthreads) nn += vout[i] * vout[i];
+            const float inv = rsqrtf(block_sum(nn, sh));
+            for (int i = tid; i < d; i += nthreads) vout[i] *= inv;
+            __syncthreads();
+            float* t = vin; vin = vout; vout = t;
+        }
+    }
+}
+
+__global__ void set_scalar_kernel(float* p, float v) { *p = v; }
+
+struct FistaWs {
+    float *D_hi, *D_lo, *y, *y_hi, *y_lo, *res_hi, *res_lo, *gram, *pw, *pw_hi, *pw_lo, *v0, *v1, *eta;
+    size_t bytes;
+};
+
+static FistaWs carve_fista(void* base, int B, int d, int N) {
+    FistaWs w;
+    Carver c(base);
+    const size_t Bz = B, dz = d, Nz = N;
+    w.D_hi = c.floats(Nz * dz); w.D_lo = c.floats(Nz * dz);
+    w.y = c.floats(Bz * Nz); w.y_hi = c.floats(Bz * Nz); w.y_lo = c.floats(Bz * Nz);
+    w.res_hi = c.floats(Bz * dz); w.res_lo = c.floats(Bz * dz);
+    w.gram = c.floats(dz * dz); w.pw = c.floats(dz * dz); w.pw_hi = c.floats(dz * dz); w.pw_lo = c.floats(dz * dz);
+    w.v0 = c.floats(dz); w.v1 = c.floats(dz); w.eta = c.floats(4);
+    w.bytes = c.off;
+    return w;
+}
+
+static int split(const float* in, float* hi, float* lo, float* copy, long long n, cudaStream_t st) {
+    const long long n4 = n / 4;
+    const int grid = static_cast<int>(n4 / 256 + 1 < 4096 ? n4 / 256 + 1 : 4096);
+    split_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const float4*>(in), reinterpret_cast<float4*>(hi),
+                                       reinterpret_cast<float4*>(lo), reinterpret_cast<float4*>(copy), n4);
+    SC_CUDA(cudaGetLastError(), "split launch");
+    return 0;
+}
+
+static int fista_impl(const ScFistaArgs& a) {
+    const int B = a.B, d = a.d, N = a.N;
+    if (B <= 0 || d <= 0 || N <= 0 || a.num_iter < 0) return fail(-1, "bad FISTA shape");
+    if ((d & 3) || (N & 3)) return fail(-1, "d and N must be multiples of 4 (got d=%d N=%d)", d, N);
+    if (!a.x || !a.D || !a.a0 || !a.out_a || !a.out_res || !a.workspace) return fail(-1, "NULL pointer argument");
+    if (a.num_iter > 0 && !a.momentum) return fail(-1, "momentum is NULL");
+    const FistaWs w = carve_fista(a.workspace, B, d, N);
+    if (a.workspace_bytes < w.bytes) return fail(-1, "workspace too small: %zu given, %zu needed", a.workspace_bytes, w.bytes);
+    cudaStream_t st = static_cast<cudaStream_t>(a.stream);
+    const long long BN_ = (long long)B * N, Nd = (long long)N * d;
+
+    SC_TRY(split(a.D, w.D_hi, w.D_lo, nullptr, Nd, st));
+    SC_TRY(split(a.a0, w.y_hi, w.y_lo, w.y, BN_, st));
+    SC_CUDA(cudaMemcpyAsync(a.out_a, a.a0, BN_ * sizeof(float), cudaMemcpyDeviceToDevice, st), "copy a0");
+
+    if (a.eta > 0.f) {
+        set_scalar_kernel<<<1, 1, 0, st>>>(w.eta, a.eta);
+    } else {
+        // G = D^T D in 3xTF32: both operands MN-major views of D (mn = d, k = N)
+        Seg s[3] = {{mnmajor(w.D_hi, d, N, 1, 0), mnmajor(w.D_lo, d, N, 1, 0)},
+                    {mnmajor(w.D_lo, d, N, 1, 0), mnmajor(w.D_hi, d, N, 1, 0)},
+                    {mnmajor(w.D_hi, d, N, 1, 0), mnmajor(w.D_hi, d, N, 1, 0)}};
+        EpiStore::Params ep{w.gram, d, 0};
+        SC_TRY((run_gemm<true, true, EpiStore>(d, d, 1, s, 3, ep, st)));
+        // repeated squaring of the trace-normalised matrix (symmetric, so B = A works K-major)
+        Seg q[3] = {{kmajor(w.pw_hi, d, d, 1, 0), kmajor(w.pw_lo, d, d, 1, 0)},
+                    {kmajor(w.pw_lo, d, d, 1, 0), kmajor(w.pw_hi, d, d, 1, 0)},
+                    {kmajor(w.pw_hi, d, d, 1, 0), kmajor(w.pw_hi, d, d, 1, 0)}};
+        GemmPlan sq;
+        SC_TRY(plan_gemm(&sq, d, d, 1, q, 3, false, false));
+        EpiStore::Params eq{w.pw, d, 0};
+        const int ngrid = ceil_div((long long)d * d, 256 * 4) < 148 ? ceil_div((long long)d * d, 256 * 4) : 148;
+        for (int k = 0; k < kSquarings; ++k) {
+            normalise_split_kernel<<<ngrid, 256, 0, st>>>(k == 0 ? w.gram : w.pw, d, w.pw_hi, w.pw_lo);
+            SC_TRY((launch_plan<false, false, EpiStore>(sq, eq, st)));
+        }
+        top_eigen_kernel<<<1, 256, 0, st>>>(w.pw, w.gram, d, w.v0, w.v1, w.eta, 6);
+    }
+    SC_CUDA(cudaGetLastError(), "eta launch");
+
+    // F1: acc = y D     A = y [B,N] K-major (k = N), B = D MN-major view (mn = d, k = N)
+    GemmPlan p1, p2;
+    {
+        Seg s[3] = {{kmajor(w.y_hi, B, N, 1, 0), mnmajor(w.D_lo, d, N, 1, 0)},
+                    {kmajor(w.y_lo, B, N, 1, 0), mnmajor(w.D_hi, d, N, 1, 0)},
+                    {kmajor(w.y_hi, B, N, 1, 0), mnmajor(w.D_hi, d, N, 1, 0)}};
+        SC_TRY(plan_gemm(&p1, B, d, 1, s, 3, false, true));
+    }
+    // F2: acc = Res D^T  A = Res [B,d] K-major, B = D [N,d] K-major
+    {
+        Seg s[3] = {{kmajor(w.res_hi, B, d, 1, 0), kmajor(w.D_lo, N, d, 1, 0)},
+                    {kmajor(w.res_lo, B, d, 1, 0), kmajor(w.D_hi, N, d, 1, 0)},
+                    {kmajor(w.res_hi, B, d, 1, 0), kmajor(w.D_hi, N, d, 1, 0)}};
+        SC_TRY(plan_gemm(&p2, B, N, 1, s, 3, false, false));
+    }
+    for (int k = 0; k < a.num_iter; ++k) {
+        EpiFistaRes::Params e1{a.x, w.res_hi, w.res_lo, nullptr};
+        SC_TRY((launch_plan<false, true, EpiFistaRes>(p1, e1, st)));
+        EpiFistaStep::Params e2{w.y, a.out_a, w.y_hi, w.y_lo, w.eta, a.l1_coef, a.momentum[k]};
+        SC_TRY((launch_plan<false, false, EpiFistaStep>(p2, e2, st)));
+    }
+    // final residual from ahat (fista.py:126): reuse the y_hi/y_lo operand buffers for the split of a
+    SC_TRY(split(a.out_a, w.y_hi, w.y_lo, nullptr, BN_, st));
+    EpiFistaRes::Params e3{a.x, nullptr, nullptr, a.out_res};
+    SC_TRY((launch_plan<false, true, EpiFistaRes>(p1, e3, st)));
+    if (a.out_eta) SC_CUDA(cudaMemcpyAsync(a.out_eta, w.eta, sizeof(float), cudaMemcpyDeviceToDevice, st), "copy eta");
+    return 0;
+}
+
+}  // namespace sc
+
+extern "C" {
+
+size_t sc_fista_workspace_bytes(int32_t B, int32_t d, int32_t N) {
+    if (B <= 0 || d <= 0 || N <= 0) return 0;
+    return sc::carve_fista(nullptr, B, d, N).bytes;
+}
+
+int sc_fista(const ScFistaArgs* args) {
+    if (!args) return sc::fail(-1, "args is NULL");
+    return sc::fista_impl(*args);
+}
+
+}  // extern "C"

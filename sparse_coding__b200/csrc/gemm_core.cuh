@@ -60,6 +60,7 @@ struct RowCtx {
     int col0;    // first global column of the tile
     int M, N;    // logical extents
     int tile_m, tile_n;
+    int tiles_m, tiles_n;
     int warp_q;  // which 32-row quarter of the tile this warp owns (0..3)
 };
 
@@ -201,7 +202,7 @@ gemm_tf32_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
             const uint32_t aph = (it >> 1) & 1;
             RowCtx ctx;
             ctx.g = g; ctx.row = tm * kBlockM + q * 32 + lane; ctx.col0 = tn * BN;
-            ctx.M = shape.M; ctx.N = shape.N; ctx.tile_m = tm; ctx.tile_n = tn; ctx.warp_q = q;
+            ctx.M = shape.M; ctx.N = shape.N; ctx.tile_m = tm; ctx.tile_n = tn; ctx.tiles_m = shape.tiles_m; ctx.tiles_n = shape.tiles_n; ctx.warp_q = q;
             Epi epi(ep, ctx);
             mbar_wait(&tmem_full[as], aph);
             tc_fence_after();

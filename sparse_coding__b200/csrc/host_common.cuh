@@ -1,0 +1,153 @@
+// Host-side plumbing shared by the C-ABI entry points: error reporting, workspace carving and the
+// "describe operands -> build TMA maps -> launch the tcgen05 core" helper.
+#pragma once
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "gemm_core.cuh"
+#include "tmap.h"
+
+namespace sc {
+
+extern thread_local char g_last_error[512];
+
+inline int fail(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_last_error, sizeof g_last_error, fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+inline int cuda_fail(cudaError_t e, const char* what) {
+    snprintf(g_last_error, sizeof g_last_error, "%s: %s", what, cudaGetErrorString(e));
+    return static_cast<int>(e);
+}
+
+#define SC_TRY(expr)            \
+    do {                        \
+        int rc_ = (expr);       \
+        if (rc_ != 0) return rc_; \
+    } while (0)
+
+#define SC_CUDA(expr, what)                              \
+    do {                                                 \
+        cudaError_t e_ = (expr);                         \
+        if (e_ != cudaSuccess) return cuda_fail(e_, what); \
+    } while (0)
+
+inline int device_sm_count(int* out) {
+    static int cached[64] = {};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetDevice");
+    if (!cached[dev & 63]) {
+        int cc_major = 0;
+        e = cudaDeviceGetAttribute(&cc_major, cudaDevAttrComputeCapabilityMajor, dev);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaDeviceGetAttribute");
+        if (cc_major != 10)
+            return fail(-2, "this library is built for sm_100a only; device %d has compute capability %d.x", dev, cc_major);
+        int n = 0;
+        e = cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaDeviceGetAttribute");
+        cached[dev & 63] = n;
+    }
+    *out = cached[dev & 63];
+    return 0;
+}
+
+// Optional per-launch timing: when enabled (sc_profile_begin), every mark records an event on the
+// caller's stream; sc_profile_end returns the elapsed time between consecutive marks.
+struct Profiler {
+    bool on = false;
+    int n = 0;
+    static constexpr int kMax = 4096;
+    cudaEvent_t ev[kMax];
+    const char* name[kMax];
+};
+extern Profiler g_prof;
+inline void prof_mark(cudaStream_t st, const char* name) {
+    if (!g_prof.on || g_prof.n >= Profiler::kMax) return;
+    cudaEvent_t e;
+    if (cudaEventCreate(&e) != cudaSuccess) return;
+    cudaEventRecord(e, st);
+    g_prof.ev[g_prof.n] = e;
+    g_prof.name[g_prof.n] = name;
+    ++g_prof.n;
+}
+
+// Bump allocator over the caller's workspace; every block is 1024-byte aligned.
+struct Carver {
+    uint8_t* base;
+    size_t off;
+    explicit Carver(void* p) : base(static_cast<uint8_t*>(p)), off(0) {}
+    float* floats(size_t n) {
+        float* r = reinterpret_cast<float*>(base + off);
+        off += (n * sizeof(float) + 1023) & ~size_t(1023);
+        return r;
+    }
+};
+
+inline int pick_bn(long long n) { return n > 128 ? 256 : (n > 64 ? 128 : 64); }
+inline int ceil_div(long long a, long long b) { return static_cast<int>((a + b - 1) / b); }
+
+struct Seg {
+    Operand a, b;
+};
+
+inline Operand kmajor(const float* base, long long mn, long long k, long long g, long long gstride) {
+    return Operand{base, mn, k, g, k, gstride, false};
+}
+inline Operand mnmajor(const float* base, long long mn, long long k, long long g, long long gstride) {
+    return Operand{base, mn, k, g, mn, gstride, true};
+}
+
+// A prepared launch: TMA maps + shape; reusable while the operand addresses and shapes stay the same.
+struct GemmPlan {
+    GemmMaps maps;
+    GemmShape sh;
+    int bn;
+    int sms;
+};
+
+inline int plan_gemm(GemmPlan* pl, int M, int N, int G, const Seg* segs, int nseg, bool a_mn, bool b_mn) {
+    memset(pl, 0, sizeof *pl);
+    SC_TRY(device_sm_count(&pl->sms));
+    pl->bn = pick_bn(N);
+    GemmShape& sh = pl->sh;
+    sh.M = M; sh.N = N; sh.G = G; sh.nseg = nseg;
+    for (int s = 0; s < nseg; ++s) {
+        if (segs[s].a.mn_major != a_mn || segs[s].b.mn_major != b_mn) return fail(-3, "operand major mismatch");
+        if (segs[s].a.k != segs[s].b.k || segs[s].a.k <= 0) return fail(-3, "segment K mismatch");
+        const char* err = nullptr;
+        int rc = make_operand_map(&pl->maps.a[s], segs[s].a, kBlockM, &err);
+        if (rc == 0) rc = make_operand_map(&pl->maps.b[s], segs[s].b, pl->bn, &err);
+        if (rc != 0) return fail(rc, "%s", err ? err : "tensor map creation failed");
+        sh.K[s] = static_cast<int>(segs[s].a.k);
+        sh.a_gmul[s] = segs[s].a.g > 1 ? 1 : 0;
+        sh.b_gmul[s] = segs[s].b.g > 1 ? 1 : 0;
+    }
+    return 0;
+}
+
+template <bool A_MN, bool B_MN, class Epi>
+int launch_plan(const GemmPlan& pl, const typename Epi::Params& ep, cudaStream_t stream) {
+    cudaError_t e;
+    if (pl.bn == 256) e = launch_gemm<256, A_MN, B_MN, Epi>(pl.maps, pl.sh, ep, pl.sms, stream);
+    else if (pl.bn == 128) e = launch_gemm<128, A_MN, B_MN, Epi>(pl.maps, pl.sh, ep, pl.sms, stream);
+    else e = launch_gemm<64, A_MN, B_MN, Epi>(pl.maps, pl.sh, ep, pl.sms, stream);
+    if (e != cudaSuccess) return cuda_fail(e, "gemm launch");
+    return 0;
+}
+
+// ACC[g] = sum_seg A_seg[g] B_seg[g]^T over G groups, epilogue Epi.  Operand majors are compile-time.
+template <bool A_MN, bool B_MN, class Epi>
+int run_gemm(int M, int N, int G, const Seg* segs, int nseg, const typename Epi::Params& ep, cudaStream_t stream) {
+    if (M <= 0 || N <= 0 || G <= 0) return 0;
+    GemmPlan pl;
+    SC_TRY(plan_gemm(&pl, M, N, G, segs, nseg, A_MN, B_MN));
+    return launch_plan<A_MN, B_MN, Epi>(pl, ep, stream);
+}
+
+}  // namespace sc

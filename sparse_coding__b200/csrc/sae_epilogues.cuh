@@ -1,0 +1,237 @@
+// Fused epilogues of the ensemble-SAE train step (reference: autoencoders/sae_ensemble.py:53-77 and
+// :134-160 for the forward, functorch's backward of it, torchopt adam for the update).
+// Notation: x [B,d] batch, W_e/W_d [N,d], b [N], c = relu(x W_e^T + b) [B,N], D = rownorm(W_d),
+// r = c D - x, R = 2 r/(B d), q = R D^T, dz = (q + lam/B [c>0]) [z>=0].
+//
+// Every tensor an epilogue writes for a later GEMM is rounded to TF32 (round to nearest) here, so
+// the tensor core's truncation of the low 13 mantissa bits never sees a non-zero bit.
+#pragma once
+#include "epi_store.cuh"
+
+namespace sc {
+
+SC_DEVICE float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// ---------------------------------------------------------------------------------------------
+// G1  z = x W_e^T + b ; c = relu(z)            rows = batch b, cols = feature n
+//   c is stored rounded to TF32; an element with z < 0 is stored as -0.0f so the backward can tell
+//   z < 0 from z == 0 (the reference's clamp passes gradient at z == 0) without keeping z.
+//   Also emits the per-warp partial sums of sum(c) for the L1 term (sae_ensemble.py:63).
+// ---------------------------------------------------------------------------------------------
+struct EpiEncode {
+    struct Params {
+        const float* bias;  // [G][N] or nullptr
+        float* c;           // [G][B][N]
+        float* l1_part;     // [G][tiles*4] or nullptr
+        long long c_gstride;
+        int signed_zero;    // 1 (training): TF32-rounded, z<0 -> -0.0f; 0 (inference API): plain fp32 relu
+    };
+    const Params& p;
+    const RowCtx c;
+    float sum;
+    SC_DEVICE EpiEncode(const Params& p_, const RowCtx& c_) : p(p_), c(c_), sum(0.f) {}
+    SC_DEVICE void chunk(int co, float (&v)[32]) {
+        const int col = c.col0 + co;
+        if (c.row >= c.M || col >= c.N) return;
+        const int ncols = c.N - col;
+        float bv[32];
+        if (p.bias) load_row32(p.bias + (long long)c.g * c.N + col, bv, ncols);
+        const float neg = p.signed_zero ? -0.0f : 0.0f;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            const float z = p.bias ? v[j] + bv[j] : v[j];
+            if (j < ncols) sum += fmaxf(z, 0.f);
+            v[j] = (z >= 0.f) ? (p.signed_zero ? rn_tf32(z) : z) : neg;
+        }
+        store_row32(p.c + c.g * p.c_gstride + (long long)c.row * c.N + col, v, ncols);
+    }
+    SC_DEVICE void finish() {
+        if (!p.l1_part) return;
+        const float s = warp_sum(sum);
+        if ((threadIdx.x & 31) == 0) {
+            const int tiles = c.tiles_m * c.tiles_n;
+            p.l1_part[((long long)c.g * tiles + c.tile_n * c.tiles_m + c.tile_m) * 4 + c.warp_q] = s;
+        }
+    }
+};
+
+// ---------------------------------------------------------------------------------------------
+// G2  x_hat = c D ; r = x_hat - x              rows = batch b, cols = activation dim j
+//   emits R = rn(2 r / (B d)) for the backward GEMMs, per-warp partials of sum(r^2)
+//   (sae_ensemble.py:62) and, when asked, x_hat itself (LearnedDict.predict, learned_dict.py:42-47).
+// ---------------------------------------------------------------------------------------------
+struct EpiDecode {
+    struct Params {
+        const float* x;     // [Gx][B][d] target (nullptr: no residual, plain decode)
+        float* R;           // [G][B][d] or nullptr
+        float* x_hat;       // [G][B][d] or nullptr
+        float* mse_part;    // [G][tiles*4] or nullptr
+        long long x_gstride, out_gstride;
+        float r_scale;      // 2/(B d)
+    };
+    const Params& p;
+    const RowCtx c;
+    float sum;
+    SC_DEVICE EpiDecode(const Params& p_, const RowCtx& c_) : p(p_), c(c_), sum(0.f) {}
+    SC_DEVICE void chunk(int co, float (&v)[32]) {
+        const int col = c.col0 + co;
+        if (c.row >= c.M || col >= c.N) return;
+        const int ncols = c.N - col;
+        const long long off = (long long)c.row * c.N + col;
+        if (p.x_hat) store_row32(p.x_hat + c.g * p.out_gstride + off, v, ncols);
+        if (!p.x) return;
+        float xv[32];
+        load_row32(p.x + c.g * p.x_gstride + off, xv, ncols);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            const float r = v[j] - xv[j];
+            if (j < ncols) sum += r * r;
+            v[j] = rn_tf32(r * p.r_scale);
+        }
+        if (p.R) store_row32(p.R + c.g * p.out_gstride + off, v, ncols);
+    }
+    SC_DEVICE void finish() {
+        if (!p.mse_part) return;
+        const float s = warp_sum(sum);
+        if ((threadIdx.x & 31) == 0) {
+            const int tiles = c.tiles_m * c.tiles_n;
+            p.mse_part[((long long)c.g * tiles + c.tile_n * c.tiles_m + c.tile_m) * 4 + c.warp_q] = s;
+        }
+    }
+};
+
+// ---------------------------------------------------------------------------------------------
+// G3  q^T = D R^T, computed TRANSPOSED         rows = feature n, cols = batch b
+//   dz = (q + lam/B [c>0]) [z>=0]  written to dz[b][n] (coalesced: the 32 lanes are 32 features);
+//   each thread owns a feature, so the two batch reductions the backward needs are plain
+//   per-thread sums, stored per column tile (deterministic, no atomics):
+//     db_part[g][tile_b][n] = sum_b dz                       (bias gradient)
+//     s_part [g][tile_b][n] = sum_b c q   (+ dz (c - b_n) when tied: encode also goes through D)
+//   s is the radial component <dD_n, D_n> that the row normalisation projects out.
+// ---------------------------------------------------------------------------------------------
+struct EpiBackCode {
+    struct Params {
+        const float* c;       // [G][B][N]
+        float* dz;            // [G][B][N]
+        const float* l1;      // [G] l1_alpha
+        const float* bias;    // [G][N] (tied only)
+        float* db_part;       // [G][tiles_b][N]
+        float* s_part;        // [G][tiles_b][N]
+        long long cb_gstride; // B*N
+        float inv_B;
+        int tied;
+        int feats;            // N (= ctx.M of this transposed GEMM)
+    };
+    const Params& p;
+    const RowCtx c;
+    float db, s, l1_over_B, bn;
+    SC_DEVICE EpiBackCode(const Params& p_, const RowCtx& c_) : p(p_), c(c_), db(0.f), s(0.f) {
+        l1_over_B = p.l1[c.g] * p.inv_B;
+        bn = (p.tied && c.row < c.M) ? p.bias[(long long)c.g * p.feats + c.row] : 0.f;
+    }
+    SC_DEVICE void chunk(int co, float (&v)[32]) {
+        if (c.row >= c.M) return;
+        const int col = c.col0 + co;  // batch index of v[0]
+        const float* cp = p.c + c.g * p.cb_gstride + (long long)col * p.feats + c.row;
+        float* dp = p.dz + c.g * p.cb_gstride + (long long)col * p.feats + c.row;
+        const int nb = c.N - col;  // c.N = B here
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            if (j < nb) {
+                const float cv = cp[(long long)j * p.feats];
+                const float q = v[j];
+                const bool live = !signbit(cv);  // z >= 0
+                const float dzv = live ? (q + (cv > 0.f ? l1_over_B : 0.f)) : 0.f;
+                dp[(long long)j * p.feats] = rn_tf32(dzv);
+                db += dzv;
+                s += cv * q;  // cv is +-0 when z <= 0
+                if (p.tied) s += dzv * (cv - bn);
+            }
+        }
+    }
+    SC_DEVICE void finish() {
+        if (c.row >= c.M) return;
+        const long long o = ((long long)c.g * c.tiles_n + c.tile_n) * p.feats + c.row;
+        p.db_part[o] = db;
+        p.s_part[o] = s;
+    }
+};
+
+// ---------------------------------------------------------------------------------------------
+// G4 / G5  weight gradient with Adam fused      rows = feature n, cols = activation dim j
+//   plain    : g = acc                                   (untied encoder: dW_e = dz^T x)
+//   projected: g = (acc - s_n D_nj) / max(||W_n||,1e-8)  (decoder / tied dictionary: gradient
+//              through D = W/||W||; rows below the clamp have D = W/1e-8 and no projection)
+//   then torchopt-0.7.1 Adam exactly as the reference executes it (ensemble.py:182-191):
+//   mu,nu updated in place, bias correction with the caller-supplied denominators (t = 1 in
+//   reference-faithful mode), p += -lr * mu_hat / (sqrt(nu_hat + eps_root) + eps).
+//   The gradient never touches HBM.
+// ---------------------------------------------------------------------------------------------
+struct AdamConst {
+    float lr, b1, b2, omb1, omb2, eps, eps_root, bc1, bc2;  // omb = 1 - beta (host double -> float), bc = 1 - beta^t
+};
+
+SC_DEVICE void adam_update(float& p, float& mu, float& nu, float g, const AdamConst& a) {
+    mu = mu * a.b1 + g * a.omb1;
+    nu = nu * a.b2 + (g * g) * a.omb2;
+    const float mh = __fdiv_rn(mu, a.bc1);
+    const float nh = __fdiv_rn(nu, a.bc2);
+    const float upd = __fdiv_rn(mh, __fsqrt_rn(nh + a.eps_root) + a.eps);
+    p = p + upd * (-a.lr);
+}
+
+struct EpiAdam {
+    struct Params {
+        float *p, *mu, *nu;     // [G][N][d]
+        const float* s_part;    // [G][tiles_b][N] (projected only)
+        const float* inv_norm;  // [G][N]  1/max(||W_n||,1e-8), negative when the clamp is active
+        float* grad_out;        // optional [G][N][d]: write the gradient instead of applying Adam (data parallel)
+        long long gstride;      // N*d
+        int tiles_b;
+        int projected;
+        AdamConst a;
+    };
+    const Params& p;
+    const RowCtx c;
+    float s, inv;
+    bool clamped;
+    SC_DEVICE EpiAdam(const Params& p_, const RowCtx& c_) : p(p_), c(c_), s(0.f), inv(1.f), clamped(false) {
+        if (p.projected && c.row < c.M) {
+            for (int t = 0; t < p.tiles_b; ++t) s += p.s_part[((long long)c.g * p.tiles_b + t) * c.M + c.row];
+            const float iv = p.inv_norm[(long long)c.g * c.M + c.row];
+            clamped = iv < 0.f;
+            inv = fabsf(iv);
+        }
+    }
+    SC_DEVICE void chunk(int co, float (&v)[32]) {
+        const int col = c.col0 + co;
+        if (c.row >= c.M || col >= c.N) return;
+        const int ncols = c.N - col;
+        const long long off = c.g * p.gstride + (long long)c.row * c.N + col;
+        float pv[32];
+        load_row32(p.p + off, pv, ncols);
+        if (p.projected) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = clamped ? v[j] * inv : (v[j] - s * (pv[j] * inv)) * inv;
+        }
+        if (p.grad_out) {
+            store_row32(p.grad_out + off, v, ncols);
+            return;
+        }
+        float mv[32], nv[32];
+        load_row32(p.mu + off, mv, ncols);
+        load_row32(p.nu + off, nv, ncols);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) adam_update(pv[j], mv[j], nv[j], v[j], p.a);
+        store_row32(p.p + off, pv, ncols);
+        store_row32(p.mu + off, mv, ncols);
+        store_row32(p.nu + off, nv, ncols);
+    }
+    SC_DEVICE void finish() {}
+};
+
+}  // namespace sc

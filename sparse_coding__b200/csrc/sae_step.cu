@@ -1,0 +1,339 @@
+// sc_sae_step: one FunctionalEnsemble.step_batch (reference autoencoders/ensemble.py:175-193) for
+// the SAE / Fista / TiedSAE signatures, as eight launches on the caller's stream:
+//   round x -> prep params -> G1 encode -> G2 decode+MSE -> G3 dL/dz -> G4/G5 dW with fused Adam
+//   -> finalize (loss scalars + bias Adam).
+// Five tcgen05 TF32 GEMMs per member carry 10 B N d flops; everything else is fused epilogue work.
+#include "../../include/sc_b200.h"
+#include "host_common.cuh"
+#include "sae_epilogues.cuh"
+
+namespace sc {
+
+thread_local char g_last_error[512] = "";
+Profiler g_prof;
+
+// ------------------------------------------------------------------------------------------------
+// out = rn_tf32(in), elementwise (the activation batch; n multiple of 4, 16-byte aligned)
+// ------------------------------------------------------------------------------------------------
+__global__ void round_copy_kernel(const float4* __restrict__ in, float4* __restrict__ out, long long n4) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+        float4 v = in[i];
+        v.x = rn_tf32(v.x); v.y = rn_tf32(v.y); v.z = rn_tf32(v.z); v.w = rn_tf32(v.w);
+        out[i] = v;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Per-step operand preparation, one warp per dictionary row (grid: ceil(N/8) x G, 256 threads).
+//   enc_r = rn_tf32(enc)                                   (when enc_r != nullptr)
+//   D_r   = rn_tf32(W / max(||W||_2, 1e-8)) per row        (sae_ensemble.py:58-59 / :135-136)
+//   inv_norm = 1 / max(||W||, 1e-8), stored NEGATIVE when the clamp is active
+// ------------------------------------------------------------------------------------------------
+__global__ void prep_params_kernel(const float* __restrict__ enc, float* __restrict__ enc_r,
+                                   const float* __restrict__ W, float* __restrict__ D_r,
+                                   float* __restrict__ inv_norm, int N, int d, int normalise) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n = blockIdx.x * 8 + warp;
+    if (n >= N) return;
+    const long long row = ((long long)blockIdx.y * N + n) * d;
+    const int d4 = d >> 2;
+    if (enc_r) {
+        const float4* src = reinterpret_cast<const float4*>(enc + row);
+        float4* dst = reinterpret_cast<float4*>(enc_r + row);
+        for (int i = lane; i < d4; i += 32) {
+            float4 v = src[i];
+            v.x = rn_tf32(v.x); v.y = rn_tf32(v.y); v.z = rn_tf32(v.z); v.w = rn_tf32(v.w);
+            dst[i] = v;
+        }
+    }
+    if (!D_r) return;
+    const float4* src = reinterpret_cast<const float4*>(W + row);
+    float inv = 1.f;
+    if (normalise) {
+        float ss = 0.f;
+        for (int i = lane; i < d4; i += 32) {
+            const float4 v = src[i];
+            ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+        }
+        ss = warp_sum(ss);
+        const float nrm = sqrtf(ss);
+        const float cl = fmaxf(nrm, 1e-8f);
+        inv = 1.f / cl;
+        if (lane == 0 && inv_norm) inv_norm[(long long)blockIdx.y * N + n] = nrm < 1e-8f ? -inv : inv;
+    }
+    float4* dst = reinterpret_cast<float4*>(D_r + row);
+    for (int i = lane; i < d4; i += 32) {
+        float4 v = src[i];
+        v.x = rn_tf32(v.x * inv); v.y = rn_tf32(v.y * inv); v.z = rn_tf32(v.z * inv); v.w = rn_tf32(v.w * inv);
+        dst[i] = v;
+    }
+}
+
+// deterministic block-wide sum (256 threads)
+SC_DEVICE float block_sum(float v, float* sh) {
+    v = warp_sum(v);
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
+    __syncthreads();
+    float t = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t += sh[i];
+    return t;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Finalize, one block per member: loss scalars (sae_ensemble.py:62-71) from the per-warp partials
+// of G1/G2, then the bias gradient db + beta b/||b|| (zero sub-gradient at b == 0) and its Adam step.
+// ------------------------------------------------------------------------------------------------
+// elementwise Adam for the data-parallel path (gradients all-reduced by the caller)
+__global__ void adam_apply_kernel(float4* __restrict__ p, float4* __restrict__ mu, float4* __restrict__ nu,
+                                  const float4* __restrict__ g, long long n4, AdamConst a) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+        float4 pv = p[i], mv = mu[i], nv = nu[i];
+        const float4 gv = g[i];
+        adam_update(pv.x, mv.x, nv.x, gv.x, a);
+        adam_update(pv.y, mv.y, nv.y, gv.y, a);
+        adam_update(pv.z, mv.z, nv.z, gv.z, a);
+        adam_update(pv.w, mv.w, nv.w, gv.w, a);
+        p[i] = pv; mu[i] = mv; nu[i] = nv;
+    }
+}
+
+__global__ void finalize_kernel(const float* __restrict__ l1_part, int n_l1, const float* __restrict__ mse_part, int n_mse,
+                                const float* __restrict__ db_part, int tiles_b, float* __restrict__ bias,
+                                float* __restrict__ bias_mu, float* __restrict__ bias_nu,
+                                const float* __restrict__ l1_alpha, const float* __restrict__ bias_decay,
+                                float* __restrict__ out_losses, int M, int B, int d, int N, int tied, AdamConst a,
+                                float* __restrict__ grad_bias) {
+    __shared__ float sh[8];
+    const int m = blockIdx.x;
+    float acc = 0.f;
+    for (int i = threadIdx.x; i < n_l1; i += blockDim.x) acc += l1_part[(long long)m * n_l1 + i];
+    const float l1_sum = block_sum(acc, sh);
+    acc = 0.f;
+    for (int i = threadIdx.x; i < n_mse; i += blockDim.x) acc += mse_part[(long long)m * n_mse + i];
+    const float sq_sum = block_sum(acc, sh);
+    acc = 0.f;
+    for (int n = threadIdx.x; n < N; n += blockDim.x) {
+        const float b = bias[(long long)m * N + n];
+        acc += b * b;
+    }
+    const float bnorm = sqrtf(block_sum(acc, sh));
+    const float lam = l1_alpha[m], beta = bias_decay[m];
+    if (threadIdx.x == 0) {
+        const float l_rec = sq_sum / ((float)B * (float)d);  // B here is the normalising (global) batch size
+        const float l_l1 = lam * (l1_sum / (float)B);
+        const float l_bd = beta * bnorm;
+        out_losses[0 * M + m] = l_rec + l_l1 + l_bd;
+        out_losses[1 * M + m] = l_rec;
+        out_losses[2 * M + m] = l_l1;
+        out_losses[3 * M + m] = l_bd;
+    }
+    const float bscale = bnorm > 0.f ? beta / bnorm : 0.f;
+    for (int n = threadIdx.x; n < N; n += blockDim.x) {
+        float g = 0.f;
+        for (int t = 0; t < tiles_b; ++t) g += db_part[((long long)m * tiles_b + t) * N + n];
+        const long long o = (long long)m * N + n;
+        float p = bias[o];
+        g += bscale * p;
+        if (grad_bias) {
+            grad_bias[o] = g;
+        } else {
+            float mu = bias_mu[o], nu = bias_nu[o];
+            adam_update(p, mu, nu, g, a);
+            bias[o] = p; bias_mu[o] = mu; bias_nu[o] = nu;
+        }
+    }
+}
+
+}  // namespace sc
+
+// ================================================================================================
+// host side
+// ================================================================================================
+namespace sc {
+
+struct StepWs {
+    float *x_r, *enc_r, *D_r, *inv_norm, *R_r, *dz, *l1_part, *mse_part, *db_part, *s_part;
+    int n_l1, n_mse, tiles_b;
+    size_t bytes;
+};
+
+static StepWs carve_step(void* base, int M, int B, int d, int N, int tied, int xpm) {
+    StepWs w;
+    Carver c(base);
+    const size_t Mz = M, Bz = B, dz_ = d, Nz = N;
+    w.x_r = c.floats((xpm ? Mz : 1) * Bz * dz_);
+    w.enc_r = tied ? nullptr : c.floats(Mz * Nz * dz_);
+    w.D_r = c.floats(Mz * Nz * dz_);
+    w.inv_norm = c.floats(Mz * Nz);
+    w.R_r = c.floats(Mz * Bz * dz_);
+    w.dz = c.floats(Mz * Bz * Nz);
+    w.n_l1 = ceil_div(B, kBlockM) * ceil_div(N, pick_bn(N)) * 4;
+    w.n_mse = ceil_div(B, kBlockM) * ceil_div(d, pick_bn(d)) * 4;
+    w.tiles_b = ceil_div(B, pick_bn(B));
+    w.l1_part = c.floats(Mz * w.n_l1);
+    w.mse_part = c.floats(Mz * w.n_mse);
+    w.db_part = c.floats(Mz * w.tiles_b * Nz);
+    w.s_part = c.floats(Mz * w.tiles_b * Nz);
+    w.bytes = c.off;
+    return w;
+}
+
+static AdamConst make_adam(const ScAdam& a) {
+    AdamConst k;
+    k.lr = a.lr; k.b1 = a.b1; k.b2 = a.b2;
+    k.omb1 = static_cast<float>(1.0 - static_cast<double>(a.b1));
+    k.omb2 = static_cast<float>(1.0 - static_cast<double>(a.b2));
+    k.eps = a.eps; k.eps_root = a.eps_root; k.bc1 = a.bc1; k.bc2 = a.bc2;
+    return k;
+}
+
+static int check_ptr(const void* p, const char* name) {
+    if (!p) return fail(-1, "%s is NULL", name);
+    if (reinterpret_cast<uintptr_t>(p) & 15) return fail(-1, "%s is not 16-byte aligned", name);
+    return 0;
+}
+
+static int sae_step_impl(const ScStepArgs& a) {
+    const int M = a.M, B = a.B, d = a.d, N = a.N;
+    if (M <= 0 || B <= 0 || d <= 0 || N <= 0) return fail(-1, "M, B, d, N must be positive (got %d %d %d %d)", M, B, d, N);
+    if ((d & 3) || (N & 3)) return fail(-1, "d and N must be multiples of 4 (got d=%d N=%d)", d, N);
+    SC_TRY(check_ptr(a.x, "x"));
+    SC_TRY(check_ptr(a.enc, "enc")); SC_TRY(check_ptr(a.enc_mu, "enc_mu")); SC_TRY(check_ptr(a.enc_nu, "enc_nu"));
+    SC_TRY(check_ptr(a.bias, "bias")); SC_TRY(check_ptr(a.bias_mu, "bias_mu")); SC_TRY(check_ptr(a.bias_nu, "bias_nu"));
+    if (!a.tied) { SC_TRY(check_ptr(a.dec, "dec")); SC_TRY(check_ptr(a.dec_mu, "dec_mu")); SC_TRY(check_ptr(a.dec_nu, "dec_nu")); }
+    SC_TRY(check_ptr(a.out_c, "out_c")); SC_TRY(check_ptr(a.workspace, "workspace"));
+    if (!a.l1_alpha || !a.bias_decay || !a.out_losses) return fail(-1, "l1_alpha / bias_decay / out_losses is NULL");
+    if (reinterpret_cast<uintptr_t>(a.workspace) & 1023) return fail(-1, "workspace must be 1024-byte aligned");
+    const StepWs w = carve_step(a.workspace, M, B, d, N, a.tied, a.x_per_member);
+    if (a.workspace_bytes < w.bytes)
+        return fail(-1, "workspace too small: %zu bytes given, %zu needed", a.workspace_bytes, w.bytes);
+    cudaStream_t st = static_cast<cudaStream_t>(a.stream);
+    const AdamConst ad = make_adam(a.adam);
+    const int xg = a.x_per_member ? M : 1;
+    const int Bn = a.B_total > 0 ? a.B_total : B;  // normalising batch size
+    const bool grad_mode = a.grad_enc != nullptr;
+    if (grad_mode) {
+        SC_TRY(check_ptr(a.grad_enc, "grad_enc")); SC_TRY(check_ptr(a.grad_bias, "grad_bias"));
+        if (!a.tied) SC_TRY(check_ptr(a.grad_dec, "grad_dec"));
+    }
+    const long long Bd = (long long)B * d, BN_ = (long long)B * N, Nd = (long long)N * d;
+
+    prof_mark(st, "begin");
+    // 1. x_r = rn(x)
+    {
+        const long long n4 = (long long)xg * Bd / 4;
+        const int grid = static_cast<int>(n4 / 256 + 1 < 2048 ? n4 / 256 + 1 : 2048);
+        round_copy_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const float4*>(a.x), reinterpret_cast<float4*>(w.x_r), n4);
+    }
+    prof_mark(st, "round_x");
+    // 2. enc_r, D_r, 1/||W||
+    {
+        dim3 grid(ceil_div(N, 8), M);
+        if (a.tied) prep_params_kernel<<<grid, 256, 0, st>>>(nullptr, nullptr, a.enc, w.D_r, w.inv_norm, N, d, 1);
+        else prep_params_kernel<<<grid, 256, 0, st>>>(a.enc, w.enc_r, a.dec, w.D_r, w.inv_norm, N, d, 1);
+        SC_CUDA(cudaGetLastError(), "prep launch");
+    }
+    prof_mark(st, "prep_params");
+    // 3. G1: c = relu(x W_e^T + b)                                  [B x N], K = d
+    {
+        Seg s{kmajor(w.x_r, B, d, xg, Bd), kmajor(a.tied ? w.D_r : w.enc_r, N, d, M, Nd)};
+        EpiEncode::Params ep{a.bias, a.out_c, w.l1_part, BN_, 1};
+        SC_TRY((run_gemm<false, false, EpiEncode>(B, N, M, &s, 1, ep, st)));
+    }
+    prof_mark(st, "G1_encode");
+    // 4. G2: r = c D - x ; R = 2 r/(B d)                             [B x d], K = N
+    {
+        Seg s{kmajor(a.out_c, B, N, M, BN_), mnmajor(w.D_r, d, N, M, Nd)};
+        EpiDecode::Params ep{a.x, w.R_r, nullptr, w.mse_part, a.x_per_member ? Bd : 0, Bd,
+                             2.0f / ((float)Bn * (float)d)};
+        SC_TRY((run_gemm<false, true, EpiDecode>(B, d, M, &s, 1, ep, st)));
+    }
+    prof_mark(st, "G2_decode_mse");
+    // 5. G3 (transposed): dz^T = f(D R^T, c)                         [N x B], K = d
+    {
+        Seg s{kmajor(w.D_r, N, d, M, Nd), kmajor(w.R_r, B, d, M, Bd)};
+        EpiBackCode::Params ep{a.out_c, w.dz, a.l1_alpha, a.bias, w.db_part, w.s_part, BN_, 1.0f / (float)Bn, a.tied, N};
+        SC_TRY((run_gemm<false, false, EpiBackCode>(N, B, M, &s, 1, ep, st)));
+    }
+    prof_mark(st, "G3_back_code");
+    // 6/7. weight gradients with fused Adam                          [N x d], K = B
+    if (!a.tied) {
+        Seg s4{mnmajor(w.dz, N, B, M, BN_), mnmajor(w.x_r, d, B, xg, Bd)};
+        EpiAdam::Params e4{a.enc, a.enc_mu, a.enc_nu, nullptr, nullptr, a.grad_enc, Nd, w.tiles_b, 0, ad};
+        SC_TRY((run_gemm<true, true, EpiAdam>(N, d, M, &s4, 1, e4, st)));
+        prof_mark(st, "G4_dWenc_adam");
+        Seg s5{mnmajor(a.out_c, N, B, M, BN_), mnmajor(w.R_r, d, B, M, Bd)};
+        EpiAdam::Params e5{a.dec, a.dec_mu, a.dec_nu, w.s_part, w.inv_norm, grad_mode ? a.grad_dec : nullptr, Nd, w.tiles_b, 1, ad};
+        SC_TRY((run_gemm<true, true, EpiAdam>(N, d, M, &s5, 1, e5, st)));
+    } else {
+        Seg s[2] = {{mnmajor(a.out_c, N, B, M, BN_), mnmajor(w.R_r, d, B, M, Bd)},
+                    {mnmajor(w.dz, N, B, M, BN_), mnmajor(w.x_r, d, B, xg, Bd)}};
+        EpiAdam::Params e{a.enc, a.enc_mu, a.enc_nu, w.s_part, w.inv_norm, a.grad_enc, Nd, w.tiles_b, 1, ad};
+        SC_TRY((run_gemm<true, true, EpiAdam>(N, d, M, s, 2, e, st)));
+    }
+    prof_mark(st, a.tied ? "G45_dW_adam" : "G5_dWdec_adam");
+    // 8. loss scalars + bias Adam
+    finalize_kernel<<<M, 256, 0, st>>>(w.l1_part, w.n_l1, w.mse_part, w.n_mse, w.db_part, w.tiles_b, a.bias, a.bias_mu,
+                                       a.bias_nu, a.l1_alpha, a.bias_decay, a.out_losses, M, Bn, d, N, a.tied, ad,
+                                       grad_mode ? a.grad_bias : nullptr);
+    SC_CUDA(cudaGetLastError(), "finalize launch");
+    prof_mark(st, "finalize");
+    return 0;
+}
+
+}  // namespace sc
+
+extern "C" {
+
+int sc_version(void) { return 100; }
+const char* sc_last_error(void) { return sc::g_last_error; }
+
+size_t sc_sae_step_workspace_bytes(int32_t M, int32_t B, int32_t d, int32_t N, int32_t tied, int32_t x_per_member) {
+    if (M <= 0 || B <= 0 || d <= 0 || N <= 0) return 0;
+    return sc::carve_step(nullptr, M, B, d, N, tied, x_per_member).bytes;
+}
+
+/* profiling hooks (used by bench.py to time individual kernels with CUDA events on the caller's stream) */
+int sc_profile_begin(void) {
+    sc::g_prof.on = true;
+    sc::g_prof.n = 0;
+    return 0;
+}
+
+/* Synchronises, writes up to `cap` (name, milliseconds since the previous mark) pairs, returns their count. */
+int sc_profile_end(const char** names, float* ms, int cap) {
+    using namespace sc;
+    g_prof.on = false;
+    int out = 0;
+    if (g_prof.n > 0) cudaEventSynchronize(g_prof.ev[g_prof.n - 1]);
+    for (int i = 1; i < g_prof.n; ++i) {
+        if (strcmp(g_prof.name[i], "begin") == 0) continue;
+        float t = 0.f;
+        cudaEventElapsedTime(&t, g_prof.ev[i - 1], g_prof.ev[i]);
+        if (out < cap) { names[out] = g_prof.name[i]; ms[out] = t; ++out; }
+    }
+    for (int i = 0; i < g_prof.n; ++i) cudaEventDestroy(g_prof.ev[i]);
+    g_prof.n = 0;
+    return out;
+}
+
+int sc_adam_apply(float* p, float* mu, float* nu, const float* g, int64_t n, const ScAdam* adam, void* stream) {
+    using namespace sc;
+    if (!p || !mu || !nu || !g || !adam || n <= 0 || (n & 3)) return fail(-1, "bad sc_adam_apply argument");
+    const long long n4 = n / 4;
+    const int grid = static_cast<int>(n4 / 256 + 1 < 148 * 16 ? n4 / 256 + 1 : 148 * 16);
+    adam_apply_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        reinterpret_cast<float4*>(p), reinterpret_cast<float4*>(mu), reinterpret_cast<float4*>(nu),
+        reinterpret_cast<const float4*>(g), n4, make_adam(*adam));
+    SC_CUDA(cudaGetLastError(), "adam_apply launch");
+    return 0;
+}
+
+int sc_sae_step(const ScStepArgs* args) {
+    if (!args) return sc::fail(-1, "args is NULL");
+    return sc::sae_step_impl(*args);
+}
+
+}  // extern "C"

@@ -147,6 +147,21 @@ int sc_row_normalise(const float* W, float* out, int32_t G, int32_t N, int32_t d
  * sum_{b,j} (x[b][j] - mean_b x[b][j])^2 for x [B,d].  workspace: at least (d + 1) floats. */
 int sc_column_variance(const float* x, float* out_sum, int32_t B, int32_t d, void* workspace, void* stream);
 
+/* Encode for callers that cannot allocate device memory.  (No counterpart in the reference: it is
+ * an addition of this library.)  Same result as sc_encode with G = 1 and only out_c requested -
+ * c = relu(x W^T + bias), x [B,d], W [N,d], bias [N] or NULL, out_c [B,N] - but the TF32-rounded
+ * operand copies live in a fixed array inside the library image instead of a caller workspace, so the
+ * call makes no cudaMalloc / cudaFree and needs no allocator: meant for a monitoring or serving loop
+ * that has given all device memory to its own pool, or cannot take cudaMalloc's device-wide
+ * synchronisation.  Limit: pad256(B*d) + pad256(N*d) <= SC_NOALLOC_SCRATCH_FLOATS, else the call
+ * returns -4 with a message and launches nothing.  Every GPU that loads the library holds the array
+ * (16 MiB) until exit.  The first call on each device looks up the array's address
+ * (cudaGetSymbolAddress) - make that call before any stream capture.  All calls share the array and
+ * simply overwrite it; calls that overlap on the GPU race on it, so serialise them. */
+#define SC_NOALLOC_SCRATCH_FLOATS (4 * 1024 * 1024)
+int sc_encode_noalloc(const float* x, const float* W, const float* bias, float* out_c, int32_t B, int32_t d, int32_t N,
+                      void* stream);
+
 /* Per-launch timing for bench.py: between sc_profile_begin() and sc_profile_end() every kernel the
  * library launches is bracketed by CUDA events on the caller's stream.  sc_profile_end synchronises and
  * returns up to `cap` (kernel name, milliseconds) pairs in launch order. */

@@ -23,7 +23,7 @@ EXPORTS = [
     "sc_version", "sc_last_error", "sc_sae_step_workspace_bytes", "sc_sae_step",
     "sc_encode_workspace_bytes", "sc_encode", "sc_decode_workspace_bytes", "sc_decode",
     "sc_fista_workspace_bytes", "sc_fista", "sc_gemm_tf32", "sc_adam_apply", "sc_row_normalise", "sc_column_variance",
-    "sc_profile_begin", "sc_profile_end",
+    "sc_profile_begin", "sc_profile_end", "sc_encode_noalloc",
 ]
 
 

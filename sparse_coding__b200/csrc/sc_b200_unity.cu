@@ -3,3 +3,4 @@
 #include "sae_step.cu"
 #include "infer.cu"
 #include "fista.cu"
+#include "noalloc.cu"

@@ -34,11 +34,14 @@ def load():
         return _loaded["ns"]
     if not available():
         raise RuntimeError(f"reference not found at {REFERENCE_ROOT}")
-    # our own package also has a sub-package called `autoencoders`, but it lives
-    # under sparse_coding__b200.*, so the top-level name is free for the reference.
+    # The engine package registers itself under the reference's import names (drop-in aliases).
+    # Import the real reference under those names, keep the module objects, then put back whatever
+    # was there so the rest of the process is unaffected.
+    saved = {k: sys.modules.pop(k) for k in list(sys.modules)
+             if k == "autoencoders" or k.startswith("autoencoders.") or k in ("torchopt", "optree", "torchtyping")}
+    saved_path = list(sys.path)
     for p in (_SHIMS, REFERENCE_ROOT):
-        if p not in sys.path:
-            sys.path.insert(0, p)
+        sys.path.insert(0, p)
 
     class NS:
         pass
@@ -111,5 +114,29 @@ def load():
     for k, v in sm.items():
         setattr(ns, k, v)
 
+    ns._modules = {k: v for k, v in sys.modules.items()
+                   if k == "autoencoders" or k.startswith("autoencoders.") or k in ("torchopt", "optree", "torchtyping")}
+    for k in ns._modules:
+        sys.modules.pop(k, None)
+    sys.modules.update(saved)
+    sys.path[:] = saved_path
     _loaded["ns"] = ns
     return ns
+
+
+class reference_modules:
+    """Context manager: the reference's modules visible under their own import names (needed to
+    unpickle the reference's own output_basic_test/*.pt files)."""
+
+    def __enter__(self):
+        ns = load()
+        self.saved = {k: sys.modules.get(k) for k in ns._modules}
+        sys.modules.update(ns._modules)
+        return ns
+
+    def __exit__(self, *exc):
+        for k, v in self.saved.items():
+            if v is None:
+                sys.modules.pop(k, None)
+            else:
+                sys.modules[k] = v

@@ -1,0 +1,117 @@
+"""The CUDA engine against the fixtures frozen from the REAL reference code (tests/golden/,
+oracle/make_golden.py): per-step losses of FunctionalEnsemble.step_batch, LearnedDict inference,
+the metrics, and FISTA.  Tolerances: BASELINE.json's (loss/FVU 1e-3 rel, L0 0.5 %, FISTA 1e-4 abs)."""
+import os
+
+import pytest
+import torch
+
+from conftest import rel_err
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def load(name):
+    return torch.load(os.path.join(GOLD, name), weights_only=False)
+
+
+@pytest.mark.parametrize("name", ["ensemble_untied.pt", "ensemble_tied.pt"])
+def test_step_batch_against_reference_fixture(name):
+    import sparse_coding__b200 as sc
+    g = load(name)
+    tied = g["kind"] == "tied"
+    M = g["init_params"]["encoder"].shape[0]
+    models = []
+    for m in range(M):
+        models.append(({k: v[m].clone() for k, v in g["init_params"].items()},
+                       {k: v[m].clone() for k, v in g["buffers"].items()}))
+    sig = sc.FunctionalTiedSAE if tied else sc.FunctionalSAE
+    ens = sc.FunctionalEnsemble(models, sig, sc.torchopt_compat.adam, {"lr": g["lr"]}, device="cuda")
+    B = g["batch"]
+    for s, want in enumerate(g["losses"]):
+        got, aux = ens.step_batch(g["data"][s * B:(s + 1) * B].cuda())
+        assert set(got.keys()) == set(want.keys())
+        for k in want:
+            assert torch.allclose(got[k].cpu(), want[k], rtol=1e-3, atol=1e-7), (s, k, got[k].cpu(), want[k])
+    c = aux["c"].cpu()
+    assert rel_err(c, g["last_c"]) < 3e-3
+    l0_got, l0_want = (c != 0).float().sum(-1).mean(-1), (g["last_c"] != 0).float().sum(-1).mean(-1)
+    assert float(((l0_got - l0_want).abs() / l0_want.clamp_min(1)).max()) < 5e-3
+    for k in g["final_params"]:
+        assert float((ens.params[k].cpu() - g["final_params"][k]).abs().mean()) < 2e-4, k  # lr = 1e-3 per step
+        assert rel_err(ens.optim_states[0].mu[k], g["final_mu"][k]) < 2e-2
+    assert all(int(v.sum()) == 0 for v in ens.optim_states[0].count.values())
+
+
+def test_inference_and_metrics_against_reference_fixture():
+    import sparse_coding__b200 as sc
+    from sparse_coding__b200 import standard_metrics as sm
+    g = load("inference.pt")
+    We, Wd, b, x = (g[k].cuda() for k in ("We", "Wd", "b", "x"))
+    tr, rot, scale = (t.cuda() for t in g["tied_centering"])
+    models = {"untied": sc.UntiedSAE(We, Wd, b),
+              "tied": sc.TiedSAE(We.clone(), b.clone(), centering=(tr, rot, scale), norm_encoder=True)}
+    for name, m in models.items():
+        w = g[name]
+        assert rel_err(m.encode(m.center(x))[:256], w["c_head"]) < 2e-3
+        assert rel_err(m.predict(x)[:256], w["predict_head"]) < 3e-3
+        assert rel_err(m.get_learned_dict(), w["learned_dict"]) < 1e-6
+        fvu = float(sm.fraction_variance_unexplained(m, x))
+        assert abs(fvu - float(w["fvu"])) <= 1e-3 * float(w["fvu"])
+        mnz = sm.mean_nonzero_activations(m, x).cpu()
+        assert abs(float(mnz.sum()) - float(w["mean_nonzero"].sum())) <= 5e-3 * float(w["mean_nonzero"].sum())
+        assert abs(sm.batched_calc_feature_n_ever_active(m, m.center(x), threshold=10) - w["n_ever_active_10"]) <= 1
+        assert abs(sm.batched_calc_feature_n_ever_active(m, m.center(x)[:1000], threshold=1) - w["n_ever_active_1"]) <= 1
+        got = sm.calc_moments_streaming(m, m.center(x), batch_size=1000)
+        for nm, a, r, tol in zip(["times_active", "mean", "var", "skew", "kurtosis", "m4"], got, w["moments"],
+                                 [0.5, 2e-3, 4e-3, 2e-2, 5e-2, 6e-3]):
+            assert float((a.cpu() - r).abs().max()) <= tol * max(1.0, float(r.abs().max())), (name, nm)
+
+
+def test_fista_against_reference_fixture():
+    import sparse_coding__b200 as sc
+    g = load("fista.pt")
+    x, D, a0 = g["x"].cuda(), g["D"].cuda(), g["a0"].cuda()
+    for iters in (1, 10, 60):
+        a, res = sc.FunctionalFista.fista(x, D, torch.tensor(g["l1"]), a0, iters, "cuda")
+        assert float((a.cpu() - g[f"a_{iters}"]).abs().max()) < 1e-4, iters
+        assert float((res.cpu() - g[f"res_{iters}"]).abs().max()) < 1e-4, iters
+    du = g["du"]
+    buffers = {"l1_alpha": torch.tensor(g["l1"]).cuda(), "hessian_diag": torch.zeros(du["D"].shape[0]).cuda()}
+    new_dict, res = sc.FunctionalFista.dictionary_update({"encoder": du["D"].cuda()}, buffers, x, du["c"].cuda(), du["D"].cuda())
+    assert rel_err(new_dict, du["new_dict"]) < 1e-3
+    assert rel_err(buffers["hessian_diag"], du["hessian_diag"]) < 1e-3
+
+
+def test_train_loop_with_fista_dictionary_update_runs_only_when_square():
+    """big_sweep.py:161-230 as this fork has it: after each Adam step a FISTA dictionary update per
+    member, valid only for N == d and M > 1 (reference raises otherwise)."""
+    import sparse_coding__b200 as sc
+
+    class Cfg:
+        use_wandb = False
+
+    class Counter:
+        value = -1
+
+    d = N = 32
+    torch.manual_seed(0)
+    models = [sc.FunctionalFista.init(d, N, l1, device="cuda") for l1 in (1e-3, 1e-2)]
+    ens = sc.FunctionalEnsemble(models, sc.FunctionalFista, sc.torchopt_compat.adam, {"lr": 1e-3}, device="cuda")
+    data = torch.randn(64, d)
+    sampler = [list(range(0, 16)), list(range(16, 32))]
+    before = ens.params["decoder"].clone()
+    pc = Counter()
+    sc.ensemble_train_loop(ens, Cfg(), {"device": "cuda", "dict_size": N}, "e", sampler, data, pc, torch.float32)
+    assert pc.value == 1
+    after = ens.params["decoder"]
+    assert after.shape == before.shape and torch.isfinite(after).all() and not torch.equal(after, before)
+    # column-normalised, as fista.py:137 does (dim 0)
+    assert torch.allclose(after.norm(dim=1), torch.ones(2, d, device="cuda"), atol=1e-4)
+    models = [sc.FunctionalFista.init(d, 2 * d, l1, device="cuda") for l1 in (1e-3, 1e-2)]
+    ens2 = sc.FunctionalEnsemble(models, sc.FunctionalFista, sc.torchopt_compat.adam, {"lr": 1e-3}, device="cuda")
+    with pytest.raises(RuntimeError):
+        sc.ensemble_train_loop(ens2, Cfg(), {"device": "cuda", "dict_size": 2 * d}, "e", sampler, data, Counter(), torch.float32)
+    sc.ensemble_train_loop(ens2, Cfg(), {"device": "cuda", "dict_size": 2 * d}, "e", sampler, data, Counter(), torch.float32,
+                           fista_dictionary_update=False)

@@ -3,7 +3,8 @@
 //   ACC[g][m][n] = sum_seg sum_k A_seg[g][m][k] * B_seg[g][n][k]        (TF32 in, fp32 accumulate)
 //
 // * one CTA per SM, 256 threads: warp 0 = TMA producer, warp 1 = MMA issuer, warp 2 = TMEM
-//   allocator, warps 4..7 = epilogue (thread t of the four owns accumulator row t = TMEM lane t)
+//   allocator, warps 4..11 = epilogue: two warps per 32-row quarter of the tile (TMEM lanes are
+//   only reachable from warps with the matching warp%4), the pair splitting the 32-column chunks
 // * operand tiles [128 x 32] / [BN x 32] fp32 arrive by TMA into 128-byte-swizzled shared memory,
 //   a ring of kStages stages guarded by full/empty mbarriers
 // * one elected thread issues tcgen05.mma.kind::tf32 128 x BN x 8; accumulators live in TMEM,
@@ -25,7 +26,8 @@ constexpr int kBlockM = 128;
 constexpr int kBlockK = 32;  // fp32 elements: 128 bytes, one swizzle span
 constexpr int kUmmaK = 8;    // tf32: 32 bytes of K per instruction
 constexpr int kMaxSeg = 3;
-constexpr int kGemmThreads = 256;
+constexpr int kGemmThreads = 384;
+constexpr int kEpiHalves = 2;  // epilogue warps per row quarter
 constexpr int kATileBytes = kBlockM * kBlockK * 4;
 
 struct alignas(64) GemmMaps {
@@ -62,6 +64,8 @@ struct RowCtx {
     int tile_m, tile_n;
     int tiles_m, tiles_n;
     int warp_q;  // which 32-row quarter of the tile this warp owns (0..3)
+    int half;    // which of the kEpiHalves warps of that quarter (takes chunks half, half+2, ...)
+    int part;    // warp_q + 4*half: slot for per-warp partial results (0..4*kEpiHalves-1)
 };
 
 template <int BN, bool A_MN, bool B_MN, class Epi>
@@ -94,7 +98,7 @@ gemm_tf32_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(&tmem_full[i], 1);
-            mbar_init(&tmem_empty[i], 128);
+            mbar_init(&tmem_empty[i], 128 * kEpiHalves);
         }
         fence_mbar_init();
     }
@@ -192,6 +196,7 @@ gemm_tf32_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
     } else if (warp >= 4) {
         // ------------------------------------------------------------------ epilogue
         const int q = warp & 3;
+        const int half = (warp - 4) >> 2;
         int it = 0;
         for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
             const int g = tile / tiles_per_group;
@@ -202,13 +207,13 @@ gemm_tf32_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
             const uint32_t aph = (it >> 1) & 1;
             RowCtx ctx;
             ctx.g = g; ctx.row = tm * kBlockM + q * 32 + lane; ctx.col0 = tn * BN;
-            ctx.M = shape.M; ctx.N = shape.N; ctx.tile_m = tm; ctx.tile_n = tn; ctx.tiles_m = shape.tiles_m; ctx.tiles_n = shape.tiles_n; ctx.warp_q = q;
+            ctx.M = shape.M; ctx.N = shape.N; ctx.tile_m = tm; ctx.tile_n = tn; ctx.tiles_m = shape.tiles_m; ctx.tiles_n = shape.tiles_n; ctx.warp_q = q; ctx.half = half; ctx.part = q + 4 * half;
             Epi epi(ep, ctx);
             mbar_wait(&tmem_full[as], aph);
             tc_fence_after();
             const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
 #pragma unroll 1
-            for (int c = 0; c < BN / 32; ++c) {
+            for (int c = half; c < BN / 32; c += kEpiHalves) {
                 float v[32];
                 tmem_ld32(taddr + c * 32, v);
                 tmem_ld_wait();

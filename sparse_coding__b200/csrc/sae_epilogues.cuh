@@ -54,7 +54,7 @@ struct EpiEncode {
         const float s = warp_sum(sum);
         if ((threadIdx.x & 31) == 0) {
             const int tiles = c.tiles_m * c.tiles_n;
-            p.l1_part[((long long)c.g * tiles + c.tile_n * c.tiles_m + c.tile_m) * 4 + c.warp_q] = s;
+            p.l1_part[((long long)c.g * tiles + c.tile_n * c.tiles_m + c.tile_m) * (4 * kEpiHalves) + c.part] = s;
         }
     }
 };
@@ -99,7 +99,7 @@ struct EpiDecode {
         const float s = warp_sum(sum);
         if ((threadIdx.x & 31) == 0) {
             const int tiles = c.tiles_m * c.tiles_n;
-            p.mse_part[((long long)c.g * tiles + c.tile_n * c.tiles_m + c.tile_m) * 4 + c.warp_q] = s;
+            p.mse_part[((long long)c.g * tiles + c.tile_n * c.tiles_m + c.tile_m) * (4 * kEpiHalves) + c.part] = s;
         }
     }
 };
@@ -109,7 +109,7 @@ struct EpiDecode {
 //   dz = (q + lam/B [c>0]) [z>=0]  written to dz[b][n] (coalesced: the 32 lanes are 32 features);
 //   each thread owns a feature, so the two batch reductions the backward needs are plain
 //   per-thread sums, stored per column tile (deterministic, no atomics):
-//     db_part[g][tile_b][n] = sum_b dz                       (bias gradient)
+//     db_part[g][tile_b*2+half][n] = sum_b dz                       (bias gradient)
 //     s_part [g][tile_b][n] = sum_b c q   (+ dz (c - b_n) when tied: encode also goes through D)
 //   s is the radial component <dD_n, D_n> that the row normalisation projects out.
 // ---------------------------------------------------------------------------------------------
@@ -139,10 +139,13 @@ struct EpiBackCode {
         const float* cp = p.c + c.g * p.cb_gstride + (long long)col * p.feats + c.row;
         float* dp = p.dz + c.g * p.cb_gstride + (long long)col * p.feats + c.row;
         const int nb = c.N - col;  // c.N = B here
+        float cvs[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) cvs[j] = (j < nb) ? __ldg(cp + (long long)j * p.feats) : 0.f;  // 32 loads in flight
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
             if (j < nb) {
-                const float cv = cp[(long long)j * p.feats];
+                const float cv = cvs[j];
                 const float q = v[j];
                 const bool live = !signbit(cv);  // z >= 0
                 const float dzv = live ? (q + (cv > 0.f ? l1_over_B : 0.f)) : 0.f;
@@ -155,7 +158,7 @@ struct EpiBackCode {
     }
     SC_DEVICE void finish() {
         if (c.row >= c.M) return;
-        const long long o = ((long long)c.g * c.tiles_n + c.tile_n) * p.feats + c.row;
+        const long long o = ((long long)c.g * c.tiles_n * kEpiHalves + c.tile_n * kEpiHalves + c.half) * p.feats + c.row;
         p.db_part[o] = db;
         p.s_part[o] = s;
     }

@@ -43,7 +43,8 @@ struct EpiFistaRes {
     const Params& p;
     const RowCtx c;
     SC_DEVICE EpiFistaRes(const Params& p_, const RowCtx& c_) : p(p_), c(c_) {}
-    SC_DEVICE void chunk(int co, float (&v)[32]) {
+    SC_DEVICE void prefetch(int) {}
+    SC_DEVICE void chunk(int co, float (&v)[32], int /*next_co*/) {
         const int col = c.col0 + co;
         if (c.row >= c.M || col >= c.N) return;
         const int ncols = c.N - col;
@@ -82,7 +83,8 @@ struct EpiFistaStep {
         eta = *p.eta;
         thr = eta * p.l1;
     }
-    SC_DEVICE void chunk(int co, float (&v)[32]) {
+    SC_DEVICE void prefetch(int) {}
+    SC_DEVICE void chunk(int co, float (&v)[32], int /*next_co*/) {
         const int col = c.col0 + co;
         if (c.row >= c.M || col >= c.N) return;
         const int ncols = c.N - col;

@@ -13,7 +13,8 @@
 //   SAE gradient (c^T R + dz^T x) and for the 3xTF32 split products of FISTA
 // * either operand may be K-major (k contiguous) or MN-major (m/n contiguous); MN-major fp32 tiles
 //   use the 128-byte swizzle with 32-byte atoms, the only MN-major layout tcgen05 takes for 32-bit
-// * the epilogue is a functor that sees its accumulator row 32 columns at a time
+// * the epilogue is a functor that sees its accumulator row 32 columns at a time:
+//     Epi(params, ctx); prefetch(col); chunk(col, v[32], next_col or -1); finish()
 //
 // Group (member) index g lets one launch cover every SAE of the ensemble; an operand that all
 // members share (the activation batch) has gmul = 0 and is fetched from the same address by all.
@@ -40,6 +41,7 @@ struct GemmShape {
     int nseg;
     int K[kMaxSeg];
     int a_gmul[kMaxSeg], b_gmul[kMaxSeg];
+    int a_one_box[kMaxSeg], b_one_box[kMaxSeg];  // MN-major operand described 4-D: one TMA box per tile
     int tiles_m, tiles_n;
 };
 
@@ -136,6 +138,8 @@ gemm_tf32_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
                         const int k0 = kb * kBlockK;
                         if (!A_MN) {
                             tma_load_3d(&maps.a[seg], &full_bar[stage], sa, k0, m0, ga);
+                        } else if (shape.a_one_box[seg]) {
+                            tma_load_4d(&maps.a[seg], &full_bar[stage], sa, 0, k0, m0 >> 5, ga);
                         } else {
 #pragma unroll
                             for (int i = 0; i < kBlockM / 32; ++i)
@@ -143,6 +147,8 @@ gemm_tf32_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
                         }
                         if (!B_MN) {
                             tma_load_3d(&maps.b[seg], &full_bar[stage], sb, k0, n0, gb);
+                        } else if (shape.b_one_box[seg]) {
+                            tma_load_4d(&maps.b[seg], &full_bar[stage], sb, 0, k0, n0 >> 5, gb);
                         } else {
 #pragma unroll
                             for (int i = 0; i < BN / 32; ++i)
@@ -209,15 +215,22 @@ gemm_tf32_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
             ctx.g = g; ctx.row = tm * kBlockM + q * 32 + lane; ctx.col0 = tn * BN;
             ctx.M = shape.M; ctx.N = shape.N; ctx.tile_m = tm; ctx.tile_n = tn; ctx.tiles_m = shape.tiles_m; ctx.tiles_n = shape.tiles_n; ctx.warp_q = q; ctx.half = half; ctx.part = q + 4 * half;
             Epi epi(ep, ctx);
+            constexpr int kChunks = (BN / 32 + kEpiHalves - 1) / kEpiHalves;
+            // global loads the functor needs for its first chunk do not depend on the accumulator: issue them
+            // before waiting for the MMAs, and the next chunk's while the current one is processed
+            if (half < BN / 32) epi.prefetch(half * 32);
             mbar_wait(&tmem_full[as], aph);
             tc_fence_after();
             const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
-#pragma unroll 1
-            for (int c = half; c < BN / 32; c += kEpiHalves) {
-                float v[32];
-                tmem_ld32(taddr + c * 32, v);
-                tmem_ld_wait();
-                epi.chunk(c * 32, v);
+#pragma unroll 1  // keep the (large) functor body in the instruction cache
+            for (int i = 0; i < kChunks; ++i) {
+                const int c = half + i * kEpiHalves;
+                if (c < BN / 32) {
+                    float v[32];
+                    tmem_ld32(taddr + c * 32, v);
+                    tmem_ld_wait();
+                    epi.chunk(c * 32, v, (c + kEpiHalves < BN / 32) ? (c + kEpiHalves) * 32 : -1);
+                }
             }
             tc_fence_before();
             mbar_arrive(&tmem_empty[as]);

@@ -121,8 +121,11 @@ inline int plan_gemm(GemmPlan* pl, int M, int N, int G, const Seg* segs, int nse
         if (segs[s].a.mn_major != a_mn || segs[s].b.mn_major != b_mn) return fail(-3, "operand major mismatch");
         if (segs[s].a.k != segs[s].b.k || segs[s].a.k <= 0) return fail(-3, "segment K mismatch");
         const char* err = nullptr;
-        int rc = make_operand_map(&pl->maps.a[s], segs[s].a, kBlockM, &err);
-        if (rc == 0) rc = make_operand_map(&pl->maps.b[s], segs[s].b, pl->bn, &err);
+        bool a1 = false, b1 = false;
+        int rc = make_operand_map(&pl->maps.a[s], segs[s].a, kBlockM, &a1, &err);
+        if (rc == 0) rc = make_operand_map(&pl->maps.b[s], segs[s].b, pl->bn, &b1, &err);
+        sh.a_one_box[s] = a1;
+        sh.b_one_box[s] = b1;
         if (rc != 0) return fail(rc, "%s", err ? err : "tensor map creation failed");
         sh.K[s] = static_cast<int>(segs[s].a.k);
         sh.a_gmul[s] = segs[s].a.g > 1 ? 1 : 0;

@@ -41,7 +41,8 @@ struct EpiEncodeT {
     SC_DEVICE EpiEncodeT(const Params& p_, const RowCtx& c_) : p(p_), c(c_), cnt(0.f), m1(0.f), m2(0.f), m3(0.f), m4(0.f) {
         bn = (p.bias && c.row < c.M) ? p.bias[(long long)c.g * p.feats + c.row] : 0.f;
     }
-    SC_DEVICE void chunk(int co, float (&v)[32]) {
+    SC_DEVICE void prefetch(int) {}
+    SC_DEVICE void chunk(int co, float (&v)[32], int /*next_co*/) {
         if (c.row >= c.M) return;
         const int col = c.col0 + co;
         const int nb = c.N - col;

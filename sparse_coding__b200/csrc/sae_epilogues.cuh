@@ -34,7 +34,8 @@ struct EpiEncode {
     const RowCtx c;
     float sum;
     SC_DEVICE EpiEncode(const Params& p_, const RowCtx& c_) : p(p_), c(c_), sum(0.f) {}
-    SC_DEVICE void chunk(int co, float (&v)[32]) {
+    SC_DEVICE void prefetch(int) {}
+    SC_DEVICE void chunk(int co, float (&v)[32], int /*next_co*/) {
         const int col = c.col0 + co;
         if (c.row >= c.M || col >= c.N) return;
         const int ncols = c.N - col;
@@ -77,7 +78,8 @@ struct EpiDecode {
     const RowCtx c;
     float sum;
     SC_DEVICE EpiDecode(const Params& p_, const RowCtx& c_) : p(p_), c(c_), sum(0.f) {}
-    SC_DEVICE void chunk(int co, float (&v)[32]) {
+    SC_DEVICE void prefetch(int) {}
+    SC_DEVICE void chunk(int co, float (&v)[32], int /*next_co*/) {
         const int col = c.col0 + co;
         if (c.row >= c.M || col >= c.N) return;
         const int ncols = c.N - col;
@@ -129,19 +131,29 @@ struct EpiBackCode {
     const Params& p;
     const RowCtx c;
     float db, s, l1_over_B, bn;
+    float nxt[32];  // c values of the chunk after the current one, loads in flight
     SC_DEVICE EpiBackCode(const Params& p_, const RowCtx& c_) : p(p_), c(c_), db(0.f), s(0.f) {
         l1_over_B = p.l1[c.g] * p.inv_B;
         bn = (p.tied && c.row < c.M) ? p.bias[(long long)c.g * p.feats + c.row] : 0.f;
     }
-    SC_DEVICE void chunk(int co, float (&v)[32]) {
+    // 32 coalesced loads (lanes = 32 consecutive features of one batch row each) left in flight
+    SC_DEVICE void prefetch(int co) {
+        if (c.row >= c.M) return;
+        const int col = c.col0 + co;
+        const float* cp = p.c + c.g * p.cb_gstride + (long long)col * p.feats + c.row;
+        const int nb = c.N - col;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) nxt[j] = (j < nb) ? __ldg(cp + (long long)j * p.feats) : 0.f;
+    }
+    SC_DEVICE void chunk(int co, float (&v)[32], int next_co) {
         if (c.row >= c.M) return;
         const int col = c.col0 + co;  // batch index of v[0]
-        const float* cp = p.c + c.g * p.cb_gstride + (long long)col * p.feats + c.row;
         float* dp = p.dz + c.g * p.cb_gstride + (long long)col * p.feats + c.row;
         const int nb = c.N - col;  // c.N = B here
         float cvs[32];
 #pragma unroll
-        for (int j = 0; j < 32; ++j) cvs[j] = (j < nb) ? __ldg(cp + (long long)j * p.feats) : 0.f;  // 32 loads in flight
+        for (int j = 0; j < 32; ++j) cvs[j] = nxt[j];
+        if (next_co >= 0) prefetch(next_co);
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
             if (j < nb) {
@@ -175,16 +187,30 @@ struct EpiBackCode {
 //   The gradient never touches HBM.
 // ---------------------------------------------------------------------------------------------
 struct AdamConst {
-    float lr, b1, b2, omb1, omb2, eps, eps_root, bc1, bc2;  // omb = 1 - beta (host double -> float), bc = 1 - beta^t
+    float lr, b1, b2, omb1, omb2, eps, eps_root, rbc1, rbc2;  // omb = 1 - beta, rbc = 1 / (1 - beta^t)
 };
 
+SC_DEVICE float sqrt_approx(float x) {
+    float r;
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+SC_DEVICE float rcp_approx(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
+// ~10 instructions per element (MUFU sqrt / rcp, 1-2 ulp): the update is lr * O(1), so the
+// approximation is far below fp32 resolution of the parameter and keeps the epilogue small enough
+// for the instruction cache.
 SC_DEVICE void adam_update(float& p, float& mu, float& nu, float g, const AdamConst& a) {
-    mu = mu * a.b1 + g * a.omb1;
-    nu = nu * a.b2 + (g * g) * a.omb2;
-    const float mh = __fdiv_rn(mu, a.bc1);
-    const float nh = __fdiv_rn(nu, a.bc2);
-    const float upd = __fdiv_rn(mh, __fsqrt_rn(nh + a.eps_root) + a.eps);
-    p = p + upd * (-a.lr);
+    mu = fmaf(mu, a.b1, g * a.omb1);
+    nu = fmaf(nu, a.b2, (g * g) * a.omb2);
+    const float mh = mu * a.rbc1;
+    const float nh = nu * a.rbc2;
+    const float upd = mh * rcp_approx(sqrt_approx(nh + a.eps_root) + a.eps);
+    p = fmaf(upd, -a.lr, p);
 }
 
 struct EpiAdam {
@@ -210,7 +236,8 @@ struct EpiAdam {
             inv = fabsf(iv);
         }
     }
-    SC_DEVICE void chunk(int co, float (&v)[32]) {
+    SC_DEVICE void prefetch(int) {}
+    SC_DEVICE void chunk(int co, float (&v)[32], int /*next_co*/) {
         const int col = c.col0 + co;
         if (c.row >= c.M || col >= c.N) return;
         const int ncols = c.N - col;

@@ -185,7 +185,7 @@ static AdamConst make_adam(const ScAdam& a) {
     k.lr = a.lr; k.b1 = a.b1; k.b2 = a.b2;
     k.omb1 = static_cast<float>(1.0 - static_cast<double>(a.b1));
     k.omb2 = static_cast<float>(1.0 - static_cast<double>(a.b2));
-    k.eps = a.eps; k.eps_root = a.eps_root; k.bc1 = a.bc1; k.bc2 = a.bc2;
+    k.eps = a.eps; k.eps_root = a.eps_root; k.rbc1 = 1.0f / a.bc1; k.rbc2 = 1.0f / a.bc2;
     return k;
 }
 

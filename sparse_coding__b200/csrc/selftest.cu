@@ -74,11 +74,12 @@ int main(int argc, char** argv) {
         CK(cudaMemcpy(dB[s], hB[s].data(), hB[s].size() * 4, cudaMemcpyHostToDevice));
         Operand oa{dA[s], M, K, G, ldA, (int64_t)szA, a_mn != 0};
         Operand ob{dB[s], N, K, G, ldB, (int64_t)szB, b_mn != 0};
-        if (make_operand_map(&maps.a[s], oa, 128, &err) || make_operand_map(&maps.b[s], ob, BN, &err)) {
+        bool a1 = false, b1 = false;
+        if (make_operand_map(&maps.a[s], oa, 128, &a1, &err) || make_operand_map(&maps.b[s], ob, BN, &b1, &err)) {
             printf("tensor map error: %s\n", err ? err : "?");
             return 2;
         }
-        sh.K[s] = K; sh.a_gmul[s] = G > 1; sh.b_gmul[s] = G > 1;
+        sh.K[s] = K; sh.a_gmul[s] = G > 1; sh.b_gmul[s] = G > 1; sh.a_one_box[s] = a1; sh.b_one_box[s] = b1;
     }
     const int ldC = (N + 3) & ~3;
     CK(cudaMalloc(&dC, (size_t)G * M * ldC * 4));

@@ -36,7 +36,7 @@ static int encode(CUtensorMap* out, const void* base, int rank, const cuuint64_t
         if (err) *err = "tensor base address is not 16-byte aligned";
         return -11;
     }
-    for (int i = 0; i < rank - 1; ++i) {
+    for (int i = 0; i < (rank - 1 < 2 ? rank - 1 : 2); ++i) {
         if (strides_bytes[i] % 16 != 0 || strides_bytes[i] == 0) {
             snprintf(g_msg, sizeof g_msg, "tensor stride %d = %llu bytes is not a positive multiple of 16", i,
                      (unsigned long long)strides_bytes[i]);
@@ -45,6 +45,10 @@ static int encode(CUtensorMap* out, const void* base, int rank, const cuuint64_t
         }
     }
     cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+    if (rank == 4 && (strides_bytes[2] % 16 != 0 || strides_bytes[2] == 0)) {
+        if (err) *err = "tensor group stride is not a positive multiple of 16 bytes";
+        return -12;
+    }
     CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, rank, const_cast<void*>(base), dims, strides_bytes, box, estr,
                     CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -59,7 +63,8 @@ static int encode(CUtensorMap* out, const void* base, int rank, const cuuint64_t
     return 0;
 }
 
-int make_operand_map(CUtensorMap* out, const Operand& op, int box_mn, const char** err) {
+int make_operand_map(CUtensorMap* out, const Operand& op, int box_mn, bool* one_box, const char** err) {
+    if (one_box) *one_box = false;
     const int64_t g = op.g < 1 ? 1 : op.g;
     // a never-used outer stride still has to be a legal one
     const int64_t gs = (g > 1 && op.gstride > 0) ? op.gstride : op.ld * (op.mn_major ? op.k : op.mn);
@@ -68,6 +73,13 @@ int make_operand_map(CUtensorMap* out, const Operand& op, int box_mn, const char
         cuuint64_t dims[3] = {(cuuint64_t)op.k, (cuuint64_t)op.mn, (cuuint64_t)g};
         cuuint32_t box[3] = {32, (cuuint32_t)box_mn, 1};
         return encode(out, op.base, 3, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B, err);
+    }
+    if (one_box && op.mn % 32 == 0) {
+        cuuint64_t dims4[4] = {32, (cuuint64_t)op.k, (cuuint64_t)(op.mn / 32), (cuuint64_t)g};
+        cuuint64_t strides4[3] = {(cuuint64_t)op.ld * 4, 128, (cuuint64_t)gs * 4};
+        cuuint32_t box4[4] = {32, 32, (cuuint32_t)(box_mn / 32), 1};
+        *one_box = true;
+        return encode(out, op.base, 4, dims4, strides4, box4, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, err);
     }
     cuuint64_t dims[3] = {(cuuint64_t)op.mn, (cuuint64_t)op.k, (cuuint64_t)g};
     cuuint32_t box[3] = {32, 32, 1};

@@ -22,10 +22,12 @@ struct Operand {
 
 // box_mn: rows of the operand tile (128 for the A side, BLOCK_N for the B side); BLOCK_K = 32.
 // K-major : one box {32 k, box_mn rows}, 128-byte swizzle.
-// MN-major: boxes {32 mn, 32 k}, 128-byte swizzle with 32-byte atoms (the only layout tcgen05
-//           accepts for MN-major 32-bit operands); the kernel issues box_mn/32 loads per stage.
+// MN-major: 128-byte swizzle with 32-byte atoms (the only layout tcgen05 accepts for MN-major 32-bit
+//           operands).  When mn is a multiple of 32 the tensor is described in 4-D as
+//           {32, k, mn/32, g} and ONE box {32, 32 k, box_mn/32} fills the whole tile (*one_box = true);
+//           otherwise boxes {32 mn, 32 k} and the kernel issues box_mn/32 loads per stage.
 // Returns 0 on success, else a negative sc error code with the message in *err.
-int make_operand_map(CUtensorMap* out, const Operand& op, int box_mn, const char** err);
+int make_operand_map(CUtensorMap* out, const Operand& op, int box_mn, bool* one_box, const char** err);
 
 // Plain row-major fp32 [G][rows][cols] map for TMA stores / epilogue tile loads, no swizzle.
 int make_rowmajor_map(CUtensorMap* out, const float* base, int64_t rows, int64_t cols, int64_t g, int64_t ld,

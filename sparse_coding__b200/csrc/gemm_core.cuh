@@ -43,6 +43,8 @@ struct GemmShape {
     int a_gmul[kMaxSeg], b_gmul[kMaxSeg];
     int a_one_box[kMaxSeg], b_one_box[kMaxSeg];  // MN-major operand described 4-D: one TMA box per tile
     int tiles_m, tiles_n;
+    int nprob;  // > 1: segment p is an independent problem p (own operands, own epilogue parameters) sharing
+                // the launch; groups are then laid out as [problem][member]
 };
 
 template <int BN>
@@ -66,6 +68,7 @@ struct RowCtx {
     int tile_m, tile_n;
     int tiles_m, tiles_n;
     int warp_q;  // which 32-row quarter of the tile this warp owns (0..3)
+    int prob;    // problem index when the launch batches independent problems (else 0)
     int half;    // which of the kEpiHalves warps of that quarter (takes chunks half, half+2, ...)
     int part;    // warp_q + 4*half: slot for per-warp partial results (0..4*kEpiHalves-1)
 };
@@ -114,7 +117,8 @@ gemm_tf32_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
     const uint32_t tmem_base = *tmem_ptr;
 
     const int tiles_per_group = shape.tiles_m * shape.tiles_n;
-    const int total_tiles = tiles_per_group * shape.G;
+    const int nprob = shape.nprob > 1 ? shape.nprob : 1;
+    const int total_tiles = tiles_per_group * shape.G * nprob;
 
     if (warp == 0) {
         // ------------------------------------------------------------------ TMA producer
@@ -122,12 +126,15 @@ gemm_tf32_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
             int stage = 0;
             uint32_t phase = 0;
             for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-                const int g = tile / tiles_per_group;
-                const int rem = tile - g * tiles_per_group;
+                const int gg = tile / tiles_per_group;
+                const int prob = gg / shape.G;
+                const int g = gg - prob * shape.G;
+                const int rem = tile - gg * tiles_per_group;
                 const int tn = rem / shape.tiles_m;
                 const int tm = rem - tn * shape.tiles_m;
                 const int m0 = tm * kBlockM, n0 = tn * BN;
-                for (int seg = 0; seg < shape.nseg; ++seg) {
+                const int seg_lo = nprob > 1 ? prob : 0, seg_hi = nprob > 1 ? prob + 1 : shape.nseg;
+                for (int seg = seg_lo; seg < seg_hi; ++seg) {
                     const int kblocks = (shape.K[seg] + kBlockK - 1) / kBlockK;
                     const int ga = g * shape.a_gmul[seg], gb = g * shape.b_gmul[seg];
                     for (int kb = 0; kb < kblocks; ++kb) {
@@ -173,7 +180,9 @@ gemm_tf32_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + as * BN;
                 uint32_t accumulate = 0;
-                for (int seg = 0; seg < shape.nseg; ++seg) {
+                const int prob = (tile / tiles_per_group) / shape.G;
+                const int seg_lo = nprob > 1 ? prob : 0, seg_hi = nprob > 1 ? prob + 1 : shape.nseg;
+                for (int seg = seg_lo; seg < seg_hi; ++seg) {
                     const int kblocks = (shape.K[seg] + kBlockK - 1) / kBlockK;
                     for (int kb = 0; kb < kblocks; ++kb) {
                         mbar_wait(&full_bar[stage], phase);
@@ -205,15 +214,17 @@ gemm_tf32_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
         const int half = (warp - 4) >> 2;
         int it = 0;
         for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
-            const int g = tile / tiles_per_group;
-            const int rem = tile - g * tiles_per_group;
+            const int gg = tile / tiles_per_group;
+            const int prob = gg / shape.G;
+            const int g = gg - prob * shape.G;
+            const int rem = tile - gg * tiles_per_group;
             const int tn = rem / shape.tiles_m;
             const int tm = rem - tn * shape.tiles_m;
             const int as = it & 1;
             const uint32_t aph = (it >> 1) & 1;
             RowCtx ctx;
             ctx.g = g; ctx.row = tm * kBlockM + q * 32 + lane; ctx.col0 = tn * BN;
-            ctx.M = shape.M; ctx.N = shape.N; ctx.tile_m = tm; ctx.tile_n = tn; ctx.tiles_m = shape.tiles_m; ctx.tiles_n = shape.tiles_n; ctx.warp_q = q; ctx.half = half; ctx.part = q + 4 * half;
+            ctx.M = shape.M; ctx.N = shape.N; ctx.tile_m = tm; ctx.tile_n = tn; ctx.tiles_m = shape.tiles_m; ctx.tiles_n = shape.tiles_n; ctx.warp_q = q; ctx.prob = prob; ctx.half = half; ctx.part = q + 4 * half;
             Epi epi(ep, ctx);
             constexpr int kChunks = (BN / 32 + kEpiHalves - 1) / kEpiHalves;
             // global loads the functor needs for its first chunk do not depend on the accumulator: issue them
@@ -262,7 +273,7 @@ cudaError_t launch_gemm(const GemmMaps& maps, GemmShape shape, const typename Ep
     }
     shape.tiles_m = (shape.M + kBlockM - 1) / kBlockM;
     shape.tiles_n = (shape.N + BN - 1) / BN;
-    const long long total = 1LL * shape.tiles_m * shape.tiles_n * shape.G;
+    const long long total = 1LL * shape.tiles_m * shape.tiles_n * shape.G * (shape.nprob > 1 ? shape.nprob : 1);
     if (total <= 0) return cudaSuccess;
     const int grid = static_cast<int>(total < num_sms ? total : num_sms);
     kern<<<grid, kGemmThreads, Cfg::kSmemBytes, stream>>>(maps, shape, ep);

@@ -111,12 +111,14 @@ struct GemmPlan {
     int sms;
 };
 
-inline int plan_gemm(GemmPlan* pl, int M, int N, int G, const Seg* segs, int nseg, bool a_mn, bool b_mn) {
+inline int plan_gemm(GemmPlan* pl, int M, int N, int G, const Seg* segs, int nseg, bool a_mn, bool b_mn,
+                     bool segs_are_problems = false) {
     memset(pl, 0, sizeof *pl);
     SC_TRY(device_sm_count(&pl->sms));
     pl->bn = pick_bn(N);
     GemmShape& sh = pl->sh;
     sh.M = M; sh.N = N; sh.G = G; sh.nseg = nseg;
+    sh.nprob = segs_are_problems ? nseg : 1;
     for (int s = 0; s < nseg; ++s) {
         if (segs[s].a.mn_major != a_mn || segs[s].b.mn_major != b_mn) return fail(-3, "operand major mismatch");
         if (segs[s].a.k != segs[s].b.k || segs[s].a.k <= 0) return fail(-3, "segment K mismatch");
@@ -146,10 +148,11 @@ int launch_plan(const GemmPlan& pl, const typename Epi::Params& ep, cudaStream_t
 
 // ACC[g] = sum_seg A_seg[g] B_seg[g]^T over G groups, epilogue Epi.  Operand majors are compile-time.
 template <bool A_MN, bool B_MN, class Epi>
-int run_gemm(int M, int N, int G, const Seg* segs, int nseg, const typename Epi::Params& ep, cudaStream_t stream) {
+int run_gemm(int M, int N, int G, const Seg* segs, int nseg, const typename Epi::Params& ep, cudaStream_t stream,
+             bool segs_are_problems = false) {
     if (M <= 0 || N <= 0 || G <= 0) return 0;
     GemmPlan pl;
-    SC_TRY(plan_gemm(&pl, M, N, G, segs, nseg, A_MN, B_MN));
+    SC_TRY(plan_gemm(&pl, M, N, G, segs, nseg, A_MN, B_MN, segs_are_problems));
     return launch_plan<A_MN, B_MN, Epi>(pl, ep, stream);
 }
 

@@ -214,24 +214,28 @@ SC_DEVICE void adam_update(float& p, float& mu, float& nu, float g, const AdamCo
 }
 
 struct EpiAdam {
-    struct Params {
+    struct Sub {
         float *p, *mu, *nu;     // [G][N][d]
-        const float* s_part;    // [G][tiles_b][N] (projected only)
+        const float* s_part;    // [G][parts][N] (projected only)
         const float* inv_norm;  // [G][N]  1/max(||W_n||,1e-8), negative when the clamp is active
         float* grad_out;        // optional [G][N][d]: write the gradient instead of applying Adam (data parallel)
-        long long gstride;      // N*d
-        int tiles_b;
         int projected;
+    };
+    struct Params {
+        Sub sub[2];             // one per batched problem (untied: [0] encoder, [1] decoder)
+        long long gstride;      // N*d
+        int tiles_b;            // partial slots per feature in s_part
         AdamConst a;
     };
     const Params& p;
+    const Sub& u;
     const RowCtx c;
     float s, inv;
     bool clamped;
-    SC_DEVICE EpiAdam(const Params& p_, const RowCtx& c_) : p(p_), c(c_), s(0.f), inv(1.f), clamped(false) {
-        if (p.projected && c.row < c.M) {
-            for (int t = 0; t < p.tiles_b; ++t) s += p.s_part[((long long)c.g * p.tiles_b + t) * c.M + c.row];
-            const float iv = p.inv_norm[(long long)c.g * c.M + c.row];
+    SC_DEVICE EpiAdam(const Params& p_, const RowCtx& c_) : p(p_), u(p_.sub[c_.prob]), c(c_), s(0.f), inv(1.f), clamped(false) {
+        if (u.projected && c.row < c.M) {
+            for (int t = 0; t < p.tiles_b; ++t) s += u.s_part[((long long)c.g * p.tiles_b + t) * c.M + c.row];
+            const float iv = u.inv_norm[(long long)c.g * c.M + c.row];
             clamped = iv < 0.f;
             inv = fabsf(iv);
         }
@@ -243,23 +247,23 @@ struct EpiAdam {
         const int ncols = c.N - col;
         const long long off = c.g * p.gstride + (long long)c.row * c.N + col;
         float pv[32];
-        load_row32(p.p + off, pv, ncols);
-        if (p.projected) {
+        load_row32(u.p + off, pv, ncols);
+        if (u.projected) {
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] = clamped ? v[j] * inv : (v[j] - s * (pv[j] * inv)) * inv;
         }
-        if (p.grad_out) {
-            store_row32(p.grad_out + off, v, ncols);
+        if (u.grad_out) {
+            store_row32(u.grad_out + off, v, ncols);
             return;
         }
         float mv[32], nv[32];
-        load_row32(p.mu + off, mv, ncols);
-        load_row32(p.nu + off, nv, ncols);
+        load_row32(u.mu + off, mv, ncols);
+        load_row32(u.nu + off, nv, ncols);
 #pragma unroll
         for (int j = 0; j < 32; ++j) adam_update(pv[j], mv[j], nv[j], v[j], p.a);
-        store_row32(p.p + off, pv, ncols);
-        store_row32(p.mu + off, mv, ncols);
-        store_row32(p.nu + off, nv, ncols);
+        store_row32(u.p + off, pv, ncols);
+        store_row32(u.mu + off, mv, ncols);
+        store_row32(u.nu + off, nv, ncols);
     }
     SC_DEVICE void finish() {}
 };

@@ -104,33 +104,34 @@ __global__ void finalize_kernel(const float* __restrict__ l1_part, int n_l1, con
                                 float* __restrict__ bias_mu, float* __restrict__ bias_nu,
                                 const float* __restrict__ l1_alpha, const float* __restrict__ bias_decay,
                                 float* __restrict__ out_losses, int M, int B, int d, int N, int tied, AdamConst a,
-                                float* __restrict__ grad_bias) {
+                                float* __restrict__ grad_bias, float* __restrict__ bnorm_ws) {
+    // grid (ceil(N/256), M).  Every block needs ||b|| of the PRE-update bias: block x == 0 of each member
+    // computed it into bnorm_ws in bias_norm_kernel (launched before), so no block reads a bias another
+    // block already updated.
     __shared__ float sh[8];
-    const int m = blockIdx.x;
-    float acc = 0.f;
-    for (int i = threadIdx.x; i < n_l1; i += blockDim.x) acc += l1_part[(long long)m * n_l1 + i];
-    const float l1_sum = block_sum(acc, sh);
-    acc = 0.f;
-    for (int i = threadIdx.x; i < n_mse; i += blockDim.x) acc += mse_part[(long long)m * n_mse + i];
-    const float sq_sum = block_sum(acc, sh);
-    acc = 0.f;
-    for (int n = threadIdx.x; n < N; n += blockDim.x) {
-        const float b = bias[(long long)m * N + n];
-        acc += b * b;
-    }
-    const float bnorm = sqrtf(block_sum(acc, sh));
+    const int m = blockIdx.y;
+    const float bnorm = bnorm_ws[m];
     const float lam = l1_alpha[m], beta = bias_decay[m];
-    if (threadIdx.x == 0) {
-        const float l_rec = sq_sum / ((float)B * (float)d);  // B here is the normalising (global) batch size
-        const float l_l1 = lam * (l1_sum / (float)B);
-        const float l_bd = beta * bnorm;
-        out_losses[0 * M + m] = l_rec + l_l1 + l_bd;
-        out_losses[1 * M + m] = l_rec;
-        out_losses[2 * M + m] = l_l1;
-        out_losses[3 * M + m] = l_bd;
+    if (blockIdx.x == 0) {
+        float acc = 0.f;
+        for (int i = threadIdx.x; i < n_l1; i += blockDim.x) acc += l1_part[(long long)m * n_l1 + i];
+        const float l1_sum = block_sum(acc, sh);
+        acc = 0.f;
+        for (int i = threadIdx.x; i < n_mse; i += blockDim.x) acc += mse_part[(long long)m * n_mse + i];
+        const float sq_sum = block_sum(acc, sh);
+        if (threadIdx.x == 0) {
+            const float l_rec = sq_sum / ((float)B * (float)d);  // B here is the normalising (global) batch size
+            const float l_l1 = lam * (l1_sum / (float)B);
+            const float l_bd = beta * bnorm;
+            out_losses[0 * M + m] = l_rec + l_l1 + l_bd;
+            out_losses[1 * M + m] = l_rec;
+            out_losses[2 * M + m] = l_l1;
+            out_losses[3 * M + m] = l_bd;
+        }
     }
     const float bscale = bnorm > 0.f ? beta / bnorm : 0.f;
-    for (int n = threadIdx.x; n < N; n += blockDim.x) {
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n < N) {
         float g = 0.f;
         for (int t = 0; t < tiles_b; ++t) g += db_part[((long long)m * tiles_b + t) * N + n];
         const long long o = (long long)m * N + n;
@@ -146,6 +147,18 @@ __global__ void finalize_kernel(const float* __restrict__ l1_part, int n_l1, con
     }
 }
 
+// ||b||_2 per member (sae_ensemble.py:64), one block per member
+__global__ void bias_norm_kernel(const float* __restrict__ bias, int N, float* __restrict__ out) {
+    __shared__ float sh[8];
+    float acc = 0.f;
+    for (int n = threadIdx.x; n < N; n += blockDim.x) {
+        const float b = bias[(long long)blockIdx.x * N + n];
+        acc += b * b;
+    }
+    const float t = block_sum(acc, sh);
+    if (threadIdx.x == 0) out[blockIdx.x] = sqrtf(t);
+}
+
 }  // namespace sc
 
 // ================================================================================================
@@ -154,7 +167,7 @@ __global__ void finalize_kernel(const float* __restrict__ l1_part, int n_l1, con
 namespace sc {
 
 struct StepWs {
-    float *x_r, *enc_r, *D_r, *inv_norm, *R_r, *dz, *l1_part, *mse_part, *db_part, *s_part;
+    float *x_r, *enc_r, *D_r, *inv_norm, *R_r, *dz, *l1_part, *mse_part, *db_part, *s_part, *bnorm;
     int n_l1, n_mse, tiles_b;
     size_t bytes;
 };
@@ -176,6 +189,7 @@ static StepWs carve_step(void* base, int M, int B, int d, int N, int tied, int x
     w.mse_part = c.floats(Mz * w.n_mse);
     w.db_part = c.floats(Mz * w.tiles_b * Nz);
     w.s_part = c.floats(Mz * w.tiles_b * Nz);
+    w.bnorm = c.floats(Mz);
     w.bytes = c.off;
     return w;
 }
@@ -260,24 +274,30 @@ static int sae_step_impl(const ScStepArgs& a) {
     prof_mark(st, "G3_back_code");
     // 6/7. weight gradients with fused Adam                          [N x d], K = B
     if (!a.tied) {
-        Seg s4{mnmajor(w.dz, N, B, M, BN_), mnmajor(w.x_r, d, B, xg, Bd)};
-        EpiAdam::Params e4{a.enc, a.enc_mu, a.enc_nu, nullptr, nullptr, a.grad_enc, Nd, w.tiles_b, 0, ad};
-        SC_TRY((run_gemm<true, true, EpiAdam>(N, d, M, &s4, 1, e4, st)));
-        prof_mark(st, "G4_dWenc_adam");
-        Seg s5{mnmajor(a.out_c, N, B, M, BN_), mnmajor(w.R_r, d, B, M, Bd)};
-        EpiAdam::Params e5{a.dec, a.dec_mu, a.dec_nu, w.s_part, w.inv_norm, grad_mode ? a.grad_dec : nullptr, Nd, w.tiles_b, 1, ad};
-        SC_TRY((run_gemm<true, true, EpiAdam>(N, d, M, &s5, 1, e5, st)));
+        // one launch, two independent problems: dW_e = dz^T x (plain) and dW_d = c^T R (projected)
+        Seg s45[2] = {{mnmajor(w.dz, N, B, M, BN_), mnmajor(w.x_r, d, B, xg, Bd)},
+                      {mnmajor(a.out_c, N, B, M, BN_), mnmajor(w.R_r, d, B, M, Bd)}};
+        EpiAdam::Params e{};
+        e.sub[0] = {a.enc, a.enc_mu, a.enc_nu, nullptr, nullptr, a.grad_enc, 0};
+        e.sub[1] = {a.dec, a.dec_mu, a.dec_nu, w.s_part, w.inv_norm, grad_mode ? a.grad_dec : nullptr, 1};
+        e.gstride = Nd; e.tiles_b = w.tiles_b; e.a = ad;
+        SC_TRY((run_gemm<true, true, EpiAdam>(N, d, M, s45, 2, e, st, /*segs_are_problems=*/true)));
     } else {
         Seg s[2] = {{mnmajor(a.out_c, N, B, M, BN_), mnmajor(w.R_r, d, B, M, Bd)},
                     {mnmajor(w.dz, N, B, M, BN_), mnmajor(w.x_r, d, B, xg, Bd)}};
-        EpiAdam::Params e{a.enc, a.enc_mu, a.enc_nu, w.s_part, w.inv_norm, a.grad_enc, Nd, w.tiles_b, 1, ad};
+        EpiAdam::Params e{};
+        e.sub[0] = {a.enc, a.enc_mu, a.enc_nu, w.s_part, w.inv_norm, a.grad_enc, 1};
+        e.sub[1] = e.sub[0];
+        e.gstride = Nd; e.tiles_b = w.tiles_b; e.a = ad;
         SC_TRY((run_gemm<true, true, EpiAdam>(N, d, M, s, 2, e, st)));
     }
-    prof_mark(st, a.tied ? "G45_dW_adam" : "G5_dWdec_adam");
+    prof_mark(st, "G45_dW_adam");
     // 8. loss scalars + bias Adam
-    finalize_kernel<<<M, 256, 0, st>>>(w.l1_part, w.n_l1, w.mse_part, w.n_mse, w.db_part, w.tiles_b, a.bias, a.bias_mu,
-                                       a.bias_nu, a.l1_alpha, a.bias_decay, a.out_losses, M, Bn, d, N, a.tied, ad,
-                                       grad_mode ? a.grad_bias : nullptr);
+    bias_norm_kernel<<<M, 256, 0, st>>>(a.bias, N, w.bnorm);
+    finalize_kernel<<<dim3(ceil_div(N, 256), M), 256, 0, st>>>(w.l1_part, w.n_l1, w.mse_part, w.n_mse, w.db_part, w.tiles_b,
+                                                             a.bias, a.bias_mu, a.bias_nu, a.l1_alpha, a.bias_decay,
+                                                             a.out_losses, M, Bn, d, N, a.tied, ad,
+                                                             grad_mode ? a.grad_bias : nullptr, w.bnorm);
     SC_CUDA(cudaGetLastError(), "finalize launch");
     prof_mark(st, "finalize");
     return 0;

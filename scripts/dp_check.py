@@ -1,0 +1,80 @@
+"""Multi-GPU check of the data-parallel single-dictionary path (BASELINE.json configs[4] shape family):
+torchrun --nproc-per-node G scripts/dp_check.py [--d 2048 --n 65536 --batch 8192 --steps 5]
+Every rank trains the same dictionary on its slice of the rows (gradient-only fused step + one NCCL
+all-reduce + sc_adam_apply); rank 0 also steps a single-GPU copy on the full batch and reports the
+difference, then times the data-parallel step."""
+import argparse
+import json
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import sparse_coding__b200 as sc  # noqa: E402
+from sparse_coding__b200.dist import DataParallelEnsemble, shard_rows  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--d", type=int, default=512)
+    ap.add_argument("--n", type=int, default=8192)
+    ap.add_argument("--batch", type=int, default=2048, help="rows per GPU")
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--check", type=int, default=1)
+    a = ap.parse_args()
+    rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    torch.manual_seed(0)
+    model = sc.FunctionalSAE.init(a.d, a.n, 1e-3, device=dev)
+    ens = sc.FunctionalEnsemble([model], sc.FunctionalSAE, sc.torchopt_compat.adam, {"lr": 1e-3}, device=dev)
+    dp = DataParallelEnsemble(ens)
+    dp.broadcast_parameters(0)
+    B = a.batch * world
+    g = torch.Generator(device="cpu").manual_seed(1)
+    full = torch.randn(B, a.d, generator=g).to(dev)
+    lo, hi = shard_rows(B, rank, world)
+    out = {"world": world, "d": a.d, "n": a.n, "global_batch": B}
+    if a.check:
+        ref = None
+        if rank == 0:
+            torch.manual_seed(0)
+            ref = sc.FunctionalEnsemble([sc.FunctionalSAE.init(a.d, a.n, 1e-3, device=dev)], sc.FunctionalSAE,
+                                        sc.torchopt_compat.adam, {"lr": 1e-3}, device=dev)
+        worst = 0.0
+        for s in range(3):
+            l, _ = dp.step_batch(full[lo:hi])
+            if rank == 0:
+                lr, _ = ref.step_batch(full)
+                worst = max(worst, float(((l["loss"] - lr["loss"]).abs() / lr["loss"].abs()).max()))
+        if rank == 0:
+            out["max_rel_loss_diff_vs_single_gpu_full_batch"] = worst
+            out["mean_abs_param_diff"] = {k: float((ens.params[k] - ref.params[k]).abs().mean()) for k in ens.params}
+            del ref
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for s in range(a.steps):
+        dp.step_batch(full[lo:hi])
+    e1.record()
+    torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1) / a.steps], device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    if rank == 0:
+        out["ms_per_step"] = float(t)
+        out["activations_per_s"] = B / (float(t) * 1e-3)
+        out["step_tflops"] = 10.0 * B * a.n * a.d / (float(t) * 1e-3) / 1e12
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -168,3 +168,25 @@ def test_rejects_cpu_and_unknown_signature():
     ens = sc.FunctionalEnsemble(models, sc.FunctionalSAE, sc.torchopt_compat.adam, {"lr": 1e-3}, device="cuda")
     with pytest.raises(NotImplementedError):
         ens.step_batch(torch.randn(8, 16))
+
+
+def test_gradient_only_then_adam_apply_equals_fused_step():
+    """The data-parallel path (gradient-only step -> [all-reduce] -> sc_adam_apply) must land where the
+    fused step lands; also exercises DataParallelEnsemble with a world of one."""
+    import sparse_coding__b200 as sc
+    from sparse_coding__b200.dist import DataParallelEnsemble
+    M, B, d, N = 2, 300, 64, 256
+    for kind in ("untied", "tied"):
+        ens_a, _ = _pair(kind, d, N, [1e-3, 1e-2], seed=5, bias_decay=0.03)
+        ens_b, _ = _pair(kind, d, N, [1e-3, 1e-2], seed=5, bias_decay=0.03)
+        for e in (ens_a, ens_b):
+            e.params["encoder_bias"] += 0.01
+        dp = DataParallelEnsemble(ens_b)
+        x = make_sparse_data(3 * B, d, 2 * d, 6, seed=6).cuda()
+        for s in range(3):
+            la, _ = ens_a.step_batch(x[s * B:(s + 1) * B])
+            lb, _ = dp.step_batch(x[s * B:(s + 1) * B])
+            for k in ("loss", "l_reconstruction", "l_l1"):
+                assert torch.allclose(la[k], lb[k], rtol=1e-5, atol=1e-8), (kind, s, k)
+        for k in ens_a.params:
+            assert float((ens_a.params[k] - ens_b.params[k]).abs().max()) < 1e-6, (kind, k)

@@ -217,6 +217,13 @@ def run_ours(args):
     ms_step = float(t.item()) / args.steps
     value = B * M * world / (ms_step * 1e-3)
 
+    if args.quick:
+        if rank == 0:
+            print(json.dumps({"metric": METRIC, "value": value, "unit": UNIT, "ms_per_step": ms_step, "quick": True}))
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
     # end to end: pinned host batch -> device, loss scalars -> host, every step
     for i in range(min(args.warmup, 5)):
         e2e_step(i)
@@ -301,6 +308,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--batch", type=int, default=2048)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--quick", action="store_true", help="profiling runs: skip e2e, peak measurement and the CPU baseline")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":

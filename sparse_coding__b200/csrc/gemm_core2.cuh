@@ -1,0 +1,261 @@
+// CTA-pair variant of the GEMM core: tcgen05.mma.cta_group::2, one 256 x BN accumulator tile per
+// cluster of two CTAs (two SMs of a TPC).  Each CTA stages its own 128 rows of A and HALF of the B
+// tile (BN/2 rows), so a pipeline stage is 16 KB + BN/2*128 B instead of 16 KB + BN*128 B: for BN = 256
+// that is 32 KB instead of 48 KB per 128x256x32 MACs of work per SM - a third less L2 -> SM traffic
+// and 7 stages instead of 4 in the same shared memory, i.e. more latency tolerance where the
+// single-CTA kernel stalls on operand delivery (ncu: tensor pipe ~37 %, L2 ~40 %, nothing saturated).
+//
+// Differences to gemm_core.cuh, following the 2-SM pattern of the public sm_100 GEMMs:
+//   * TMA loads of both CTAs complete on the LEADER's full barrier (2 arrivals: leader's
+//     arrive.expect_tx for both CTAs' bytes + the peer's remote arrive)
+//   * only the leader issues MMAs; tcgen05.commit is multicast to both CTAs' empty / tmem_full barriers
+//   * epilogue warps of both CTAs arrive remotely on the leader's tmem_empty barrier
+//   * TMEM alloc / dealloc with cta_group::2 in both CTAs, cluster barriers around set-up and tear-down
+// Epilogue functors, operand descriptions and the RowCtx are shared with the single-CTA core.
+#pragma once
+#include <cuda_runtime.h>
+
+#include "gemm_core.cuh"
+
+namespace sc {
+
+template <int BN>
+struct GemmCfg2 {
+    static constexpr int kBHalf = BN / 2;
+    static constexpr int kBTileBytes = kBHalf * kBlockK * 4;
+    static constexpr int kStageBytes = kATileBytes + kBTileBytes;
+    static constexpr int kStagesRaw = (227 * 1024 - 2048) / kStageBytes;
+    static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
+    static constexpr int kTmemCols = GemmCfg<BN>::kTmemCols;
+    static constexpr int kBarrierBytes = (2 * kStages + 4) * 8 + 16;
+    static constexpr int kSmemBytes = kStages * kStageBytes + kBarrierBytes + 1024;
+    static_assert(BN % 64 == 0 && BN >= 64 && BN <= 256, "paired kernel: BN multiple of 64 in [64,256]");
+};
+
+template <int BN, bool A_MN, bool B_MN, class Epi>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
+                      const __grid_constant__ typename Epi::Params ep) {
+    using Cfg = GemmCfg2<BN>;
+    constexpr int kStages = Cfg::kStages;
+    constexpr int kBHalf = Cfg::kBHalf;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kStages * Cfg::kStageBytes);
+    uint64_t* empty_bar = full_bar + kStages;
+    uint64_t* tmem_full = empty_bar + kStages;
+    uint64_t* tmem_empty = tmem_full + 2;
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    const bool leader = rank == 0;
+
+    cluster_sync_all();  // both CTAs resident before any cross-CTA state is touched
+    if (warp == 0 && lane == 0) {
+        for (int s = 0; s < shape.nseg; ++s) {
+            tma_prefetch_desc(&maps.a[s]);
+            tma_prefetch_desc(&maps.b[s]);
+        }
+    }
+    if (warp == 1 && lane == 0) {
+        for (int i = 0; i < kStages; ++i) {
+            mbar_init(&full_bar[i], 2);   // leader's expect_tx arrive + peer's remote arrive (used on the leader only)
+            mbar_init(&empty_bar[i], 1);  // multicast commit from the leader's MMA thread
+        }
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&tmem_full[i], 1);
+            mbar_init(&tmem_empty[i], 2 * 128 * kEpiHalves);  // epilogue threads of BOTH CTAs (leader's copy is used)
+        }
+        fence_mbar_init();
+    }
+    if (warp == 2) {
+        tmem_alloc_2cta(tmem_ptr, Cfg::kTmemCols);
+        tmem_relinquish_2cta();
+    }
+    tc_fence_before();
+    cluster_sync_all();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr;
+
+    const int nprob = shape.nprob > 1 ? shape.nprob : 1;
+    const int tiles_per_group = shape.tiles_m * shape.tiles_n;  // tiles_m counts 256-row tiles here
+    const int total_tiles = tiles_per_group * shape.G * nprob;
+    const int cluster_id = blockIdx.x >> 1;
+    const int num_clusters = gridDim.x >> 1;
+
+    if (warp == 0) {
+        // ------------------------------------------------------------------ TMA producer (both CTAs)
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int tile = cluster_id; tile < total_tiles; tile += num_clusters) {
+                const int gg = tile / tiles_per_group;
+                const int prob = gg / shape.G;
+                const int g = gg - prob * shape.G;
+                const int rem = tile - gg * tiles_per_group;
+                const int tn = rem / shape.tiles_m;
+                const int tm = rem - tn * shape.tiles_m;
+                const int m0 = tm * (2 * kBlockM) + rank * kBlockM;
+                const int n0 = tn * BN + rank * kBHalf;
+                const int seg_lo = nprob > 1 ? prob : 0, seg_hi = nprob > 1 ? prob + 1 : shape.nseg;
+                for (int seg = seg_lo; seg < seg_hi; ++seg) {
+                    const int kblocks = (shape.K[seg] + kBlockK - 1) / kBlockK;
+                    const int ga = g * shape.a_gmul[seg], gb = g * shape.b_gmul[seg];
+                    for (int kb = 0; kb < kblocks; ++kb) {
+                        mbar_wait(&empty_bar[stage], phase ^ 1);
+                        uint8_t* sa = smem + stage * Cfg::kStageBytes;
+                        uint8_t* sb = sa + kATileBytes;
+                        const int k0 = kb * kBlockK;
+                        if (!A_MN) {
+                            tma_load_3d_2cta(&maps.a[seg], &full_bar[stage], sa, k0, m0, ga);
+                        } else if (shape.a_one_box[seg]) {
+                            tma_load_4d_2cta(&maps.a[seg], &full_bar[stage], sa, 0, k0, m0 >> 5, ga);
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < kBlockM / 32; ++i)
+                                tma_load_3d_2cta(&maps.a[seg], &full_bar[stage], sa + i * 4096, m0 + 32 * i, k0, ga);
+                        }
+                        if (!B_MN) {
+                            tma_load_3d_2cta(&maps.b[seg], &full_bar[stage], sb, k0, n0, gb);
+                        } else if (shape.b_one_box[seg]) {
+                            tma_load_4d_2cta(&maps.b[seg], &full_bar[stage], sb, 0, k0, n0 >> 5, gb);
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < kBHalf / 32; ++i)
+                                tma_load_3d_2cta(&maps.b[seg], &full_bar[stage], sb + i * 4096, n0 + 32 * i, k0, gb);
+                        }
+                        if (leader) mbar_arrive_expect_tx(&full_bar[stage], 2 * Cfg::kStageBytes);
+                        else mbar_arrive_remote(&full_bar[stage], 0);
+                        if (++stage == kStages) { stage = 0; phase ^= 1; }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ------------------------------------------------------------------ MMA issuer (leader CTA only)
+        if (leader && lane == 0) {
+            constexpr uint32_t idesc = make_idesc_tf32(2 * kBlockM, BN, A_MN, B_MN);
+            int stage = 0;
+            uint32_t phase = 0;
+            int it = 0;
+            for (int tile = cluster_id; tile < total_tiles; tile += num_clusters, ++it) {
+                const int as = it & 1;
+                const uint32_t aph = (it >> 1) & 1;
+                mbar_wait(&tmem_empty[as], aph ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + as * BN;
+                uint32_t accumulate = 0;
+                const int prob = (tile / tiles_per_group) / shape.G;
+                const int seg_lo = nprob > 1 ? prob : 0, seg_hi = nprob > 1 ? prob + 1 : shape.nseg;
+                for (int seg = seg_lo; seg < seg_hi; ++seg) {
+                    const int kblocks = (shape.K[seg] + kBlockK - 1) / kBlockK;
+                    for (int kb = 0; kb < kblocks; ++kb) {
+                        mbar_wait(&full_bar[stage], phase);
+                        tc_fence_after();
+                        const uint32_t a_base = smem_u32(smem + stage * Cfg::kStageBytes);
+                        const uint32_t b_base = a_base + kATileBytes;
+#pragma unroll
+                        for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+                            const uint64_t da = A_MN ? make_smem_desc(a_base + k * 1024, 4096, 512, kLayoutSw128Base32)
+                                                     : make_smem_desc(a_base + k * 32, 16, 1024, kLayoutSw128);
+                            const uint64_t db = B_MN ? make_smem_desc(b_base + k * 1024, 4096, 512, kLayoutSw128Base32)
+                                                     : make_smem_desc(b_base + k * 32, 16, 1024, kLayoutSw128);
+                            umma_tf32_2cta(d_tmem, da, db, idesc, accumulate);
+                            accumulate = 1;
+                        }
+                        umma_commit_2cta(&empty_bar[stage]);
+                        if (++stage == kStages) { stage = 0; phase ^= 1; }
+                    }
+                }
+                umma_commit_2cta(&tmem_full[as]);
+            }
+        }
+    } else if (warp >= 4) {
+        // ------------------------------------------------------------------ epilogue (both CTAs, own 128 rows)
+        const int q = warp & 3;
+        const int half = (warp - 4) >> 2;
+        int it = 0;
+        for (int tile = cluster_id; tile < total_tiles; tile += num_clusters, ++it) {
+            const int gg = tile / tiles_per_group;
+            const int prob = gg / shape.G;
+            const int g = gg - prob * shape.G;
+            const int rem = tile - gg * tiles_per_group;
+            const int tn = rem / shape.tiles_m;
+            const int tm = rem - tn * shape.tiles_m;
+            const int as = it & 1;
+            const uint32_t aph = (it >> 1) & 1;
+            RowCtx ctx;
+            ctx.g = g; ctx.row = tm * (2 * kBlockM) + rank * kBlockM + q * 32 + lane; ctx.col0 = tn * BN;
+            ctx.M = shape.M; ctx.N = shape.N;
+            // partial-sum slots are indexed by 128-row tile: report this CTA's half as its own row tile
+            ctx.tile_m = tm * 2 + rank; ctx.tile_n = tn; ctx.tiles_m = shape.tiles_m * 2; ctx.tiles_n = shape.tiles_n;
+            ctx.warp_q = q; ctx.prob = prob; ctx.half = half; ctx.part = q + 4 * half;
+            Epi epi(ep, ctx);
+            constexpr int kChunks = (BN / 32 + kEpiHalves - 1) / kEpiHalves;
+            if (half < BN / 32) epi.prefetch(half * 32);
+            mbar_wait(&tmem_full[as], aph);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
+#pragma unroll 1
+            for (int i = 0; i < kChunks; ++i) {
+                const int c = half + i * kEpiHalves;
+                if (c < BN / 32) {
+                    float v[32];
+                    tmem_ld32(taddr + c * 32, v);
+                    tmem_ld_wait();
+                    epi.chunk(c * 32, v, (c + kEpiHalves < BN / 32) ? (c + kEpiHalves) * 32 : -1);
+                }
+            }
+            tc_fence_before();
+            if (leader) mbar_arrive(&tmem_empty[as]);
+            else mbar_arrive_remote(&tmem_empty[as], 0);
+            epi.finish();
+        }
+    }
+
+    tc_fence_before();
+    cluster_sync_all();  // every remote arrive has landed and every TMEM read is done in both CTAs
+    if (warp == 2) {
+        tc_fence_after();
+        tmem_dealloc_2cta(tmem_base, Cfg::kTmemCols);
+    }
+}
+
+// grid = 2 * min(#tiles, #SMs / 2) persistent CTAs in clusters of two.
+template <int BN, bool A_MN, bool B_MN, class Epi>
+cudaError_t launch_gemm_2cta(const GemmMaps& maps, GemmShape shape, const typename Epi::Params& ep, int num_sms,
+                             cudaStream_t stream) {
+    using Cfg = GemmCfg2<BN>;
+    auto kern = gemm_tf32_2cta_kernel<BN, A_MN, B_MN, Epi>;
+    static bool attr_set[64] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (!attr_set[dev & 63]) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
+        if (e != cudaSuccess) return e;
+        attr_set[dev & 63] = true;
+    }
+    shape.tiles_m = (shape.M + 2 * kBlockM - 1) / (2 * kBlockM);
+    shape.tiles_n = (shape.N + BN - 1) / BN;
+    const long long total = 1LL * shape.tiles_m * shape.tiles_n * shape.G * (shape.nprob > 1 ? shape.nprob : 1);
+    if (total <= 0) return cudaSuccess;
+    const int pairs = num_sms / 2;
+    const int clusters = static_cast<int>(total < pairs ? total : pairs);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2 * clusters);
+    cfg.blockDim = dim3(kGemmThreads);
+    cfg.dynamicSmemBytes = Cfg::kSmemBytes;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kern, maps, shape, ep);
+}
+
+}  // namespace sc

@@ -5,7 +5,10 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <stdlib.h>
+
 #include "gemm_core.cuh"
+#include "gemm_core2.cuh"
 #include "tmap.h"
 
 namespace sc {
@@ -89,6 +92,20 @@ struct Carver {
     }
 };
 
+// CTA-pair (cta_group::2) kernels are the default; SC_B200_CTA_PAIRS=0 selects the single-CTA core.
+inline bool use_cta_pairs() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("SC_B200_CTA_PAIRS");
+        v = (e && e[0] == '0') ? 0 : 1;
+    }
+    return v == 1;
+}
+// number of 128-row tile slots the epilogues index for an output with `rows` rows
+inline int row_tiles128(long long rows) {
+    return use_cta_pairs() ? 2 * static_cast<int>((rows + 255) / 256) : static_cast<int>((rows + 127) / 128);
+}
+
 inline int pick_bn(long long n) { return n > 128 ? 256 : (n > 64 ? 128 : 64); }
 inline int ceil_div(long long a, long long b) { return static_cast<int>((a + b - 1) / b); }
 
@@ -109,6 +126,7 @@ struct GemmPlan {
     GemmShape sh;
     int bn;
     int sms;
+    bool cta2;
 };
 
 inline int plan_gemm(GemmPlan* pl, int M, int N, int G, const Seg* segs, int nseg, bool a_mn, bool b_mn,
@@ -116,6 +134,7 @@ inline int plan_gemm(GemmPlan* pl, int M, int N, int G, const Seg* segs, int nse
     memset(pl, 0, sizeof *pl);
     SC_TRY(device_sm_count(&pl->sms));
     pl->bn = pick_bn(N);
+    pl->cta2 = use_cta_pairs();
     GemmShape& sh = pl->sh;
     sh.M = M; sh.N = N; sh.G = G; sh.nseg = nseg;
     sh.nprob = segs_are_problems ? nseg : 1;
@@ -125,7 +144,7 @@ inline int plan_gemm(GemmPlan* pl, int M, int N, int G, const Seg* segs, int nse
         const char* err = nullptr;
         bool a1 = false, b1 = false;
         int rc = make_operand_map(&pl->maps.a[s], segs[s].a, kBlockM, &a1, &err);
-        if (rc == 0) rc = make_operand_map(&pl->maps.b[s], segs[s].b, pl->bn, &b1, &err);
+        if (rc == 0) rc = make_operand_map(&pl->maps.b[s], segs[s].b, pl->cta2 ? pl->bn / 2 : pl->bn, &b1, &err);
         sh.a_one_box[s] = a1;
         sh.b_one_box[s] = b1;
         if (rc != 0) return fail(rc, "%s", err ? err : "tensor map creation failed");
@@ -139,6 +158,13 @@ inline int plan_gemm(GemmPlan* pl, int M, int N, int G, const Seg* segs, int nse
 template <bool A_MN, bool B_MN, class Epi>
 int launch_plan(const GemmPlan& pl, const typename Epi::Params& ep, cudaStream_t stream) {
     cudaError_t e;
+    if (pl.cta2) {
+        if (pl.bn == 256) e = launch_gemm_2cta<256, A_MN, B_MN, Epi>(pl.maps, pl.sh, ep, pl.sms, stream);
+        else if (pl.bn == 128) e = launch_gemm_2cta<128, A_MN, B_MN, Epi>(pl.maps, pl.sh, ep, pl.sms, stream);
+        else e = launch_gemm_2cta<64, A_MN, B_MN, Epi>(pl.maps, pl.sh, ep, pl.sms, stream);
+        if (e != cudaSuccess) return cuda_fail(e, "gemm (CTA pair) launch");
+        return 0;
+    }
     if (pl.bn == 256) e = launch_gemm<256, A_MN, B_MN, Epi>(pl.maps, pl.sh, ep, pl.sms, stream);
     else if (pl.bn == 128) e = launch_gemm<128, A_MN, B_MN, Epi>(pl.maps, pl.sh, ep, pl.sms, stream);
     else e = launch_gemm<64, A_MN, B_MN, Epi>(pl.maps, pl.sh, ep, pl.sms, stream);

@@ -179,7 +179,7 @@ static int decode_impl(const ScDecodeArgs& a) {
     const long long Bd = (long long)B * d, Nd = (long long)N * d, BN_ = (long long)B * N;
     float* c_r = cv.floats((size_t)G * BN_);
     float* D_r = cv.floats((size_t)G * Nd);
-    const int n_part = ceil_div(B, kBlockM) * ceil_div(d, pick_bn(d)) * 4 * kEpiHalves;
+    const int n_part = row_tiles128(B) * ceil_div(d, pick_bn(d)) * 4 * kEpiHalves;
     float* part = cv.floats((size_t)G * n_part);
     SC_TRY(round_copy(a.c, c_r, G * BN_, st));
     dim3 grid(ceil_div(N, 8), G);
@@ -215,7 +215,7 @@ size_t sc_decode_workspace_bytes(int32_t G, int32_t B, int32_t d, int32_t N) {
     sc::Carver cv(nullptr);
     cv.floats((size_t)G * B * N);
     cv.floats((size_t)G * N * d);
-    cv.floats((size_t)G * sc::ceil_div(B, sc::kBlockM) * sc::ceil_div(d, sc::pick_bn(d)) * 4 * sc::kEpiHalves);
+    cv.floats((size_t)G * sc::row_tiles128(B) * sc::ceil_div(d, sc::pick_bn(d)) * 4 * sc::kEpiHalves);
     return cv.off;
 }
 

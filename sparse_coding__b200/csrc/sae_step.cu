@@ -182,8 +182,8 @@ static StepWs carve_step(void* base, int M, int B, int d, int N, int tied, int x
     w.inv_norm = c.floats(Mz * Nz);
     w.R_r = c.floats(Mz * Bz * dz_);
     w.dz = c.floats(Mz * Bz * Nz);
-    w.n_l1 = ceil_div(B, kBlockM) * ceil_div(N, pick_bn(N)) * 4 * kEpiHalves;
-    w.n_mse = ceil_div(B, kBlockM) * ceil_div(d, pick_bn(d)) * 4 * kEpiHalves;
+    w.n_l1 = row_tiles128(B) * ceil_div(N, pick_bn(N)) * 4 * kEpiHalves;
+    w.n_mse = row_tiles128(B) * ceil_div(d, pick_bn(d)) * 4 * kEpiHalves;
     w.tiles_b = ceil_div(B, pick_bn(B)) * kEpiHalves;  // partial slots per feature
     w.l1_part = c.floats(Mz * w.n_l1);
     w.mse_part = c.floats(Mz * w.n_mse);

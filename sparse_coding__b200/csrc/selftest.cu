@@ -10,6 +10,7 @@
 #include <vector>
 
 #include "epi_store.cuh"
+#include "gemm_core2.cuh"
 #include "tmap.h"
 
 using namespace sc;
@@ -31,18 +32,21 @@ static float host_rn_tf32(float x) {
         }                                                                              \
     } while (0)
 
+static int g_cg = 1;
 template <int BN, bool A_MN, bool B_MN>
 static cudaError_t run(const GemmMaps& maps, const GemmShape& sh, const EpiStore::Params& ep, int sms) {
+    if (g_cg == 2) return launch_gemm_2cta<BN, A_MN, B_MN, EpiStore>(maps, sh, ep, sms, 0);
     return launch_gemm<BN, A_MN, B_MN, EpiStore>(maps, sh, ep, sms, 0);
 }
 
 int main(int argc, char** argv) {
     if (argc < 9) {
-        printf("usage: %s M N K G a_mn b_mn BN nseg\n", argv[0]);
+        printf("usage: %s M N K G a_mn b_mn BN nseg [cta_group]\n", argv[0]);
         return 1;
     }
     const int M = atoi(argv[1]), N = atoi(argv[2]), K = atoi(argv[3]), G = atoi(argv[4]);
     const int a_mn = atoi(argv[5]), b_mn = atoi(argv[6]), BN = atoi(argv[7]), nseg = atoi(argv[8]);
+    g_cg = argc > 9 ? atoi(argv[9]) : 1;
     const int ldA = a_mn ? ((M + 3) & ~3) : ((K + 3) & ~3);
     const int ldB = b_mn ? ((N + 3) & ~3) : ((K + 3) & ~3);
     const size_t szA = (size_t)(a_mn ? K : M) * ldA, szB = (size_t)(b_mn ? K : N) * ldB;
@@ -75,7 +79,7 @@ int main(int argc, char** argv) {
         Operand oa{dA[s], M, K, G, ldA, (int64_t)szA, a_mn != 0};
         Operand ob{dB[s], N, K, G, ldB, (int64_t)szB, b_mn != 0};
         bool a1 = false, b1 = false;
-        if (make_operand_map(&maps.a[s], oa, 128, &a1, &err) || make_operand_map(&maps.b[s], ob, BN, &b1, &err)) {
+        if (make_operand_map(&maps.a[s], oa, 128, &a1, &err) || make_operand_map(&maps.b[s], ob, g_cg == 2 ? BN / 2 : BN, &b1, &err)) {
             printf("tensor map error: %s\n", err ? err : "?");
             return 2;
         }
@@ -129,7 +133,7 @@ int main(int argc, char** argv) {
                 if (fabs(acc) > max_ref) max_ref = fabs(acc);
             }
     const double flops = 2.0 * M * N * (double)K * G * nseg;
-    printf("M=%d N=%d K=%d G=%d a_mn=%d b_mn=%d BN=%d nseg=%d : max_err=%.3e (max |ref| %.3e) bad=%lld  %.3f ms  %.1f TFLOP/s  %s\n",
-           M, N, K, G, a_mn, b_mn, BN, nseg, max_err, max_ref, bad, ms, flops / ms * 1e-9, bad == 0 ? "PASS" : "FAIL");
+    printf("cg=%d M=%d N=%d K=%d G=%d a_mn=%d b_mn=%d BN=%d nseg=%d : max_err=%.3e (max |ref| %.3e) bad=%lld  %.3f ms  %.1f TFLOP/s  %s\n",
+           g_cg, M, N, K, G, a_mn, b_mn, BN, nseg, max_err, max_ref, bad, ms, flops / ms * 1e-9, bad == 0 ? "PASS" : "FAIL");
     return bad == 0 ? 0 : 3;
 }

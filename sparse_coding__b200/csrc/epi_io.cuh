@@ -1,0 +1,63 @@
+// Coalesced global I/O for epilogue warps.  A thread of the epilogue owns one accumulator ROW, so
+// touching global memory directly costs one 128-byte line per lane per instruction (32 L1 wavefronts
+// for 512 bytes).  Instead every epilogue warp owns a few 4 KB staging tiles in shared memory -
+// [32 rows][32 fp32], 128-byte swizzled exactly as TMA's SWIZZLE_128B lays them out - and moves whole
+// tiles with TMA: tile loads complete on the warp's own mbarrier, tile stores are bulk-async groups.
+// Row reads / writes of the swizzled tile are bank-conflict free (a quarter warp covers all 32 banks).
+#pragma once
+#include "sm100_ptx.cuh"
+
+namespace sc {
+
+constexpr int kIoTileBytes = 32 * 32 * 4;
+
+struct EpiIo {
+    uint8_t* buf;     // this warp's staging tiles (Epi::kIoBufs x 4 KB, 1024-byte aligned)
+    uint64_t* bar;    // this warp's mbarrier for tile loads
+    uint32_t* phase;  // parity of the next completion on `bar` (lives across tiles)
+};
+
+// element (r, c) of a staging tile sits at r*128 + ((c/4) ^ (r & 7))*16 + (c % 4)*4
+SC_DEVICE void io_read_row(const uint8_t* tile, int r, float (&v)[32]) {
+    const uint8_t* row = tile + r * 128;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const float4 t = *reinterpret_cast<const float4*>(row + ((j ^ (r & 7)) << 4));
+        v[4 * j] = t.x; v[4 * j + 1] = t.y; v[4 * j + 2] = t.z; v[4 * j + 3] = t.w;
+    }
+}
+SC_DEVICE void io_write_row(uint8_t* tile, int r, const float (&v)[32]) {
+    uint8_t* row = tile + r * 128;
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+        *reinterpret_cast<float4*>(row + ((j ^ (r & 7)) << 4)) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+}
+
+// Whole warp.  Make the rows just written visible to the async proxy, then lane 0 stores the tile.
+// The caller commits the group (io_commit) once all tiles of the step are issued.
+SC_DEVICE void io_store_tile(const CUtensorMap* map, const uint8_t* tile, int col, int row, int g) {
+    fence_proxy_async_smem();
+    __syncwarp();
+    if ((threadIdx.x & 31) == 0) tma_store_3d(map, tile, col, row, g);
+}
+SC_DEVICE void io_commit() {
+    if ((threadIdx.x & 31) == 0) tma_store_commit();
+}
+// Whole warp.  The staging tiles may be overwritten once earlier stores have READ them.
+SC_DEVICE void io_wait_stores_read() {
+    if ((threadIdx.x & 31) == 0) tma_store_wait_read<0>();
+    __syncwarp();
+}
+// Whole warp, before kernel exit: the stores themselves must be complete.
+SC_DEVICE void io_wait_stores_done() {
+    if ((threadIdx.x & 31) == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    __syncwarp();
+}
+// Lane 0 arms the warp's barrier for `bytes` and the caller (lane 0) issues the tile loads.
+SC_DEVICE void io_expect(const EpiIo& io, uint32_t bytes) { mbar_arrive_expect_tx(io.bar, bytes); }
+SC_DEVICE void io_wait_loads(const EpiIo& io) {
+    mbar_wait(io.bar, *io.phase);
+    *io.phase ^= 1;
+}
+
+}  // namespace sc

@@ -38,7 +38,8 @@ struct EpiStore {
     };
     const Params& p;
     const RowCtx c;
-    SC_DEVICE EpiStore(const Params& p_, const RowCtx& c_) : p(p_), c(c_) {}
+    static constexpr int kIoBufs = 0;
+    SC_DEVICE EpiStore(const Params& p_, const RowCtx& c_, const EpiIo&) : p(p_), c(c_) {}
     SC_DEVICE void prefetch(int) {}
     SC_DEVICE void chunk(int co, float (&v)[32], int /*next_co*/) {
         if (c.row >= c.M) return;

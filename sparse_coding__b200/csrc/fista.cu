@@ -42,7 +42,8 @@ struct EpiFistaRes {
     };
     const Params& p;
     const RowCtx c;
-    SC_DEVICE EpiFistaRes(const Params& p_, const RowCtx& c_) : p(p_), c(c_) {}
+    static constexpr int kIoBufs = 0;
+    SC_DEVICE EpiFistaRes(const Params& p_, const RowCtx& c_, const EpiIo&) : p(p_), c(c_) {}
     SC_DEVICE void prefetch(int) {}
     SC_DEVICE void chunk(int co, float (&v)[32], int /*next_co*/) {
         const int col = c.col0 + co;
@@ -79,7 +80,8 @@ struct EpiFistaStep {
     const Params& p;
     const RowCtx c;
     float eta, thr;
-    SC_DEVICE EpiFistaStep(const Params& p_, const RowCtx& c_) : p(p_), c(c_) {
+    static constexpr int kIoBufs = 0;
+    SC_DEVICE EpiFistaStep(const Params& p_, const RowCtx& c_, const EpiIo&) : p(p_), c(c_) {
         eta = *p.eta;
         thr = eta * p.l1;
     }

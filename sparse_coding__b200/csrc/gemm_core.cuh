@@ -19,6 +19,7 @@
 // Group (member) index g lets one launch cover every SAE of the ensemble; an operand that all
 // members share (the activation batch) has gmul = 0 and is fetched from the same address by all.
 #pragma once
+#include "epi_io.cuh"
 #include "sm100_ptx.cuh"
 
 namespace sc {
@@ -47,16 +48,20 @@ struct GemmShape {
                 // the launch; groups are then laid out as [problem][member]
 };
 
-template <int BN>
+constexpr int kEpiWarps = 4 * 2;  // 4 row quarters x kEpiHalves
+
+template <int BN, int IO = 0>
 struct GemmCfg {
     static constexpr int kBTileBytes = BN * kBlockK * 4;
     static constexpr int kStageBytes = kATileBytes + kBTileBytes;
-    static constexpr int kStagesRaw = (227 * 1024 - 2048) / kStageBytes;
+    static constexpr int kIoBytes = kEpiWarps * IO * kIoTileBytes;  // epilogue staging tiles (epi_io.cuh)
+    static constexpr int kStagesRaw = (227 * 1024 - 2048 - kIoBytes) / kStageBytes;
     static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
     static constexpr int kTmemCols = (2 * BN <= 32) ? 32 : (2 * BN <= 64) ? 64 : (2 * BN <= 128) ? 128 : (2 * BN <= 256) ? 256 : 512;
-    static constexpr int kBarrierBytes = (2 * kStages + 4) * 8 + 16;
-    static constexpr int kSmemBytes = kStages * kStageBytes + kBarrierBytes + 1024;  // + alignment slack
+    static constexpr int kBarrierBytes = (2 * kStages + 4 + kEpiWarps) * 8 + 16;
+    static constexpr int kSmemBytes = kStages * kStageBytes + kIoBytes + kBarrierBytes + 1024;  // + alignment slack
     static_assert(BN % 32 == 0 && BN >= 32 && BN <= 256, "BN must be a multiple of 32 in [32,256]");
+    static_assert(kStages >= 2, "not enough shared memory left for the operand pipeline");
 };
 
 // Context handed to an epilogue functor for one accumulator row of one tile.
@@ -73,19 +78,49 @@ struct RowCtx {
     int part;    // warp_q + 4*half: slot for per-warp partial results (0..4*kEpiHalves-1)
 };
 
+// One accumulator tile through an epilogue functor (shared by the single-CTA and the CTA-pair kernels).
+//   Epi(params, ctx, io); prefetch(col); chunk(col, v[32], next_col or -1); finish()
+// `release` signals the MMA warp that the TMEM stage may be overwritten (differs between the variants).
+template <int BN, class Epi, class Release>
+SC_DEVICE void epilogue_tile(const typename Epi::Params& ep, const RowCtx& ctx, const EpiIo& io, uint64_t* full_bar,
+                             uint32_t parity, uint32_t taddr, Release release) {
+    Epi epi(ep, ctx, io);
+    constexpr int kChunks = (BN / 32 + kEpiHalves - 1) / kEpiHalves;
+    // global loads the functor needs for its first chunk do not depend on the accumulator: issue them
+    // before waiting for the MMAs, and the next chunk's while the current one is processed
+    if (ctx.half < BN / 32) epi.prefetch(ctx.half * 32);
+    mbar_wait(full_bar, parity);
+    tc_fence_after();
+#pragma unroll 1  // keep the (large) functor body in the instruction cache
+    for (int i = 0; i < kChunks; ++i) {
+        const int c = ctx.half + i * kEpiHalves;
+        if (c < BN / 32) {
+            float v[32];
+            tmem_ld32(taddr + c * 32, v);
+            tmem_ld_wait();
+            epi.chunk(c * 32, v, (c + kEpiHalves < BN / 32) ? (c + kEpiHalves) * 32 : -1);
+        }
+    }
+    tc_fence_before();
+    release();
+    epi.finish();
+}
+
 template <int BN, bool A_MN, bool B_MN, class Epi>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tf32_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
                  const __grid_constant__ typename Epi::Params ep) {
-    using Cfg = GemmCfg<BN>;
+    using Cfg = GemmCfg<BN, Epi::kIoBufs>;
     constexpr int kStages = Cfg::kStages;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kStages * Cfg::kStageBytes);
+    uint8_t* io_smem = smem + kStages * Cfg::kStageBytes;
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(io_smem + Cfg::kIoBytes);
     uint64_t* empty_bar = full_bar + kStages;
     uint64_t* tmem_full = empty_bar + kStages;
     uint64_t* tmem_empty = tmem_full + 2;
-    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+    uint64_t* io_bar = tmem_empty + 2;
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(io_bar + kEpiWarps);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -105,6 +140,7 @@ gemm_tf32_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
             mbar_init(&tmem_full[i], 1);
             mbar_init(&tmem_empty[i], 128 * kEpiHalves);
         }
+        for (int i = 0; i < kEpiWarps; ++i) mbar_init(&io_bar[i], 1);
         fence_mbar_init();
     }
     if (warp == 2) {
@@ -212,6 +248,8 @@ gemm_tf32_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
         // ------------------------------------------------------------------ epilogue
         const int q = warp & 3;
         const int half = (warp - 4) >> 2;
+        uint32_t io_phase = 0;
+        EpiIo io{io_smem + (warp - 4) * (Epi::kIoBufs * kIoTileBytes), &io_bar[warp - 4], &io_phase};
         int it = 0;
         for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
             const int gg = tile / tiles_per_group;
@@ -225,28 +263,10 @@ gemm_tf32_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
             RowCtx ctx;
             ctx.g = g; ctx.row = tm * kBlockM + q * 32 + lane; ctx.col0 = tn * BN;
             ctx.M = shape.M; ctx.N = shape.N; ctx.tile_m = tm; ctx.tile_n = tn; ctx.tiles_m = shape.tiles_m; ctx.tiles_n = shape.tiles_n; ctx.warp_q = q; ctx.prob = prob; ctx.half = half; ctx.part = q + 4 * half;
-            Epi epi(ep, ctx);
-            constexpr int kChunks = (BN / 32 + kEpiHalves - 1) / kEpiHalves;
-            // global loads the functor needs for its first chunk do not depend on the accumulator: issue them
-            // before waiting for the MMAs, and the next chunk's while the current one is processed
-            if (half < BN / 32) epi.prefetch(half * 32);
-            mbar_wait(&tmem_full[as], aph);
-            tc_fence_after();
             const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
-#pragma unroll 1  // keep the (large) functor body in the instruction cache
-            for (int i = 0; i < kChunks; ++i) {
-                const int c = half + i * kEpiHalves;
-                if (c < BN / 32) {
-                    float v[32];
-                    tmem_ld32(taddr + c * 32, v);
-                    tmem_ld_wait();
-                    epi.chunk(c * 32, v, (c + kEpiHalves < BN / 32) ? (c + kEpiHalves) * 32 : -1);
-                }
-            }
-            tc_fence_before();
-            mbar_arrive(&tmem_empty[as]);
-            epi.finish();
+            epilogue_tile<BN, Epi>(ep, ctx, io, &tmem_full[as], aph, taddr, [&] { mbar_arrive(&tmem_empty[as]); });
         }
+        if (Epi::kIoBufs > 0) io_wait_stores_done();
     }
 
     tc_fence_before();
@@ -261,7 +281,7 @@ gemm_tf32_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
 template <int BN, bool A_MN, bool B_MN, class Epi>
 cudaError_t launch_gemm(const GemmMaps& maps, GemmShape shape, const typename Epi::Params& ep, int num_sms,
                         cudaStream_t stream) {
-    using Cfg = GemmCfg<BN>;
+    using Cfg = GemmCfg<BN, Epi::kIoBufs>;
     auto kern = gemm_tf32_kernel<BN, A_MN, B_MN, Epi>;
     static bool attr_set[64] = {};  // per template instantiation, per device
     int dev = 0;

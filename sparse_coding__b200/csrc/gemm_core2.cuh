@@ -19,33 +19,37 @@
 
 namespace sc {
 
-template <int BN>
+template <int BN, int IO = 0>
 struct GemmCfg2 {
     static constexpr int kBHalf = BN / 2;
     static constexpr int kBTileBytes = kBHalf * kBlockK * 4;
     static constexpr int kStageBytes = kATileBytes + kBTileBytes;
-    static constexpr int kStagesRaw = (227 * 1024 - 2048) / kStageBytes;
+    static constexpr int kIoBytes = kEpiWarps * IO * kIoTileBytes;
+    static constexpr int kStagesRaw = (227 * 1024 - 2048 - kIoBytes) / kStageBytes;
     static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
     static constexpr int kTmemCols = GemmCfg<BN>::kTmemCols;
-    static constexpr int kBarrierBytes = (2 * kStages + 4) * 8 + 16;
-    static constexpr int kSmemBytes = kStages * kStageBytes + kBarrierBytes + 1024;
+    static constexpr int kBarrierBytes = (2 * kStages + 4 + kEpiWarps) * 8 + 16;
+    static constexpr int kSmemBytes = kStages * kStageBytes + kIoBytes + kBarrierBytes + 1024;
     static_assert(BN % 64 == 0 && BN >= 64 && BN <= 256, "paired kernel: BN multiple of 64 in [64,256]");
+    static_assert(kStages >= 2, "not enough shared memory left for the operand pipeline");
 };
 
 template <int BN, bool A_MN, bool B_MN, class Epi>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
                       const __grid_constant__ typename Epi::Params ep) {
-    using Cfg = GemmCfg2<BN>;
+    using Cfg = GemmCfg2<BN, Epi::kIoBufs>;
     constexpr int kStages = Cfg::kStages;
     constexpr int kBHalf = Cfg::kBHalf;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kStages * Cfg::kStageBytes);
+    uint8_t* io_smem = smem + kStages * Cfg::kStageBytes;
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(io_smem + Cfg::kIoBytes);
     uint64_t* empty_bar = full_bar + kStages;
     uint64_t* tmem_full = empty_bar + kStages;
     uint64_t* tmem_empty = tmem_full + 2;
-    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+    uint64_t* io_bar = tmem_empty + 2;
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(io_bar + kEpiWarps);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -68,6 +72,7 @@ gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape sha
             mbar_init(&tmem_full[i], 1);
             mbar_init(&tmem_empty[i], 2 * 128 * kEpiHalves);  // epilogue threads of BOTH CTAs (leader's copy is used)
         }
+        for (int i = 0; i < kEpiWarps; ++i) mbar_init(&io_bar[i], 1);
         fence_mbar_init();
     }
     if (warp == 2) {
@@ -176,6 +181,8 @@ gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape sha
         // ------------------------------------------------------------------ epilogue (both CTAs, own 128 rows)
         const int q = warp & 3;
         const int half = (warp - 4) >> 2;
+        uint32_t io_phase = 0;
+        EpiIo io{io_smem + (warp - 4) * (Epi::kIoBufs * kIoTileBytes), &io_bar[warp - 4], &io_phase};
         int it = 0;
         for (int tile = cluster_id; tile < total_tiles; tile += num_clusters, ++it) {
             const int gg = tile / tiles_per_group;
@@ -192,27 +199,13 @@ gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape sha
             // partial-sum slots are indexed by 128-row tile: report this CTA's half as its own row tile
             ctx.tile_m = tm * 2 + rank; ctx.tile_n = tn; ctx.tiles_m = shape.tiles_m * 2; ctx.tiles_n = shape.tiles_n;
             ctx.warp_q = q; ctx.prob = prob; ctx.half = half; ctx.part = q + 4 * half;
-            Epi epi(ep, ctx);
-            constexpr int kChunks = (BN / 32 + kEpiHalves - 1) / kEpiHalves;
-            if (half < BN / 32) epi.prefetch(half * 32);
-            mbar_wait(&tmem_full[as], aph);
-            tc_fence_after();
             const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
-#pragma unroll 1
-            for (int i = 0; i < kChunks; ++i) {
-                const int c = half + i * kEpiHalves;
-                if (c < BN / 32) {
-                    float v[32];
-                    tmem_ld32(taddr + c * 32, v);
-                    tmem_ld_wait();
-                    epi.chunk(c * 32, v, (c + kEpiHalves < BN / 32) ? (c + kEpiHalves) * 32 : -1);
-                }
-            }
-            tc_fence_before();
-            if (leader) mbar_arrive(&tmem_empty[as]);
-            else mbar_arrive_remote(&tmem_empty[as], 0);
-            epi.finish();
+            epilogue_tile<BN, Epi>(ep, ctx, io, &tmem_full[as], aph, taddr, [&] {
+                if (leader) mbar_arrive(&tmem_empty[as]);
+                else mbar_arrive_remote(&tmem_empty[as], 0);
+            });
         }
+        if (Epi::kIoBufs > 0) io_wait_stores_done();
     }
 
     tc_fence_before();
@@ -227,7 +220,7 @@ gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape sha
 template <int BN, bool A_MN, bool B_MN, class Epi>
 cudaError_t launch_gemm_2cta(const GemmMaps& maps, GemmShape shape, const typename Epi::Params& ep, int num_sms,
                              cudaStream_t stream) {
-    using Cfg = GemmCfg2<BN>;
+    using Cfg = GemmCfg2<BN, Epi::kIoBufs>;
     auto kern = gemm_tf32_2cta_kernel<BN, A_MN, B_MN, Epi>;
     static bool attr_set[64] = {};
     int dev = 0;

@@ -38,7 +38,8 @@ struct EpiEncodeT {
     const Params& p;
     const RowCtx c;
     float bn, cnt, m1, m2, m3, m4;
-    SC_DEVICE EpiEncodeT(const Params& p_, const RowCtx& c_) : p(p_), c(c_), cnt(0.f), m1(0.f), m2(0.f), m3(0.f), m4(0.f) {
+    static constexpr int kIoBufs = 0;
+    SC_DEVICE EpiEncodeT(const Params& p_, const RowCtx& c_, const EpiIo&) : p(p_), c(c_), cnt(0.f), m1(0.f), m2(0.f), m3(0.f), m4(0.f) {
         bn = (p.bias && c.row < c.M) ? p.bias[(long long)c.g * p.feats + c.row] : 0.f;
     }
     SC_DEVICE void prefetch(int) {}
@@ -160,7 +161,13 @@ static int encode_impl(const ScEncodeArgs& a) {
         SC_TRY((run_gemm<false, false, EpiEncodeT>(N, B, G, &s, 1, ep, st)));
     } else {
         Seg s{kmajor(x_r, B, d, xg, Bd), kmajor(W_r, N, d, G, Nd)};
-        EpiEncode::Params ep{a.bias, a.out_c, nullptr, BN_, 0};
+        EpiEncode::Params ep{};
+        {
+            const char* err = nullptr;
+            const int rc = make_io_map(&ep.c_map, a.out_c, B, N, G, BN_, &err);
+            if (rc != 0) return fail(rc, "%s", err ? err : "io tensor map creation failed");
+        }
+        ep.bias = a.bias; ep.l1_part = nullptr; ep.signed_zero = 0;
         SC_TRY((run_gemm<false, false, EpiEncode>(B, N, G, &s, 1, ep, st)));
     }
     return 0;

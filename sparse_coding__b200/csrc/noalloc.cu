@@ -76,7 +76,13 @@ static int encode_noalloc_impl(const float* x, const float* W, const float* bias
         reinterpret_cast<const float4*>(W), reinterpret_cast<float4*>(W_r), w4);
     SC_CUDA(cudaGetLastError(), "round_copy launch");
     Seg s{kmajor(x_r, B, d, 1, 0), kmajor(W_r, N, d, 1, 0)};
-    EpiEncode::Params ep{bias, out_c, nullptr, (long long)B * N, 0};
+    EpiEncode::Params ep{};
+    {
+        const char* err = nullptr;
+        const int rc = make_io_map(&ep.c_map, out_c, B, N, 1, (long long)B * N, &err);
+        if (rc != 0) return fail(rc, "%s", err ? err : "io tensor map creation failed");
+    }
+    ep.bias = bias; ep.l1_part = nullptr; ep.signed_zero = 0;
     return run_gemm<false, false, EpiEncode>(B, N, 1, &s, 1, ep, st);
 }
 

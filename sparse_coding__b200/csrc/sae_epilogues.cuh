@@ -6,6 +6,7 @@
 // Every tensor an epilogue writes for a later GEMM is rounded to TF32 (round to nearest) here, so
 // the tensor core's truncation of the low 13 mantissa bits never sees a non-zero bit.
 #pragma once
+#include "epi_io.cuh"
 #include "epi_store.cuh"
 
 namespace sc {
@@ -23,32 +24,37 @@ SC_DEVICE float warp_sum(float v) {
 //   Also emits the per-warp partial sums of sum(c) for the L1 term (sae_ensemble.py:63).
 // ---------------------------------------------------------------------------------------------
 struct EpiEncode {
-    struct Params {
+    static constexpr int kIoBufs = 1;  // one staging tile per warp: c leaves through TMA, fully coalesced
+    struct alignas(64) Params {
+        CUtensorMap c_map;  // io map of c [G][B][N]
         const float* bias;  // [G][N] or nullptr
-        float* c;           // [G][B][N]
-        float* l1_part;     // [G][tiles*4] or nullptr
-        long long c_gstride;
+        float* l1_part;     // [G][tiles*8] or nullptr
         int signed_zero;    // 1 (training): TF32-rounded, z<0 -> -0.0f; 0 (inference API): plain fp32 relu
     };
     const Params& p;
     const RowCtx c;
+    const EpiIo io;
     float sum;
-    SC_DEVICE EpiEncode(const Params& p_, const RowCtx& c_) : p(p_), c(c_), sum(0.f) {}
+    SC_DEVICE EpiEncode(const Params& p_, const RowCtx& c_, const EpiIo& io_) : p(p_), c(c_), io(io_), sum(0.f) {}
     SC_DEVICE void prefetch(int) {}
     SC_DEVICE void chunk(int co, float (&v)[32], int /*next_co*/) {
         const int col = c.col0 + co;
-        if (c.row >= c.M || col >= c.N) return;
-        const int ncols = c.N - col;
+        const int ncols = c.N - col;  // may be <= 0 on a ragged tile: the TMA store clips
+        const int lane = threadIdx.x & 31;
         float bv[32];
-        if (p.bias) load_row32(p.bias + (long long)c.g * c.N + col, bv, ncols);
+        if (p.bias && ncols > 0) load_row32(p.bias + (long long)c.g * c.N + col, bv, ncols);
         const float neg = p.signed_zero ? -0.0f : 0.0f;
+        const bool row_ok = c.row < c.M;
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
-            const float z = p.bias ? v[j] + bv[j] : v[j];
-            if (j < ncols) sum += fmaxf(z, 0.f);
+            const float z = (p.bias && ncols > 0) ? v[j] + bv[j] : v[j];
+            if (row_ok && j < ncols) sum += fmaxf(z, 0.f);
             v[j] = (z >= 0.f) ? (p.signed_zero ? rn_tf32(z) : z) : neg;
         }
-        store_row32(p.c + c.g * p.c_gstride + (long long)c.row * c.N + col, v, ncols);
+        io_wait_stores_read();  // the previous chunk's store has read the staging tile
+        io_write_row(io.buf, lane, v);
+        io_store_tile(&p.c_map, io.buf, col, c.row - lane, c.g);
+        io_commit();
     }
     SC_DEVICE void finish() {
         if (!p.l1_part) return;
@@ -77,7 +83,8 @@ struct EpiDecode {
     const Params& p;
     const RowCtx c;
     float sum;
-    SC_DEVICE EpiDecode(const Params& p_, const RowCtx& c_) : p(p_), c(c_), sum(0.f) {}
+    static constexpr int kIoBufs = 0;
+    SC_DEVICE EpiDecode(const Params& p_, const RowCtx& c_, const EpiIo&) : p(p_), c(c_), sum(0.f) {}
     SC_DEVICE void prefetch(int) {}
     SC_DEVICE void chunk(int co, float (&v)[32], int /*next_co*/) {
         const int col = c.col0 + co;
@@ -132,7 +139,8 @@ struct EpiBackCode {
     const RowCtx c;
     float db, s, l1_over_B, bn;
     float nxt[32];  // c values of the chunk after the current one, loads in flight
-    SC_DEVICE EpiBackCode(const Params& p_, const RowCtx& c_) : p(p_), c(c_), db(0.f), s(0.f) {
+    static constexpr int kIoBufs = 0;
+    SC_DEVICE EpiBackCode(const Params& p_, const RowCtx& c_, const EpiIo&) : p(p_), c(c_), db(0.f), s(0.f) {
         l1_over_B = p.l1[c.g] * p.inv_B;
         bn = (p.tied && c.row < c.M) ? p.bias[(long long)c.g * p.feats + c.row] : 0.f;
     }
@@ -214,25 +222,28 @@ SC_DEVICE void adam_update(float& p, float& mu, float& nu, float g, const AdamCo
 }
 
 struct EpiAdam {
-    struct Sub {
-        float *p, *mu, *nu;     // [G][N][d]
-        const float* s_part;    // [G][parts][N] (projected only)
-        const float* inv_norm;  // [G][N]  1/max(||W_n||,1e-8), negative when the clamp is active
-        float* grad_out;        // optional [G][N][d]: write the gradient instead of applying Adam (data parallel)
+    static constexpr int kIoBufs = 3;  // p, mu, nu tiles staged per warp; loaded and stored by TMA
+    struct alignas(64) Sub {
+        CUtensorMap p_map, mu_map, nu_map;  // io maps of [G][N][d]
+        CUtensorMap grad_map;               // io map of the gradient output (gradient-only mode)
+        const float* s_part;                // [G][parts][N] (projected only)
+        const float* inv_norm;              // [G][N]  1/max(||W_n||,1e-8), negative when the clamp is active
         int projected;
+        int grad_only;
     };
-    struct Params {
-        Sub sub[2];             // one per batched problem (untied: [0] encoder, [1] decoder)
-        long long gstride;      // N*d
-        int tiles_b;            // partial slots per feature in s_part
+    struct alignas(64) Params {
+        Sub sub[2];   // one per batched problem (untied: [0] encoder, [1] decoder)
+        int tiles_b;  // partial slots per feature in s_part
         AdamConst a;
     };
     const Params& p;
     const Sub& u;
     const RowCtx c;
+    const EpiIo io;
     float s, inv;
     bool clamped;
-    SC_DEVICE EpiAdam(const Params& p_, const RowCtx& c_) : p(p_), u(p_.sub[c_.prob]), c(c_), s(0.f), inv(1.f), clamped(false) {
+    SC_DEVICE EpiAdam(const Params& p_, const RowCtx& c_, const EpiIo& io_)
+        : p(p_), u(p_.sub[c_.prob]), c(c_), io(io_), s(0.f), inv(1.f), clamped(false) {
         if (u.projected && c.row < c.M) {
             for (int t = 0; t < p.tiles_b; ++t) s += u.s_part[((long long)c.g * p.tiles_b + t) * c.M + c.row];
             const float iv = u.inv_norm[(long long)c.g * c.M + c.row];
@@ -240,30 +251,56 @@ struct EpiAdam {
             inv = fabsf(iv);
         }
     }
-    SC_DEVICE void prefetch(int) {}
-    SC_DEVICE void chunk(int co, float (&v)[32], int /*next_co*/) {
-        const int col = c.col0 + co;
-        if (c.row >= c.M || col >= c.N) return;
-        const int ncols = c.N - col;
-        const long long off = c.g * p.gstride + (long long)c.row * c.N + col;
+    // tile loads for the chunk at tile column `co` (whole warp calls; lane 0 issues)
+    SC_DEVICE void prefetch(int co) {
+        io_wait_stores_read();  // staging tiles are free once the previous stores have read them
+        if ((threadIdx.x & 31) == 0) {
+            const int col = c.col0 + co, row0 = c.row;  // lane 0 owns the warp's first row
+            uint8_t* b = io.buf;
+            if (u.grad_only) {
+                io_expect(io, kIoTileBytes);
+                tma_load_3d(&u.p_map, io.bar, b, col, row0, c.g);
+            } else {
+                io_expect(io, 3 * kIoTileBytes);
+                tma_load_3d(&u.p_map, io.bar, b, col, row0, c.g);
+                tma_load_3d(&u.mu_map, io.bar, b + kIoTileBytes, col, row0, c.g);
+                tma_load_3d(&u.nu_map, io.bar, b + 2 * kIoTileBytes, col, row0, c.g);
+            }
+        }
+    }
+    SC_DEVICE void chunk(int co, float (&v)[32], int next_co) {
+        const int lane = threadIdx.x & 31;
+        const int col = c.col0 + co, row0 = c.row - lane;
+        uint8_t* b = io.buf;
+        io_wait_loads(io);
         float pv[32];
-        load_row32(u.p + off, pv, ncols);
+        io_read_row(b, lane, pv);
         if (u.projected) {
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] = clamped ? v[j] * inv : (v[j] - s * (pv[j] * inv)) * inv;
         }
-        if (u.grad_out) {
-            store_row32(u.grad_out + off, v, ncols);
-            return;
-        }
-        float mv[32], nv[32];
-        load_row32(u.mu + off, mv, ncols);
-        load_row32(u.nu + off, nv, ncols);
+        if (u.grad_only) {
+            io_write_row(b, lane, v);
+            io_store_tile(&u.grad_map, b, col, row0, c.g);
+        } else {
+            float mv[32], nv[32];
+            io_read_row(b + kIoTileBytes, lane, mv);
+            io_read_row(b + 2 * kIoTileBytes, lane, nv);
 #pragma unroll
-        for (int j = 0; j < 32; ++j) adam_update(pv[j], mv[j], nv[j], v[j], p.a);
-        store_row32(u.p + off, pv, ncols);
-        store_row32(u.mu + off, mv, ncols);
-        store_row32(u.nu + off, nv, ncols);
+            for (int j = 0; j < 32; ++j) adam_update(pv[j], mv[j], nv[j], v[j], p.a);
+            io_write_row(b, lane, pv);
+            io_write_row(b + kIoTileBytes, lane, mv);
+            io_write_row(b + 2 * kIoTileBytes, lane, nv);
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+                tma_store_3d(&u.p_map, b, col, row0, c.g);
+                tma_store_3d(&u.mu_map, b + kIoTileBytes, col, row0, c.g);
+                tma_store_3d(&u.nu_map, b + 2 * kIoTileBytes, col, row0, c.g);
+            }
+        }
+        io_commit();
+        if (next_co >= 0) prefetch(next_co);
     }
     SC_DEVICE void finish() {}
 };

@@ -203,6 +203,13 @@ static AdamConst make_adam(const ScAdam& a) {
     return k;
 }
 
+static int io_map(CUtensorMap* out, const float* base, long long rows, long long cols, long long g, long long gstride) {
+    const char* err = nullptr;
+    const int rc = make_io_map(out, base, rows, cols, g, gstride, &err);
+    if (rc != 0) return fail(rc, "%s", err ? err : "io tensor map creation failed");
+    return 0;
+}
+
 static int check_ptr(const void* p, const char* name) {
     if (!p) return fail(-1, "%s is NULL", name);
     if (reinterpret_cast<uintptr_t>(p) & 15) return fail(-1, "%s is not 16-byte aligned", name);
@@ -253,7 +260,9 @@ static int sae_step_impl(const ScStepArgs& a) {
     // 3. G1: c = relu(x W_e^T + b)                                  [B x N], K = d
     {
         Seg s{kmajor(w.x_r, B, d, xg, Bd), kmajor(a.tied ? w.D_r : w.enc_r, N, d, M, Nd)};
-        EpiEncode::Params ep{a.bias, a.out_c, w.l1_part, BN_, 1};
+        EpiEncode::Params ep{};
+        SC_TRY(io_map(&ep.c_map, a.out_c, B, N, M, BN_));
+        ep.bias = a.bias; ep.l1_part = w.l1_part; ep.signed_zero = 1;
         SC_TRY((run_gemm<false, false, EpiEncode>(B, N, M, &s, 1, ep, st)));
     }
     prof_mark(st, "G1_encode");
@@ -273,23 +282,34 @@ static int sae_step_impl(const ScStepArgs& a) {
     }
     prof_mark(st, "G3_back_code");
     // 6/7. weight gradients with fused Adam                          [N x d], K = B
-    if (!a.tied) {
-        // one launch, two independent problems: dW_e = dz^T x (plain) and dW_d = c^T R (projected)
-        Seg s45[2] = {{mnmajor(w.dz, N, B, M, BN_), mnmajor(w.x_r, d, B, xg, Bd)},
-                      {mnmajor(a.out_c, N, B, M, BN_), mnmajor(w.R_r, d, B, M, Bd)}};
+    {
         EpiAdam::Params e{};
-        e.sub[0] = {a.enc, a.enc_mu, a.enc_nu, nullptr, nullptr, a.grad_enc, 0};
-        e.sub[1] = {a.dec, a.dec_mu, a.dec_nu, w.s_part, w.inv_norm, grad_mode ? a.grad_dec : nullptr, 1};
-        e.gstride = Nd; e.tiles_b = w.tiles_b; e.a = ad;
-        SC_TRY((run_gemm<true, true, EpiAdam>(N, d, M, s45, 2, e, st, /*segs_are_problems=*/true)));
-    } else {
-        Seg s[2] = {{mnmajor(a.out_c, N, B, M, BN_), mnmajor(w.R_r, d, B, M, Bd)},
-                    {mnmajor(w.dz, N, B, M, BN_), mnmajor(w.x_r, d, B, xg, Bd)}};
-        EpiAdam::Params e{};
-        e.sub[0] = {a.enc, a.enc_mu, a.enc_nu, w.s_part, w.inv_norm, a.grad_enc, 1};
-        e.sub[1] = e.sub[0];
-        e.gstride = Nd; e.tiles_b = w.tiles_b; e.a = ad;
-        SC_TRY((run_gemm<true, true, EpiAdam>(N, d, M, s, 2, e, st)));
+        e.tiles_b = w.tiles_b; e.a = ad;
+        auto fill = [&](EpiAdam::Sub& u, float* p, float* mu, float* nu, float* grad, bool projected) -> int {
+            SC_TRY(io_map(&u.p_map, p, N, d, M, Nd));
+            SC_TRY(io_map(&u.mu_map, mu, N, d, M, Nd));
+            SC_TRY(io_map(&u.nu_map, nu, N, d, M, Nd));
+            SC_TRY(io_map(&u.grad_map, grad ? grad : p, N, d, M, Nd));
+            u.s_part = projected ? w.s_part : nullptr;
+            u.inv_norm = projected ? w.inv_norm : nullptr;
+            u.projected = projected ? 1 : 0;
+            u.grad_only = grad ? 1 : 0;
+            return 0;
+        };
+        if (!a.tied) {
+            // one launch, two independent problems: dW_e = dz^T x (plain) and dW_d = c^T R (projected)
+            Seg s45[2] = {{mnmajor(w.dz, N, B, M, BN_), mnmajor(w.x_r, d, B, xg, Bd)},
+                          {mnmajor(a.out_c, N, B, M, BN_), mnmajor(w.R_r, d, B, M, Bd)}};
+            SC_TRY(fill(e.sub[0], a.enc, a.enc_mu, a.enc_nu, a.grad_enc, false));
+            SC_TRY(fill(e.sub[1], a.dec, a.dec_mu, a.dec_nu, grad_mode ? a.grad_dec : nullptr, true));
+            SC_TRY((run_gemm<true, true, EpiAdam>(N, d, M, s45, 2, e, st, /*segs_are_problems=*/true)));
+        } else {
+            Seg s[2] = {{mnmajor(a.out_c, N, B, M, BN_), mnmajor(w.R_r, d, B, M, Bd)},
+                        {mnmajor(w.dz, N, B, M, BN_), mnmajor(w.x_r, d, B, xg, Bd)}};
+            SC_TRY(fill(e.sub[0], a.enc, a.enc_mu, a.enc_nu, a.grad_enc, true));
+            e.sub[1] = e.sub[0];
+            SC_TRY((run_gemm<true, true, EpiAdam>(N, d, M, s, 2, e, st)));
+        }
     }
     prof_mark(st, "G45_dW_adam");
     // 8. loss scalars + bias Adam

@@ -33,4 +33,8 @@ int make_operand_map(CUtensorMap* out, const Operand& op, int box_mn, bool* one_
 int make_rowmajor_map(CUtensorMap* out, const float* base, int64_t rows, int64_t cols, int64_t g, int64_t ld,
                       int64_t gstride, int box_rows, int box_cols, const char** err);
 
+// Row-major fp32 [G][rows][cols] map for the epilogue staging tiles: box {32 cols, 32 rows}, 128-byte swizzle.
+int make_io_map(CUtensorMap* out, const float* base, int64_t rows, int64_t cols, int64_t g, int64_t gstride,
+                const char** err);
+
 }  // namespace sc

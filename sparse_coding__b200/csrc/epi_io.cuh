@@ -13,8 +13,8 @@ constexpr int kIoTileBytes = 32 * 32 * 4;
 
 struct EpiIo {
     uint8_t* buf;     // this warp's staging tiles (Epi::kIoBufs x 4 KB, 1024-byte aligned)
-    uint64_t* bar;    // this warp's mbarrier for tile loads
-    uint32_t* phase;  // parity of the next completion on `bar` (lives across tiles)
+    uint64_t* bar;    // this warp's two mbarriers for tile loads (one per load slot)
+    uint32_t* phase;  // parity of the next completion on bar[0], bar[1] (lives across tiles)
 };
 
 // element (r, c) of a staging tile sits at r*128 + ((c/4) ^ (r & 7))*16 + (c % 4)*4
@@ -54,10 +54,12 @@ SC_DEVICE void io_wait_stores_done() {
     __syncwarp();
 }
 // Lane 0 arms the warp's barrier for `bytes` and the caller (lane 0) issues the tile loads.
-SC_DEVICE void io_expect(const EpiIo& io, uint32_t bytes) { mbar_arrive_expect_tx(io.bar, bytes); }
-SC_DEVICE void io_wait_loads(const EpiIo& io) {
-    mbar_wait(io.bar, *io.phase);
-    *io.phase ^= 1;
+SC_DEVICE void io_expect(const EpiIo& io, uint32_t bytes, int slot = 0) { mbar_arrive_expect_tx(io.bar + slot, bytes); }
+SC_DEVICE void io_wait_loads(const EpiIo& io, int slot = 0) {
+    mbar_wait(io.bar + slot, io.phase[slot]);
+    io.phase[slot] ^= 1;
 }
+// element (r, c) of a staging tile (see io_read_row)
+SC_DEVICE uint32_t io_elem_offset(int r, int c) { return r * 128 + (((c >> 2) ^ (r & 7)) << 4) + ((c & 3) << 2); }
 
 }  // namespace sc

@@ -58,7 +58,7 @@ struct GemmCfg {
     static constexpr int kStagesRaw = (227 * 1024 - 2048 - kIoBytes) / kStageBytes;
     static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
     static constexpr int kTmemCols = (2 * BN <= 32) ? 32 : (2 * BN <= 64) ? 64 : (2 * BN <= 128) ? 128 : (2 * BN <= 256) ? 256 : 512;
-    static constexpr int kBarrierBytes = (2 * kStages + 4 + kEpiWarps) * 8 + 16;
+    static constexpr int kBarrierBytes = (2 * kStages + 4 + 2 * kEpiWarps) * 8 + 16;
     static constexpr int kSmemBytes = kStages * kStageBytes + kIoBytes + kBarrierBytes + 1024;  // + alignment slack
     static_assert(BN % 32 == 0 && BN >= 32 && BN <= 256, "BN must be a multiple of 32 in [32,256]");
     static_assert(kStages >= 2, "not enough shared memory left for the operand pipeline");
@@ -120,7 +120,7 @@ gemm_tf32_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
     uint64_t* tmem_full = empty_bar + kStages;
     uint64_t* tmem_empty = tmem_full + 2;
     uint64_t* io_bar = tmem_empty + 2;
-    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(io_bar + kEpiWarps);
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(io_bar + 2 * kEpiWarps);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -140,7 +140,7 @@ gemm_tf32_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
             mbar_init(&tmem_full[i], 1);
             mbar_init(&tmem_empty[i], 128 * kEpiHalves);
         }
-        for (int i = 0; i < kEpiWarps; ++i) mbar_init(&io_bar[i], 1);
+        for (int i = 0; i < 2 * kEpiWarps; ++i) mbar_init(&io_bar[i], 1);
         fence_mbar_init();
     }
     if (warp == 2) {
@@ -248,8 +248,8 @@ gemm_tf32_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
         // ------------------------------------------------------------------ epilogue
         const int q = warp & 3;
         const int half = (warp - 4) >> 2;
-        uint32_t io_phase = 0;
-        EpiIo io{io_smem + (warp - 4) * (Epi::kIoBufs * kIoTileBytes), &io_bar[warp - 4], &io_phase};
+        uint32_t io_phase[2] = {0, 0};
+        EpiIo io{io_smem + (warp - 4) * (Epi::kIoBufs * kIoTileBytes), &io_bar[2 * (warp - 4)], io_phase};
         int it = 0;
         for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
             const int gg = tile / tiles_per_group;

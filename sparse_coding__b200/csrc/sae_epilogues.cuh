@@ -42,14 +42,23 @@ struct EpiEncode {
         const int ncols = c.N - col;  // may be <= 0 on a ragged tile: the TMA store clips
         const int lane = threadIdx.x & 31;
         float bv[32];
-        if (p.bias && ncols > 0) load_row32(p.bias + (long long)c.g * c.N + col, bv, ncols);
-        const float neg = p.signed_zero ? -0.0f : 0.0f;
-        const bool row_ok = c.row < c.M;
+        if (p.bias && ncols > 0) {
+            load_row32(p.bias + (long long)c.g * c.N + col, bv, ncols);
+        } else {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-            const float z = (p.bias && ncols > 0) ? v[j] + bv[j] : v[j];
-            if (row_ok && j < ncols) sum += fmaxf(z, 0.f);
-            v[j] = (z >= 0.f) ? (p.signed_zero ? rn_tf32(z) : z) : neg;
+            for (int j = 0; j < 32; ++j) bv[j] = 0.f;
+        }
+        const bool full = c.row < c.M && ncols >= 32;
+        if (p.signed_zero) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                const float z = v[j] + bv[j];
+                if (full || (c.row < c.M && j < ncols)) sum += fmaxf(z, 0.f);
+                v[j] = (z >= 0.f) ? rn_tf32(z) : -0.0f;
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j] + bv[j], 0.f);
         }
         io_wait_stores_read();  // the previous chunk's store has read the staging tile
         io_write_row(io.buf, lane, v);
@@ -150,8 +159,30 @@ struct EpiBackCode {
         const int col = c.col0 + co;
         const float* cp = p.c + c.g * p.cb_gstride + (long long)col * p.feats + c.row;
         const int nb = c.N - col;
+        if (nb >= 32) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) nxt[j] = (j < nb) ? __ldg(cp + (long long)j * p.feats) : 0.f;
+            for (int j = 0; j < 32; ++j) nxt[j] = __ldg(cp + (long long)j * p.feats);
+        } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) nxt[j] = (j < nb) ? __ldg(cp + (long long)j * p.feats) : 0.f;
+        }
+    }
+    // branch-free body, ~10 instructions per element; FULL = all 32 batch columns of the chunk exist
+    template <bool FULL, bool TIED>
+    SC_DEVICE void body(const float (&cvs)[32], const float (&v)[32], float* dp, int nb) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            if (FULL || j < nb) {
+                const float cv = cvs[j];
+                const float q = v[j];
+                const float t = q + (cv > 0.f ? l1_over_B : 0.f);
+                const float dzv = (__float_as_int(cv) < 0) ? 0.f : t;  // sign bit set <=> z < 0
+                dp[(long long)j * p.feats] = rn_tf32(dzv);
+                db += dzv;
+                s = fmaf(cv, q, s);  // cv is +-0 when z <= 0
+                if (TIED) s = fmaf(dzv, cv - bn, s);
+            }
+        }
     }
     SC_DEVICE void chunk(int co, float (&v)[32], int next_co) {
         if (c.row >= c.M) return;
@@ -162,18 +193,12 @@ struct EpiBackCode {
 #pragma unroll
         for (int j = 0; j < 32; ++j) cvs[j] = nxt[j];
         if (next_co >= 0) prefetch(next_co);
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {
-            if (j < nb) {
-                const float cv = cvs[j];
-                const float q = v[j];
-                const bool live = !signbit(cv);  // z >= 0
-                const float dzv = live ? (q + (cv > 0.f ? l1_over_B : 0.f)) : 0.f;
-                dp[(long long)j * p.feats] = rn_tf32(dzv);
-                db += dzv;
-                s += cv * q;  // cv is +-0 when z <= 0
-                if (p.tied) s += dzv * (cv - bn);
-            }
+        if (nb >= 32) {
+            if (p.tied) body<true, true>(cvs, v, dp, nb);
+            else body<true, false>(cvs, v, dp, nb);
+        } else {
+            if (p.tied) body<false, true>(cvs, v, dp, nb);
+            else body<false, false>(cvs, v, dp, nb);
         }
     }
     SC_DEVICE void finish() {

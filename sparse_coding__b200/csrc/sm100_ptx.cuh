@@ -204,8 +204,8 @@ __host__ __device__ constexpr uint32_t make_idesc_tf32(int m, int n, bool a_mn, 
 // The tensor core ignores the low 13 bits (truncation, biased); every operand this engine
 // feeds to tcgen05 is pre-rounded with this so products are unbiased (see DESIGN.md "Precision").
 SC_DEVICE float rn_tf32(float x) {
-    uint32_t u = __float_as_uint(x);
-    u = (u + 0x0fffu + ((u >> 13) & 1u)) & 0xffffe000u;
+    uint32_t u;
+    asm("cvt.rn.tf32.f32 %0, %1;" : "=r"(u) : "f"(x));  // one F2FP instruction, round to nearest even
     return __uint_as_float(u);
 }
 

@@ -1,5 +1,5 @@
 """Multi-GPU check of the data-parallel single-dictionary path (BASELINE.json configs[4] shape family):
-torchrun --nproc-per-node G scripts/dp_check.py [--d 2048 --n 65536 --batch 8192 --steps 5]
+torchrun --nproc-per-node G scripts/dp_check.py [--width 2048 --feats 65536 --batch 8192 --steps 5]
 Every rank trains the same dictionary on its slice of the rows (gradient-only fused step + one NCCL
 all-reduce + sc_adam_apply); rank 0 also steps a single-GPU copy on the full batch and reports the
 difference, then times the data-parallel step."""
@@ -18,8 +18,8 @@ from sparse_coding__b200.dist import DataParallelEnsemble, shard_rows  # noqa: E
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--d", type=int, default=512)
-    ap.add_argument("--n", type=int, default=8192)
+    ap.add_argument("--width", type=int, default=512)
+    ap.add_argument("--feats", type=int, default=8192)
     ap.add_argument("--batch", type=int, default=2048, help="rows per GPU")
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--check", type=int, default=1)
@@ -30,20 +30,20 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     torch.manual_seed(0)
-    model = sc.FunctionalSAE.init(a.d, a.n, 1e-3, device=dev)
+    model = sc.FunctionalSAE.init(a.width, a.feats, 1e-3, device=dev)
     ens = sc.FunctionalEnsemble([model], sc.FunctionalSAE, sc.torchopt_compat.adam, {"lr": 1e-3}, device=dev)
     dp = DataParallelEnsemble(ens)
     dp.broadcast_parameters(0)
     B = a.batch * world
     g = torch.Generator(device="cpu").manual_seed(1)
-    full = torch.randn(B, a.d, generator=g).to(dev)
+    full = torch.randn(B, a.width, generator=g).to(dev)
     lo, hi = shard_rows(B, rank, world)
-    out = {"world": world, "d": a.d, "n": a.n, "global_batch": B}
+    out = {"world": world, "d": a.width, "n": a.feats, "global_batch": B}
     if a.check:
         ref = None
         if rank == 0:
             torch.manual_seed(0)
-            ref = sc.FunctionalEnsemble([sc.FunctionalSAE.init(a.d, a.n, 1e-3, device=dev)], sc.FunctionalSAE,
+            ref = sc.FunctionalEnsemble([sc.FunctionalSAE.init(a.width, a.feats, 1e-3, device=dev)], sc.FunctionalSAE,
                                         sc.torchopt_compat.adam, {"lr": 1e-3}, device=dev)
         worst = 0.0
         for s in range(3):
@@ -70,7 +70,7 @@ def main():
     if rank == 0:
         out["ms_per_step"] = float(t)
         out["activations_per_s"] = B / (float(t) * 1e-3)
-        out["step_tflops"] = 10.0 * B * a.n * a.d / (float(t) * 1e-3) / 1e12
+        out["step_tflops"] = 10.0 * B * a.feats * a.width / (float(t) * 1e-3) / 1e12
         print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()

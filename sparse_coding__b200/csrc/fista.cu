@@ -68,48 +68,65 @@ struct EpiFistaRes {
     SC_DEVICE void finish() {}
 };
 
-// F2 epilogue: gradient step, shrink + ReLU, momentum (fista.py:121-123)
+// F2 epilogue: gradient step, shrink + ReLU, momentum (fista.py:121-123).
+// y lives only as its (hi, lo) TF32 pair (hi + lo carries 22+ bits, a perturbation below fp32 rounding of
+// the update itself); the three [32 x 32] tiles y_hi, y_lo, a come in and go out through the warp's
+// staging tiles by TMA, in place, so the global traffic is fully coalesced.
 struct EpiFistaStep {
-    struct Params {
-        float* y;         // [B][N] in: y_k, out: y_{k+1}
-        float* a;         // [B][N] in: a_{k-1}, out: a_k
-        float *y_hi, *y_lo;
-        const float* eta; // device scalar
+    static constexpr int kIoBufs = 3;
+    struct alignas(64) Params {
+        CUtensorMap yhi_map, ylo_map, a_map;  // io maps of [B][N]
+        const float* eta;                      // device scalar
         float l1, mom;
     };
     const Params& p;
     const RowCtx c;
+    const EpiIo io;
     float eta, thr;
-    static constexpr int kIoBufs = 0;
-    SC_DEVICE EpiFistaStep(const Params& p_, const RowCtx& c_, const EpiIo&) : p(p_), c(c_) {
+    SC_DEVICE EpiFistaStep(const Params& p_, const RowCtx& c_, const EpiIo& io_) : p(p_), c(c_), io(io_) {
         eta = *p.eta;
         thr = eta * p.l1;
     }
-    SC_DEVICE void prefetch(int) {}
-    SC_DEVICE void chunk(int co, float (&v)[32], int /*next_co*/) {
-        const int col = c.col0 + co;
-        if (c.row >= c.M || col >= c.N) return;
-        const int ncols = c.N - col;
-        const long long off = (long long)c.row * c.N + col;
-        float yv[32], av[32];
-        load_row32(p.y + off, yv, ncols);
-        load_row32(p.a + off, av, ncols);
+    SC_DEVICE void prefetch(int co) {
+        io_wait_stores_read();
+        if ((threadIdx.x & 31) == 0) {
+            const int col = c.col0 + co, row0 = c.row;
+            io_expect(io, 3 * kIoTileBytes);
+            tma_load_3d(&p.yhi_map, io.bar, io.buf, col, row0, 0);
+            tma_load_3d(&p.ylo_map, io.bar, io.buf + kIoTileBytes, col, row0, 0);
+            tma_load_3d(&p.a_map, io.bar, io.buf + 2 * kIoTileBytes, col, row0, 0);
+        }
+    }
+    SC_DEVICE void chunk(int co, float (&v)[32], int next_co) {
+        const int lane = threadIdx.x & 31;
+        const int col = c.col0 + co, row0 = c.row - lane;
+        uint8_t* b = io.buf;
+        io_wait_loads(io);
+        float yh[32], yl[32], av[32];
+        io_read_row(b, lane, yh);
+        io_read_row(b + kIoTileBytes, lane, yl);
+        io_read_row(b + 2 * kIoTileBytes, lane, av);
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
-            const float yn = yv[j] + eta * v[j];         // ahat_y.add(eta * Res D^T)
-            const float an = fmaxf(yn - thr, 0.f);       // .sub(eta*l1).clamp(min=0)
-            yv[j] = an + (an - av[j]) * p.mom;           // ahat.add(ahat.sub(ahat_pre).mul(mom))
+            const float yn = (yh[j] + yl[j]) + eta * v[j];   // ahat_y.add(eta * Res D^T)
+            const float an = fmaxf(yn - thr, 0.f);            // .sub(eta*l1).clamp(min=0)
+            const float y2 = an + (an - av[j]) * p.mom;       // ahat.add(ahat.sub(ahat_pre).mul(mom))
             av[j] = an;
+            yh[j] = rn_tf32(y2);
+            yl[j] = rn_tf32(y2 - yh[j]);
         }
-        store_row32(p.a + off, av, ncols);
-        store_row32(p.y + off, yv, ncols);
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {
-            av[j] = rn_tf32(yv[j]);
-            yv[j] = rn_tf32(yv[j] - av[j]);
+        io_write_row(b, lane, yh);
+        io_write_row(b + kIoTileBytes, lane, yl);
+        io_write_row(b + 2 * kIoTileBytes, lane, av);
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+            tma_store_3d(&p.yhi_map, b, col, row0, 0);
+            tma_store_3d(&p.ylo_map, b + kIoTileBytes, col, row0, 0);
+            tma_store_3d(&p.a_map, b + 2 * kIoTileBytes, col, row0, 0);
         }
-        store_row32(p.y_hi + off, av, ncols);
-        store_row32(p.y_lo + off, yv, ncols);
+        io_commit();
+        if (next_co >= 0) prefetch(next_co);
     }
     SC_DEVICE void finish() {}
 };
@@ -212,7 +229,7 @@ static int fista_impl(const ScFistaArgs& a) {
     const long long BN_ = (long long)B * N, Nd = (long long)N * d;
 
     SC_TRY(split(a.D, w.D_hi, w.D_lo, nullptr, Nd, st));
-    SC_TRY(split(a.a0, w.y_hi, w.y_lo, w.y, BN_, st));
+    SC_TRY(split(a.a0, w.y_hi, w.y_lo, nullptr, BN_, st));
     SC_CUDA(cudaMemcpyAsync(a.out_a, a.a0, BN_ * sizeof(float), cudaMemcpyDeviceToDevice, st), "copy a0");
 
     if (a.eta > 0.f) {
@@ -255,10 +272,19 @@ static int fista_impl(const ScFistaArgs& a) {
                     {kmajor(w.res_hi, B, d, 1, 0), kmajor(w.D_hi, N, d, 1, 0)}};
         SC_TRY(plan_gemm(&p2, B, N, 1, s, 3, false, false));
     }
+    EpiFistaStep::Params e2{};
+    {
+        const char* err = nullptr;
+        int rc = make_io_map(&e2.yhi_map, w.y_hi, B, N, 1, 0, &err);
+        if (rc == 0) rc = make_io_map(&e2.ylo_map, w.y_lo, B, N, 1, 0, &err);
+        if (rc == 0) rc = make_io_map(&e2.a_map, a.out_a, B, N, 1, 0, &err);
+        if (rc != 0) return fail(rc, "%s", err ? err : "io tensor map creation failed");
+    }
+    e2.eta = w.eta; e2.l1 = a.l1_coef;
     for (int k = 0; k < a.num_iter; ++k) {
         EpiFistaRes::Params e1{a.x, w.res_hi, w.res_lo, nullptr};
         SC_TRY((launch_plan<false, true, EpiFistaRes>(p1, e1, st)));
-        EpiFistaStep::Params e2{w.y, a.out_a, w.y_hi, w.y_lo, w.eta, a.l1_coef, a.momentum[k]};
+        e2.mom = a.momentum[k];
         SC_TRY((launch_plan<false, false, EpiFistaStep>(p2, e2, st)));
     }
     // final residual from ahat (fista.py:126): reuse the y_hi/y_lo operand buffers for the split of a

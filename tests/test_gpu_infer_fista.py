@@ -146,3 +146,22 @@ def test_single_member_loss_matches_oracle():
     total, (ld, aux) = sc.FunctionalTiedSAE.loss({k: v.cuda() for k, v in tp.items()}, {k: v.cuda() for k, v in tb.items()}, x.cuda())
     assert "l_bias_decay" not in ld
     assert abs(float(ld["loss"]) - float(ls["loss"])) <= 1e-3 * abs(float(ls["loss"]))
+
+
+def test_fista_300_iterations_at_pythia_width():
+    """T3 at the BASELINE.json configs[3] dictionary shape (d=512, N=4096, 300 iterations), on as many
+    rows as the float64 CPU oracle finishes in seconds; rows are independent, so this is the full-size
+    check per row."""
+    import sparse_coding__b200 as sc
+    B, d, N, iters = 320, 512, 4096, 300
+    torch.manual_seed(10)
+    D = R.row_normalise(torch.randn(N, d))[0]
+    x = make_sparse_data(B, d, 2 * d, 10, seed=11)
+    a0 = torch.relu(x @ D.T - 0.05)
+    l1 = 1e-3
+    a_ref, res_ref = R.fista(x.double(), D.double(), l1, a0.double(), iters)
+    a, res = sc.FunctionalFista.fista(x.cuda(), D.cuda(), l1, a0.cuda(), iters, "cuda")
+    assert float((a.cpu().double() - a_ref).abs().max()) < 1e-4
+    assert float((res.cpu().double() - res_ref).abs().max()) < 1e-4
+    # size-independent property: residual is consistent with the codes
+    assert float((x.cuda() - a @ D.cuda() - res).abs().max()) < 1e-4

@@ -34,13 +34,20 @@ struct GemmCfg2 {
     static_assert(kStages >= 2, "not enough shared memory left for the operand pipeline");
 };
 
-template <int BN, bool A_MN, bool B_MN, class Epi>
+// EB = bytes per operand element: 4 (fp32 storage, .kind::tf32, 32 elements per 128-byte k-block row) or
+// 2 (fp16, .kind::f16, 64 elements).  Tile bytes, stage bytes and the four MMAs per k-block are the same.
+// MN-major fp16 tiles use the plain 128-byte swizzle: chunks of 64 m/n x 64 k (8 KB), 8-row groups 1 KB apart.
+template <int BN, bool A_MN, bool B_MN, class Epi, int EB = 4>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
                       const __grid_constant__ typename Epi::Params ep) {
     using Cfg = GemmCfg2<BN, Epi::kIoBufs>;
     constexpr int kStages = Cfg::kStages;
     constexpr int kBHalf = Cfg::kBHalf;
+    constexpr int kKElems = 128 / EB;            // operand elements per k-block
+    constexpr int kMnChunk = EB == 4 ? 32 : 64;  // m/n elements per 128-byte MN-major chunk
+    constexpr int kMnChunkBytes = kMnChunk == 32 ? 4096 : 8192;
+    constexpr int kMnShift = EB == 4 ? 5 : 6;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* io_smem = smem + kStages * Cfg::kStageBytes;
@@ -106,30 +113,30 @@ gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape sha
                 const int n0 = tn * BN + rank * kBHalf;
                 const int seg_lo = nprob > 1 ? prob : 0, seg_hi = nprob > 1 ? prob + 1 : shape.nseg;
                 for (int seg = seg_lo; seg < seg_hi; ++seg) {
-                    const int kblocks = (shape.K[seg] + kBlockK - 1) / kBlockK;
+                    const int kblocks = (shape.K[seg] + kKElems - 1) / kKElems;
                     const int ga = g * shape.a_gmul[seg], gb = g * shape.b_gmul[seg];
                     for (int kb = 0; kb < kblocks; ++kb) {
                         mbar_wait(&empty_bar[stage], phase ^ 1);
                         uint8_t* sa = smem + stage * Cfg::kStageBytes;
                         uint8_t* sb = sa + kATileBytes;
-                        const int k0 = kb * kBlockK;
+                        const int k0 = kb * kKElems;
                         if (!A_MN) {
                             tma_load_3d_2cta(&maps.a[seg], &full_bar[stage], sa, k0, m0, ga);
                         } else if (shape.a_one_box[seg]) {
-                            tma_load_4d_2cta(&maps.a[seg], &full_bar[stage], sa, 0, k0, m0 >> 5, ga);
+                            tma_load_4d_2cta(&maps.a[seg], &full_bar[stage], sa, 0, k0, m0 >> kMnShift, ga);
                         } else {
 #pragma unroll
-                            for (int i = 0; i < kBlockM / 32; ++i)
-                                tma_load_3d_2cta(&maps.a[seg], &full_bar[stage], sa + i * 4096, m0 + 32 * i, k0, ga);
+                            for (int i = 0; i < kBlockM / kMnChunk; ++i)
+                                tma_load_3d_2cta(&maps.a[seg], &full_bar[stage], sa + i * kMnChunkBytes, m0 + kMnChunk * i, k0, ga);
                         }
                         if (!B_MN) {
                             tma_load_3d_2cta(&maps.b[seg], &full_bar[stage], sb, k0, n0, gb);
                         } else if (shape.b_one_box[seg]) {
-                            tma_load_4d_2cta(&maps.b[seg], &full_bar[stage], sb, 0, k0, n0 >> 5, gb);
+                            tma_load_4d_2cta(&maps.b[seg], &full_bar[stage], sb, 0, k0, n0 >> kMnShift, gb);
                         } else {
 #pragma unroll
-                            for (int i = 0; i < kBHalf / 32; ++i)
-                                tma_load_3d_2cta(&maps.b[seg], &full_bar[stage], sb + i * 4096, n0 + 32 * i, k0, gb);
+                            for (int i = 0; i < (kBHalf + kMnChunk - 1) / kMnChunk; ++i)
+                                tma_load_3d_2cta(&maps.b[seg], &full_bar[stage], sb + i * kMnChunkBytes, n0 + kMnChunk * i, k0, gb);
                         }
                         if (leader) mbar_arrive_expect_tx(&full_bar[stage], 2 * Cfg::kStageBytes);
                         else mbar_arrive_remote(&full_bar[stage], 0);
@@ -141,7 +148,7 @@ gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape sha
     } else if (warp == 1) {
         // ------------------------------------------------------------------ MMA issuer (leader CTA only)
         if (leader && lane == 0) {
-            constexpr uint32_t idesc = make_idesc_tf32(2 * kBlockM, BN, A_MN, B_MN);
+            constexpr uint32_t idesc = EB == 4 ? make_idesc_tf32(2 * kBlockM, BN, A_MN, B_MN) : make_idesc_f16(2 * kBlockM, BN, A_MN, B_MN);
             int stage = 0;
             uint32_t phase = 0;
             int it = 0;
@@ -155,7 +162,7 @@ gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape sha
                 const int prob = (tile / tiles_per_group) / shape.G;
                 const int seg_lo = nprob > 1 ? prob : 0, seg_hi = nprob > 1 ? prob + 1 : shape.nseg;
                 for (int seg = seg_lo; seg < seg_hi; ++seg) {
-                    const int kblocks = (shape.K[seg] + kBlockK - 1) / kBlockK;
+                    const int kblocks = (shape.K[seg] + kKElems - 1) / kKElems;
                     for (int kb = 0; kb < kblocks; ++kb) {
                         mbar_wait(&full_bar[stage], phase);
                         tc_fence_after();
@@ -163,11 +170,22 @@ gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape sha
                         const uint32_t b_base = a_base + kATileBytes;
 #pragma unroll
                         for (int k = 0; k < kBlockK / kUmmaK; ++k) {
-                            const uint64_t da = A_MN ? make_smem_desc(a_base + k * 1024, 4096, 512, kLayoutSw128Base32)
-                                                     : make_smem_desc(a_base + k * 32, 16, 1024, kLayoutSw128);
-                            const uint64_t db = B_MN ? make_smem_desc(b_base + k * 1024, 4096, 512, kLayoutSw128Base32)
-                                                     : make_smem_desc(b_base + k * 32, 16, 1024, kLayoutSw128);
-                            umma_tf32_2cta(d_tmem, da, db, idesc, accumulate);
+                            // one MMA consumes 32 bytes of K: 8 tf32 or 16 fp16 elements
+                            uint64_t da, db;
+                            if (EB == 4) {
+                                da = A_MN ? make_smem_desc(a_base + k * 1024, 4096, 512, kLayoutSw128Base32)
+                                          : make_smem_desc(a_base + k * 32, 16, 1024, kLayoutSw128);
+                                db = B_MN ? make_smem_desc(b_base + k * 1024, 4096, 512, kLayoutSw128Base32)
+                                          : make_smem_desc(b_base + k * 32, 16, 1024, kLayoutSw128);
+                                umma_tf32_2cta(d_tmem, da, db, idesc, accumulate);
+                            } else {
+                                // MN-major fp16: 16 k-rows per MMA = two 8-row groups (SBO 1024); 64-wide chunks 8 KB apart (LBO)
+                                da = A_MN ? make_smem_desc(a_base + k * 2048, 8192, 1024, kLayoutSw128)
+                                          : make_smem_desc(a_base + k * 32, 16, 1024, kLayoutSw128);
+                                db = B_MN ? make_smem_desc(b_base + k * 2048, 8192, 1024, kLayoutSw128)
+                                          : make_smem_desc(b_base + k * 32, 16, 1024, kLayoutSw128);
+                                umma_f16_2cta(d_tmem, da, db, idesc, accumulate);
+                            }
                             accumulate = 1;
                         }
                         umma_commit_2cta(&empty_bar[stage]);
@@ -217,11 +235,11 @@ gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape sha
 }
 
 // grid = 2 * min(#tiles, #SMs / 2) persistent CTAs in clusters of two.
-template <int BN, bool A_MN, bool B_MN, class Epi>
+template <int BN, bool A_MN, bool B_MN, class Epi, int EB = 4>
 cudaError_t launch_gemm_2cta(const GemmMaps& maps, GemmShape shape, const typename Epi::Params& ep, int num_sms,
                              cudaStream_t stream) {
     using Cfg = GemmCfg2<BN, Epi::kIoBufs>;
-    auto kern = gemm_tf32_2cta_kernel<BN, A_MN, B_MN, Epi>;
+    auto kern = gemm_tf32_2cta_kernel<BN, A_MN, B_MN, Epi, EB>;
     static bool attr_set[64] = {};
     int dev = 0;
     cudaGetDevice(&dev);

@@ -119,6 +119,13 @@ inline Operand kmajor(const float* base, long long mn, long long k, long long g,
 inline Operand mnmajor(const float* base, long long mn, long long k, long long g, long long gstride) {
     return Operand{base, mn, k, g, mn, gstride, true};
 }
+// fp16 operands (base points at __half data)
+inline Operand kmajor_h(const void* base, long long mn, long long k, long long g, long long gstride) {
+    return Operand{base, mn, k, g, k, gstride, false, 2};
+}
+inline Operand mnmajor_h(const void* base, long long mn, long long k, long long g, long long gstride) {
+    return Operand{base, mn, k, g, mn, gstride, true, 2};
+}
 
 // A prepared launch: TMA maps + shape; reusable while the operand addresses and shapes stay the same.
 struct GemmPlan {
@@ -127,6 +134,7 @@ struct GemmPlan {
     int bn;
     int sms;
     bool cta2;
+    int eb;  // operand element bytes (4: TF32 path, 2: fp16 path - CTA-pair kernel only)
 };
 
 inline int plan_gemm(GemmPlan* pl, int M, int N, int G, const Seg* segs, int nseg, bool a_mn, bool b_mn,
@@ -134,13 +142,16 @@ inline int plan_gemm(GemmPlan* pl, int M, int N, int G, const Seg* segs, int nse
     memset(pl, 0, sizeof *pl);
     SC_TRY(device_sm_count(&pl->sms));
     pl->bn = pick_bn(N);
-    pl->cta2 = use_cta_pairs();
+    pl->eb = segs[0].a.elem_bytes == 2 ? 2 : 4;
+    pl->cta2 = use_cta_pairs() || pl->eb == 2;
     GemmShape& sh = pl->sh;
     sh.M = M; sh.N = N; sh.G = G; sh.nseg = nseg;
     sh.nprob = segs_are_problems ? nseg : 1;
     for (int s = 0; s < nseg; ++s) {
         if (segs[s].a.mn_major != a_mn || segs[s].b.mn_major != b_mn) return fail(-3, "operand major mismatch");
         if (segs[s].a.k != segs[s].b.k || segs[s].a.k <= 0) return fail(-3, "segment K mismatch");
+        if ((segs[s].a.elem_bytes == 2) != (pl->eb == 2) || (segs[s].b.elem_bytes == 2) != (pl->eb == 2))
+            return fail(-3, "operand element size mismatch");
         const char* err = nullptr;
         bool a1 = false, b1 = false;
         int rc = make_operand_map(&pl->maps.a[s], segs[s].a, kBlockM, &a1, &err);
@@ -155,9 +166,17 @@ inline int plan_gemm(GemmPlan* pl, int M, int N, int G, const Seg* segs, int nse
     return 0;
 }
 
-template <bool A_MN, bool B_MN, class Epi>
+template <bool A_MN, bool B_MN, class Epi, bool F16 = false>
 int launch_plan(const GemmPlan& pl, const typename Epi::Params& ep, cudaStream_t stream) {
     cudaError_t e;
+    if (F16) {
+        if (pl.eb != 2 || pl.bn < 128) return fail(-3, "fp16 operand path needs bn >= 128");
+        if (pl.bn == 256) e = launch_gemm_2cta<256, A_MN, B_MN, Epi, 2>(pl.maps, pl.sh, ep, pl.sms, stream);
+        else e = launch_gemm_2cta<128, A_MN, B_MN, Epi, 2>(pl.maps, pl.sh, ep, pl.sms, stream);
+        if (e != cudaSuccess) return cuda_fail(e, "gemm (fp16, CTA pair) launch");
+        return 0;
+    }
+    if (pl.eb != 4) return fail(-3, "fp16 operands given to a TF32 launch");
     if (pl.cta2) {
         if (pl.bn == 256) e = launch_gemm_2cta<256, A_MN, B_MN, Epi>(pl.maps, pl.sh, ep, pl.sms, stream);
         else if (pl.bn == 128) e = launch_gemm_2cta<128, A_MN, B_MN, Epi>(pl.maps, pl.sh, ep, pl.sms, stream);
@@ -173,13 +192,13 @@ int launch_plan(const GemmPlan& pl, const typename Epi::Params& ep, cudaStream_t
 }
 
 // ACC[g] = sum_seg A_seg[g] B_seg[g]^T over G groups, epilogue Epi.  Operand majors are compile-time.
-template <bool A_MN, bool B_MN, class Epi>
+template <bool A_MN, bool B_MN, class Epi, bool F16 = false>
 int run_gemm(int M, int N, int G, const Seg* segs, int nseg, const typename Epi::Params& ep, cudaStream_t stream,
              bool segs_are_problems = false) {
     if (M <= 0 || N <= 0 || G <= 0) return 0;
     GemmPlan pl;
     SC_TRY(plan_gemm(&pl, M, N, G, segs, nseg, A_MN, B_MN, segs_are_problems));
-    return launch_plan<A_MN, B_MN, Epi>(pl, ep, stream);
+    return launch_plan<A_MN, B_MN, Epi, F16>(pl, ep, stream);
 }
 
 }  // namespace sc

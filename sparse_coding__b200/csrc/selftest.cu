@@ -7,6 +7,8 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <cuda_fp16.h>
+
 #include <vector>
 
 #include "epi_store.cuh"
@@ -48,6 +50,7 @@ struct EpiNull {
 };
 static int g_null = 0;
 static int g_cg = 1;
+static int g_eb = 4;
 template <int BN, bool A_MN, bool B_MN>
 static cudaError_t run(const GemmMaps& maps, const GemmShape& sh, const EpiStore::Params& ep, int sms) {
     if (g_null) {
@@ -55,6 +58,7 @@ static cudaError_t run(const GemmMaps& maps, const GemmShape& sh, const EpiStore
         if (g_cg == 2) return launch_gemm_2cta<BN, A_MN, B_MN, EpiNull>(maps, sh, en, sms, 0);
         return launch_gemm<BN, A_MN, B_MN, EpiNull>(maps, sh, en, sms, 0);
     }
+    if (g_eb == 2) return launch_gemm_2cta<BN, A_MN, B_MN, EpiStore, 2>(maps, sh, ep, sms, 0);
     if (g_cg == 2) return launch_gemm_2cta<BN, A_MN, B_MN, EpiStore>(maps, sh, ep, sms, 0);
     return launch_gemm<BN, A_MN, B_MN, EpiStore>(maps, sh, ep, sms, 0);
 }
@@ -68,16 +72,20 @@ int main(int argc, char** argv) {
     const int a_mn = atoi(argv[5]), b_mn = atoi(argv[6]), BN = atoi(argv[7]), nseg = atoi(argv[8]);
     g_cg = argc > 9 ? atoi(argv[9]) : 1;
     g_null = getenv("SC_SELFTEST_NULL_EPI") != nullptr;
-    const int ldA = a_mn ? ((M + 3) & ~3) : ((K + 3) & ~3);
-    const int ldB = b_mn ? ((N + 3) & ~3) : ((K + 3) & ~3);
+    g_eb = argc > 10 ? atoi(argv[10]) : 4;
+    if (g_eb == 2) g_cg = 2;
+    g_eb = argc > 10 ? atoi(argv[10]) : 4;
+    const int al = g_eb == 2 ? 7 : 3;
+    const int ldA = a_mn ? ((M + al) & ~al) : ((K + al) & ~al);
+    const int ldB = b_mn ? ((N + al) & ~al) : ((K + al) & ~al);
     const size_t szA = (size_t)(a_mn ? K : M) * ldA, szB = (size_t)(b_mn ? K : N) * ldB;
     std::vector<std::vector<float>> hA(nseg), hB(nseg);
     srand(1234);
     for (int s = 0; s < nseg; ++s) {
         hA[s].resize(szA * G);
         hB[s].resize(szB * G);
-        for (auto& v : hA[s]) v = host_rn_tf32((rand() / (float)RAND_MAX) * 2.f - 1.f);
-        for (auto& v : hB[s]) v = host_rn_tf32((rand() / (float)RAND_MAX) * 2.f - 1.f);
+        for (auto& v : hA[s]) v = g_eb == 2 ? __half2float(__float2half((rand() / (float)RAND_MAX) * 2.f - 1.f)) : host_rn_tf32((rand() / (float)RAND_MAX) * 2.f - 1.f);
+        for (auto& v : hB[s]) v = g_eb == 2 ? __half2float(__float2half((rand() / (float)RAND_MAX) * 2.f - 1.f)) : host_rn_tf32((rand() / (float)RAND_MAX) * 2.f - 1.f);
     }
     auto A = [&](int s, int g, int m, int k) { return hA[s][g * szA + (a_mn ? (size_t)k * ldA + m : (size_t)m * ldA + k)]; };
     auto B = [&](int s, int g, int n, int k) { return hB[s][g * szB + (b_mn ? (size_t)k * ldB + n : (size_t)n * ldB + k)]; };
@@ -95,10 +103,18 @@ int main(int argc, char** argv) {
     for (int s = 0; s < nseg; ++s) {
         CK(cudaMalloc(&dA[s], hA[s].size() * 4));
         CK(cudaMalloc(&dB[s], hB[s].size() * 4));
-        CK(cudaMemcpy(dA[s], hA[s].data(), hA[s].size() * 4, cudaMemcpyHostToDevice));
-        CK(cudaMemcpy(dB[s], hB[s].data(), hB[s].size() * 4, cudaMemcpyHostToDevice));
-        Operand oa{dA[s], M, K, G, ldA, (int64_t)szA, a_mn != 0};
-        Operand ob{dB[s], N, K, G, ldB, (int64_t)szB, b_mn != 0};
+        if (g_eb == 2) {
+            std::vector<__half> ha(hA[s].size()), hb(hB[s].size());
+            for (size_t i = 0; i < ha.size(); ++i) ha[i] = __float2half(hA[s][i]);
+            for (size_t i = 0; i < hb.size(); ++i) hb[i] = __float2half(hB[s][i]);
+            CK(cudaMemcpy(dA[s], ha.data(), ha.size() * 2, cudaMemcpyHostToDevice));
+            CK(cudaMemcpy(dB[s], hb.data(), hb.size() * 2, cudaMemcpyHostToDevice));
+        } else {
+            CK(cudaMemcpy(dA[s], hA[s].data(), hA[s].size() * 4, cudaMemcpyHostToDevice));
+            CK(cudaMemcpy(dB[s], hB[s].data(), hB[s].size() * 4, cudaMemcpyHostToDevice));
+        }
+        Operand oa{dA[s], M, K, G, ldA, (int64_t)szA, a_mn != 0, g_eb};
+        Operand ob{dB[s], N, K, G, ldB, (int64_t)szB, b_mn != 0, g_eb};
         bool a1 = false, b1 = false;
         if (make_operand_map(&maps.a[s], oa, 128, &a1, &err) || make_operand_map(&maps.b[s], ob, g_cg == 2 ? BN / 2 : BN, &b1, &err)) {
             printf("tensor map error: %s\n", err ? err : "?");
@@ -154,7 +170,7 @@ int main(int argc, char** argv) {
                 if (fabs(acc) > max_ref) max_ref = fabs(acc);
             }
     const double flops = 2.0 * M * N * (double)K * G * nseg;
-    printf("cg=%d M=%d N=%d K=%d G=%d a_mn=%d b_mn=%d BN=%d nseg=%d : max_err=%.3e (max |ref| %.3e) bad=%lld  %.3f ms  %.1f TFLOP/s  %s\n",
-           g_cg, M, N, K, G, a_mn, b_mn, BN, nseg, max_err, max_ref, bad, ms, flops / ms * 1e-9, bad == 0 ? "PASS" : "FAIL");
+    printf("eb=%d cg=%d M=%d N=%d K=%d G=%d a_mn=%d b_mn=%d BN=%d nseg=%d : max_err=%.3e (max |ref| %.3e) bad=%lld  %.3f ms  %.1f TFLOP/s  %s\n",
+           g_eb, g_cg, M, N, K, G, a_mn, b_mn, BN, nseg, max_err, max_ref, bad, ms, flops / ms * 1e-9, bad == 0 ? "PASS" : "FAIL");
     return bad == 0 ? 0 : 3;
 }

@@ -29,7 +29,8 @@ static PFN_cuTensorMapEncodeTiled get_encode(const char** err) {
 static thread_local char g_msg[256];
 
 static int encode(CUtensorMap* out, const void* base, int rank, const cuuint64_t* dims, const cuuint64_t* strides_bytes,
-                  const cuuint32_t* box, CUtensorMapSwizzle swz, const char** err) {
+                  const cuuint32_t* box, CUtensorMapSwizzle swz, const char** err,
+                  CUtensorMapDataType dtype = CU_TENSOR_MAP_DATA_TYPE_FLOAT32) {
     PFN_cuTensorMapEncodeTiled fn = get_encode(err);
     if (!fn) return -10;
     if (reinterpret_cast<uintptr_t>(base) & 15) {
@@ -49,7 +50,7 @@ static int encode(CUtensorMap* out, const void* base, int rank, const cuuint64_t
         if (err) *err = "tensor group stride is not a positive multiple of 16 bytes";
         return -12;
     }
-    CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, rank, const_cast<void*>(base), dims, strides_bytes, box, estr,
+    CUresult r = fn(out, dtype, rank, const_cast<void*>(base), dims, strides_bytes, box, estr,
                     CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
@@ -65,25 +66,31 @@ static int encode(CUtensorMap* out, const void* base, int rank, const cuuint64_t
 
 int make_operand_map(CUtensorMap* out, const Operand& op, int box_mn, bool* one_box, const char** err) {
     if (one_box) *one_box = false;
+    const int eb = op.elem_bytes == 2 ? 2 : 4;
+    const CUtensorMapDataType dt = eb == 2 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+    const cuuint32_t kelems = 128 / eb;  // one 128-byte swizzle span of K (or of M/N when MN-major)
     const int64_t g = op.g < 1 ? 1 : op.g;
     // a never-used outer stride still has to be a legal one
     const int64_t gs = (g > 1 && op.gstride > 0) ? op.gstride : op.ld * (op.mn_major ? op.k : op.mn);
-    cuuint64_t strides[2] = {(cuuint64_t)op.ld * 4, (cuuint64_t)gs * 4};
+    cuuint64_t strides[2] = {(cuuint64_t)op.ld * eb, (cuuint64_t)gs * eb};
     if (!op.mn_major) {
         cuuint64_t dims[3] = {(cuuint64_t)op.k, (cuuint64_t)op.mn, (cuuint64_t)g};
-        cuuint32_t box[3] = {32, (cuuint32_t)box_mn, 1};
-        return encode(out, op.base, 3, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B, err);
+        cuuint32_t box[3] = {kelems, (cuuint32_t)box_mn, 1};
+        return encode(out, op.base, 3, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B, err, dt);
     }
-    if (one_box && op.mn % 32 == 0) {
-        cuuint64_t dims4[4] = {32, (cuuint64_t)op.k, (cuuint64_t)(op.mn / 32), (cuuint64_t)g};
-        cuuint64_t strides4[3] = {(cuuint64_t)op.ld * 4, 128, (cuuint64_t)gs * 4};
-        cuuint32_t box4[4] = {32, 32, (cuuint32_t)(box_mn / 32), 1};
+    // MN-major: fp32 needs the 32-byte-atom flavour of the 128-byte swizzle, fp16 the plain one
+    const CUtensorMapSwizzle swz = eb == 4 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B;
+    const cuuint32_t chunk = kelems;  // m/n elements per 128-byte chunk: 32 fp32 or 64 fp16
+    if (one_box && op.mn % chunk == 0 && box_mn % (int)chunk == 0) {
+        cuuint64_t dims4[4] = {chunk, (cuuint64_t)op.k, (cuuint64_t)(op.mn / chunk), (cuuint64_t)g};
+        cuuint64_t strides4[3] = {(cuuint64_t)op.ld * eb, 128, (cuuint64_t)gs * eb};
+        cuuint32_t box4[4] = {chunk, kelems, (cuuint32_t)(box_mn / chunk), 1};
         *one_box = true;
-        return encode(out, op.base, 4, dims4, strides4, box4, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, err);
+        return encode(out, op.base, 4, dims4, strides4, box4, swz, err, dt);
     }
     cuuint64_t dims[3] = {(cuuint64_t)op.mn, (cuuint64_t)op.k, (cuuint64_t)g};
-    cuuint32_t box[3] = {32, 32, 1};
-    return encode(out, op.base, 3, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, err);
+    cuuint32_t box[3] = {chunk, kelems, 1};
+    return encode(out, op.base, 3, dims, strides, box, swz, err, dt);
 }
 
 int make_rowmajor_map(CUtensorMap* out, const float* base, int64_t rows, int64_t cols, int64_t g, int64_t ld,
@@ -104,6 +111,16 @@ int make_io_map(CUtensorMap* out, const float* base, int64_t rows, int64_t cols,
     cuuint64_t strides[2] = {(cuuint64_t)cols * 4, (cuuint64_t)gs * 4};
     cuuint32_t box[3] = {32, 32, 1};
     return encode(out, base, 3, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B, err);
+}
+
+int make_io_map_h(CUtensorMap* out, const void* base, int64_t rows, int64_t cols, int64_t g, int64_t gstride,
+                  const char** err) {
+    if (g < 1) g = 1;
+    const int64_t gs = (g > 1 && gstride > 0) ? gstride : cols * rows;
+    cuuint64_t dims[3] = {(cuuint64_t)cols, (cuuint64_t)rows, (cuuint64_t)g};
+    cuuint64_t strides[2] = {(cuuint64_t)cols * 2, (cuuint64_t)gs * 2};
+    cuuint32_t box[3] = {32, 32, 1};
+    return encode(out, base, 3, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_64B, err, CU_TENSOR_MAP_DATA_TYPE_FLOAT16);
 }
 
 }  // namespace sc

@@ -14,10 +14,11 @@ namespace sc {
 // ld and gstride in elements, multiples of 4 (TMA strides are multiples of 16 bytes);
 // base 16-byte aligned.  G == 1 and gstride == 0 describe an operand shared by every group.
 struct Operand {
-    const float* base;
+    const void* base;
     int64_t mn, k, g;
     int64_t ld, gstride;
     bool mn_major;
+    int elem_bytes = 4;  // 4: fp32 storage (TF32 MMA), 2: fp16
 };
 
 // box_mn: rows of the operand tile (128 for the A side, BLOCK_N for the B side); BLOCK_K = 32.
@@ -36,5 +37,8 @@ int make_rowmajor_map(CUtensorMap* out, const float* base, int64_t rows, int64_t
 // Row-major fp32 [G][rows][cols] map for the epilogue staging tiles: box {32 cols, 32 rows}, 128-byte swizzle.
 int make_io_map(CUtensorMap* out, const float* base, int64_t rows, int64_t cols, int64_t g, int64_t gstride,
                 const char** err);
+// Same for fp16 tensors: box {32 cols, 32 rows} = 64-byte rows, 64-byte swizzle.
+int make_io_map_h(CUtensorMap* out, const void* base, int64_t rows, int64_t cols, int64_t g, int64_t gstride,
+                  const char** err);
 
 }  // namespace sc

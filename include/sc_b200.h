@@ -66,10 +66,18 @@ typedef struct {
      * the 1/B and 1/(B d) loss normalisations so that per-rank results add up to the global-batch ones. */
     float *grad_enc, *grad_bias, *grad_dec;
     int32_t B_total;
+    /* operand_format 0: GEMM operands and c / R / dz in fp32 storage rounded to TF32 (kind::tf32).
+     * operand_format 1: the same tensors in fp16 (kind::f16, same 11-bit significand, twice the MMA rate, half
+     * the bytes; residual and dz kept unscaled so nothing underflows); needs sc_sae_step_f16_supported(B,d,N).
+     * In format 1 the codes are written to out_c_half ([M,B,N] fp16, required) and out_c may be NULL
+     * (when given it is filled from the fp16 codes).  Inputs with |x| > 65504 overflow fp16: use format 0. */
+    int32_t operand_format;
+    void* out_c_half;
 } ScStepArgs;
 
 size_t sc_sae_step_workspace_bytes(int32_t M, int32_t B, int32_t d, int32_t N, int32_t tied, int32_t x_per_member);
 int sc_sae_step(const ScStepArgs* args);
+int sc_sae_step_f16_supported(int32_t B, int32_t d, int32_t N);
 
 /* Elementwise Adam exactly as the fused epilogues apply it (torchopt 0.7.1 semantics, see ScAdam):
  * p, mu, nu updated in place from gradient g, n elements (multiple of 4). */

@@ -23,7 +23,7 @@ EXPORTS = [
     "sc_version", "sc_last_error", "sc_sae_step_workspace_bytes", "sc_sae_step",
     "sc_encode_workspace_bytes", "sc_encode", "sc_decode_workspace_bytes", "sc_decode",
     "sc_fista_workspace_bytes", "sc_fista", "sc_gemm_tf32", "sc_adam_apply", "sc_row_normalise", "sc_column_variance",
-    "sc_profile_begin", "sc_profile_end", "sc_encode_noalloc",
+    "sc_profile_begin", "sc_profile_end", "sc_encode_noalloc", "sc_sae_step_f16_supported",
 ]
 
 
@@ -47,6 +47,7 @@ class ScStepArgs(C.Structure):
         ("stream", C.c_void_p),
         ("grad_enc", C.c_void_p), ("grad_bias", C.c_void_p), ("grad_dec", C.c_void_p),
         ("B_total", C.c_int32),
+        ("operand_format", C.c_int32), ("out_c_half", C.c_void_p),
     ]
 
 
@@ -121,6 +122,8 @@ def lib() -> C.CDLL:
         L.sc_gemm_tf32.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p] + [C.c_int32] * 6 + [C.c_void_p]
         L.sc_row_normalise.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]
         L.sc_column_variance.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]
+        L.sc_sae_step_f16_supported.argtypes = [C.c_int32] * 3
+        L.sc_sae_step_f16_supported.restype = C.c_int
         L.sc_adam_apply.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(ScAdam), C.c_void_p]
         L.sc_adam_apply.restype = C.c_int
         for name in ("sc_sae_step", "sc_encode", "sc_decode", "sc_fista", "sc_gemm_tf32", "sc_row_normalise",

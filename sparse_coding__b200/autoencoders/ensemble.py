@@ -62,8 +62,47 @@ def _sig_kind(sig) -> str:
     return kind
 
 
+class LazyCodes(dict):
+    """aux dict of step_batch in fp16-operand mode: {"c": codes}.  The engine keeps the codes as an fp16
+    [M,B,N] tensor (that is what its GEMMs read); the float32 tensor the reference returns
+    (sae_ensemble.py:73-75) is produced on first access, so callers that ignore `aux` - most do - never
+    pay for the 4*M*B*N-byte write."""
+
+    def __init__(self, c_half):
+        super().__init__(c=None)
+        self.c_half = c_half
+        self._c = None
+
+    def _materialise(self):
+        if self._c is None:
+            self._c = self.c_half.float()
+            dict.__setitem__(self, "c", self._c)
+        return self._c
+
+    def __getitem__(self, key):
+        if key == "c":
+            return self._materialise()
+        return dict.__getitem__(self, key)
+
+    def get(self, key, default=None):
+        return self[key] if key in self else default
+
+    def values(self):
+        self._materialise()
+        return dict.values(self)
+
+    def items(self):
+        self._materialise()
+        return dict.items(self)
+
+
 class FunctionalEnsemble:
     """Drop-in for reference ensemble.py:68-193.
+
+    `operand_format`: "auto" (default: fp16 operands when the shape allows it, else TF32), "tf32" or "f16"
+    (env SC_B200_OPERANDS overrides the default).  Both keep an 11-bit significand on every GEMM operand
+    and fp32 accumulation / master weights; fp16 halves the operand bytes and doubles the MMA rate but
+    overflows for |activation| > 65504.
 
     `reference_faithful` (default True) reproduces the reference's Adam as it actually runs:
     the stored step count is never advanced (ensemble.py:185-189 writes the new optimizer state
@@ -102,6 +141,9 @@ class FunctionalEnsemble:
         self._adam = spec_from(self.optimizer_func, self.optimizer_kwargs)
         self._ws = nat.Workspace()
         self._step = 0
+        if not hasattr(self, "operand_format"):
+            import os
+            self.operand_format = os.environ.get("SC_B200_OPERANDS", "auto")
         if not hasattr(self, "reference_faithful"):
             self.reference_faithful = True
         nat.lib()  # fail now, loudly, if the native library is missing
@@ -294,8 +336,15 @@ class FunctionalEnsemble:
             if not tied:
                 grads["decoder"] = torch.empty_like(dec)
 
+        fmt = self.operand_format
+        if fmt not in ("auto", "tf32", "f16"):
+            raise ValueError(f"operand_format {fmt!r}: expected 'auto', 'tf32' or 'f16'")
+        f16 = fmt != "tf32" and bool(L.sc_sae_step_f16_supported(B, d, N))
+        if fmt == "f16" and not f16:
+            raise ValueError(f"operand_format 'f16' needs d, N multiples of 64 and >= 128 and B > 64 (got B={B} d={d} N={N})")
         losses = torch.empty((4, M), dtype=torch.float32, device=x.device)
-        c = torch.empty((M, B, N), dtype=torch.float32, device=x.device)
+        c = None if f16 else torch.empty((M, B, N), dtype=torch.float32, device=x.device)
+        c_half = torch.empty((M, B, N), dtype=torch.float16, device=x.device) if f16 else None
         need = L.sc_sae_step_workspace_bytes(M, B, d, N, int(tied), int(per_member))
         ws_ptr, ws_bytes = self._ws.aligned(need, x.device)
         args = nat.ScStepArgs(
@@ -310,6 +359,7 @@ class FunctionalEnsemble:
             grad_bias=nat.ptr(grads["encoder_bias"]) if grad_only else None,
             grad_dec=nat.ptr(grads.get("decoder")) if grad_only else None,
             B_total=int(batch_total),
+            operand_format=int(f16), out_c_half=nat.ptr(c_half),
         )
         with torch.cuda.device(x.device):
             nat.check(L.sc_sae_step(C.byref(args)), "sc_sae_step")
@@ -318,6 +368,7 @@ class FunctionalEnsemble:
             loss_dict["l_bias_decay"] = losses[3]
         elif grad_only:
             loss_dict["l_bias_decay"] = losses[3]
+        aux = LazyCodes(c_half) if f16 else {"c": c}
         if grad_only:
-            return grads, loss_dict, {"c": c}
-        return loss_dict, {"c": c}
+            return grads, loss_dict, aux
+        return loss_dict, aux

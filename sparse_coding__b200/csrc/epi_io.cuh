@@ -5,6 +5,8 @@
 // tiles with TMA: tile loads complete on the warp's own mbarrier, tile stores are bulk-async groups.
 // Row reads / writes of the swizzled tile are bank-conflict free (a quarter warp covers all 32 banks).
 #pragma once
+#include <cuda_fp16.h>
+
 #include "sm100_ptx.cuh"
 
 namespace sc {
@@ -61,5 +63,18 @@ SC_DEVICE void io_wait_loads(const EpiIo& io, int slot = 0) {
 }
 // element (r, c) of a staging tile (see io_read_row)
 SC_DEVICE uint32_t io_elem_offset(int r, int c) { return r * 128 + (((c >> 2) ^ (r & 7)) << 4) + ((c & 3) << 2); }
+
+// fp16 staging tile [32 rows][32 halves] = 64-byte rows, laid out as TMA's SWIZZLE_64B expects:
+// 16-byte chunk j of row r sits at r*64 + ((j ^ ((r >> 1) & 3)) << 4).  Conflict free for row writes.
+SC_DEVICE void io_write_row_h(uint8_t* tile, int r, const float (&v)[32]) {
+    uint8_t* row = tile + r * 64;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        __half2 h[4];
+#pragma unroll
+        for (int t = 0; t < 4; ++t) h[t] = __floats2half2_rn(v[8 * j + 2 * t], v[8 * j + 2 * t + 1]);
+        *reinterpret_cast<uint4*>(row + ((j ^ ((r >> 1) & 3)) << 4)) = *reinterpret_cast<uint4*>(h);
+    }
+}
 
 }  // namespace sc

@@ -259,6 +259,7 @@ struct EpiAdam {
     struct alignas(64) Params {
         Sub sub[2];   // one per batched problem (untied: [0] encoder, [1] decoder)
         int tiles_b;  // partial slots per feature in s_part
+        float g_scale;  // applied to the accumulator and to s (fp16 mode keeps them scaled by B d / 2; else 1)
         AdamConst a;
     };
     const Params& p;
@@ -271,6 +272,7 @@ struct EpiAdam {
         : p(p_), u(p_.sub[c_.prob]), c(c_), io(io_), s(0.f), inv(1.f), clamped(false) {
         if (u.projected && c.row < c.M) {
             for (int t = 0; t < p.tiles_b; ++t) s += u.s_part[((long long)c.g * p.tiles_b + t) * c.M + c.row];
+            s *= p.g_scale;
             const float iv = u.inv_norm[(long long)c.g * c.M + c.row];
             clamped = iv < 0.f;
             inv = fabsf(iv);
@@ -300,6 +302,10 @@ struct EpiAdam {
         io_wait_loads(io);
         float pv[32];
         io_read_row(b, lane, pv);
+        if (p.g_scale != 1.f) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] *= p.g_scale;
+        }
         if (u.projected) {
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] = clamped ? v[j] * inv : (v[j] - s * (pv[j] * inv)) * inv;

@@ -104,7 +104,7 @@ __global__ void finalize_kernel(const float* __restrict__ l1_part, int n_l1, con
                                 float* __restrict__ bias_mu, float* __restrict__ bias_nu,
                                 const float* __restrict__ l1_alpha, const float* __restrict__ bias_decay,
                                 float* __restrict__ out_losses, int M, int B, int d, int N, int tied, AdamConst a,
-                                float* __restrict__ grad_bias, float* __restrict__ bnorm_ws) {
+                                float* __restrict__ grad_bias, float* __restrict__ bnorm_ws, float db_scale) {
     // grid (ceil(N/256), M).  Every block needs ||b|| of the PRE-update bias: block x == 0 of each member
     // computed it into bnorm_ws in bias_norm_kernel (launched before), so no block reads a bias another
     // block already updated.
@@ -134,6 +134,7 @@ __global__ void finalize_kernel(const float* __restrict__ l1_part, int n_l1, con
     if (n < N) {
         float g = 0.f;
         for (int t = 0; t < tiles_b; ++t) g += db_part[((long long)m * tiles_b + t) * N + n];
+        g *= db_scale;
         const long long o = (long long)m * N + n;
         float p = bias[o];
         g += bscale * p;
@@ -216,6 +217,8 @@ static int check_ptr(const void* p, const char* name) {
     return 0;
 }
 
+int sae_step_f16_impl(const ScStepArgs& a);
+
 static int sae_step_impl(const ScStepArgs& a) {
     const int M = a.M, B = a.B, d = a.d, N = a.N;
     if (M <= 0 || B <= 0 || d <= 0 || N <= 0) return fail(-1, "M, B, d, N must be positive (got %d %d %d %d)", M, B, d, N);
@@ -224,9 +227,12 @@ static int sae_step_impl(const ScStepArgs& a) {
     SC_TRY(check_ptr(a.enc, "enc")); SC_TRY(check_ptr(a.enc_mu, "enc_mu")); SC_TRY(check_ptr(a.enc_nu, "enc_nu"));
     SC_TRY(check_ptr(a.bias, "bias")); SC_TRY(check_ptr(a.bias_mu, "bias_mu")); SC_TRY(check_ptr(a.bias_nu, "bias_nu"));
     if (!a.tied) { SC_TRY(check_ptr(a.dec, "dec")); SC_TRY(check_ptr(a.dec_mu, "dec_mu")); SC_TRY(check_ptr(a.dec_nu, "dec_nu")); }
-    SC_TRY(check_ptr(a.out_c, "out_c")); SC_TRY(check_ptr(a.workspace, "workspace"));
+    if (a.operand_format == 0) SC_TRY(check_ptr(a.out_c, "out_c"));
+    SC_TRY(check_ptr(a.workspace, "workspace"));
     if (!a.l1_alpha || !a.bias_decay || !a.out_losses) return fail(-1, "l1_alpha / bias_decay / out_losses is NULL");
     if (reinterpret_cast<uintptr_t>(a.workspace) & 1023) return fail(-1, "workspace must be 1024-byte aligned");
+    if (a.operand_format == 1) return sae_step_f16_impl(a);
+    if (a.operand_format != 0) return fail(-1, "unknown operand_format %d", a.operand_format);
     const StepWs w = carve_step(a.workspace, M, B, d, N, a.tied, a.x_per_member);
     if (a.workspace_bytes < w.bytes)
         return fail(-1, "workspace too small: %zu bytes given, %zu needed", a.workspace_bytes, w.bytes);
@@ -284,7 +290,7 @@ static int sae_step_impl(const ScStepArgs& a) {
     // 6/7. weight gradients with fused Adam                          [N x d], K = B
     {
         EpiAdam::Params e{};
-        e.tiles_b = w.tiles_b; e.a = ad;
+        e.tiles_b = w.tiles_b; e.a = ad; e.g_scale = 1.0f;
         auto fill = [&](EpiAdam::Sub& u, float* p, float* mu, float* nu, float* grad, bool projected) -> int {
             SC_TRY(io_map(&u.p_map, p, N, d, M, Nd));
             SC_TRY(io_map(&u.mu_map, mu, N, d, M, Nd));
@@ -317,7 +323,7 @@ static int sae_step_impl(const ScStepArgs& a) {
     finalize_kernel<<<dim3(ceil_div(N, 256), M), 256, 0, st>>>(w.l1_part, w.n_l1, w.mse_part, w.n_mse, w.db_part, w.tiles_b,
                                                              a.bias, a.bias_mu, a.bias_nu, a.l1_alpha, a.bias_decay,
                                                              a.out_losses, M, Bn, d, N, a.tied, ad,
-                                                             grad_mode ? a.grad_bias : nullptr, w.bnorm);
+                                                             grad_mode ? a.grad_bias : nullptr, w.bnorm, 1.0f);
     SC_CUDA(cudaGetLastError(), "finalize launch");
     prof_mark(st, "finalize");
     return 0;

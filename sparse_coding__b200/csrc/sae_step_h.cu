@@ -1,0 +1,201 @@
+// fp16-operand mode of sc_sae_step (ScStepArgs.operand_format == 1): same eight launches, GEMM operands
+// and the intermediate tensors c / r / dz in fp16 (see sae_epilogues_h.cuh for the scaling), master
+// weights, Adam state, accumulators and all loss arithmetic in fp32.  Needs the CTA-pair kernel, d and N
+// multiples of 64 and >= 128, B > 64 (sc_sae_step_f16_supported); other shapes use the TF32 mode.
+#include "../../include/sc_b200.h"
+#include "host_common.cuh"
+#include "sae_epilogues_h.cuh"
+
+namespace sc {
+
+__global__ void to_half_kernel(const float4* __restrict__ in, uint2* __restrict__ out, long long n4) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+        const float4 v = in[i];
+        __half2 h[2] = {__floats2half2_rn(v.x, v.y), __floats2half2_rn(v.z, v.w)};
+        out[i] = *reinterpret_cast<uint2*>(h);
+    }
+}
+
+__global__ void half_to_float_kernel(const uint2* __restrict__ in, float4* __restrict__ out, long long n4) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+        uint2 u = in[i];
+        const __half2* h = reinterpret_cast<const __half2*>(&u);
+        const float2 a = __half22float2(h[0]), b = __half22float2(h[1]);
+        out[i] = make_float4(a.x, a.y, b.x, b.y);
+    }
+}
+
+// one warp per dictionary row: enc_h = half(enc), D_h = half(W / max(||W||,1e-8)), inv_norm as in prep_params_kernel
+__global__ void prep_params_h_kernel(const float* __restrict__ enc, __half* __restrict__ enc_h,
+                                     const float* __restrict__ W, __half* __restrict__ D_h,
+                                     float* __restrict__ inv_norm, int N, int d) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n = blockIdx.x * 8 + warp;
+    if (n >= N) return;
+    const long long row = ((long long)blockIdx.y * N + n) * d;
+    const int d4 = d >> 2;
+    if (enc_h) {
+        const float4* src = reinterpret_cast<const float4*>(enc + row);
+        uint2* dst = reinterpret_cast<uint2*>(enc_h + row);
+        for (int i = lane; i < d4; i += 32) {
+            const float4 v = src[i];
+            __half2 h[2] = {__floats2half2_rn(v.x, v.y), __floats2half2_rn(v.z, v.w)};
+            dst[i] = *reinterpret_cast<uint2*>(h);
+        }
+    }
+    const float4* src = reinterpret_cast<const float4*>(W + row);
+    float ss = 0.f;
+    for (int i = lane; i < d4; i += 32) {
+        const float4 v = src[i];
+        ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+    }
+    ss = warp_sum(ss);
+    const float nrm = sqrtf(ss);
+    const float inv = 1.f / fmaxf(nrm, 1e-8f);
+    if (lane == 0) inv_norm[(long long)blockIdx.y * N + n] = nrm < 1e-8f ? -inv : inv;
+    uint2* dst = reinterpret_cast<uint2*>(D_h + row);
+    for (int i = lane; i < d4; i += 32) {
+        const float4 v = src[i];
+        __half2 h[2] = {__floats2half2_rn(v.x * inv, v.y * inv), __floats2half2_rn(v.z * inv, v.w * inv)};
+        dst[i] = *reinterpret_cast<uint2*>(h);
+    }
+}
+
+struct StepWsH {
+    __half *x_h, *enc_h, *D_h, *r_h, *dz_h;
+    float *inv_norm, *l1_part, *mse_part, *db_part, *s_part, *bnorm;
+    int n_l1, n_mse, tiles_b;
+    size_t bytes;
+};
+
+static StepWsH carve_step_h(void* base, int M, int B, int d, int N, int tied, int xpm) {
+    StepWsH w;
+    Carver c(base);
+    const size_t Mz = M, Bz = B, dz_ = d, Nz = N;
+    auto halves = [&](size_t n) { return reinterpret_cast<__half*>(c.floats((n + 1) / 2)); };
+    w.x_h = halves((xpm ? Mz : 1) * Bz * dz_);
+    w.enc_h = tied ? nullptr : halves(Mz * Nz * dz_);
+    w.D_h = halves(Mz * Nz * dz_);
+    w.inv_norm = c.floats(Mz * Nz);
+    w.r_h = halves(Mz * Bz * dz_);
+    w.dz_h = halves(Mz * Bz * Nz);
+    w.n_l1 = row_tiles128(B) * ceil_div(N, pick_bn(N)) * 4 * kEpiHalves;
+    w.n_mse = row_tiles128(B) * ceil_div(d, pick_bn(d)) * 4 * kEpiHalves;
+    w.tiles_b = ceil_div(B, pick_bn(B)) * kEpiHalves;
+    w.l1_part = c.floats(Mz * w.n_l1);
+    w.mse_part = c.floats(Mz * w.n_mse);
+    w.db_part = c.floats(Mz * w.tiles_b * Nz);
+    w.s_part = c.floats(Mz * w.tiles_b * Nz);
+    w.bnorm = c.floats(Mz);
+    w.bytes = c.off;
+    return w;
+}
+
+static bool f16_supported(int B, int d, int N) {
+    return use_cta_pairs() && d >= 128 && N >= 128 && (d % 64) == 0 && (N % 64) == 0 && B > 64;
+}
+
+static int io_map_h(CUtensorMap* out, const void* base, long long rows, long long cols, long long g, long long gstride) {
+    const char* err = nullptr;
+    const int rc = make_io_map_h(out, base, rows, cols, g, gstride, &err);
+    if (rc != 0) return fail(rc, "%s", err ? err : "io tensor map creation failed");
+    return 0;
+}
+
+static int grid1d(long long n4) { return static_cast<int>(n4 / 256 + 1 < 4096 ? n4 / 256 + 1 : 4096); }
+
+int sae_step_f16_impl(const ScStepArgs& a) {
+    const int M = a.M, B = a.B, d = a.d, N = a.N;
+    if (!f16_supported(B, d, N))
+        return fail(-1, "fp16 operand mode needs the CTA-pair kernels, d and N multiples of 64 and >= 128, B > 64 "
+                        "(got B=%d d=%d N=%d); use operand_format 0", B, d, N);
+    if (!a.out_c_half) return fail(-1, "out_c_half is NULL in fp16 operand mode");
+    if (reinterpret_cast<uintptr_t>(a.out_c_half) & 15) return fail(-1, "out_c_half is not 16-byte aligned");
+    const StepWsH w = carve_step_h(a.workspace, M, B, d, N, a.tied, a.x_per_member);
+    if (a.workspace_bytes < w.bytes) return fail(-1, "workspace too small: %zu bytes given, %zu needed", a.workspace_bytes, w.bytes);
+    cudaStream_t st = static_cast<cudaStream_t>(a.stream);
+    const AdamConst ad = make_adam(a.adam);
+    const int xg = a.x_per_member ? M : 1;
+    const int Bn = a.B_total > 0 ? a.B_total : B;
+    const bool grad_mode = a.grad_enc != nullptr;
+    const long long Bd = (long long)B * d, BN_ = (long long)B * N, Nd = (long long)N * d;
+    const float sc_ = 2.0f / ((float)Bn * (float)d);
+    __half* c_h = static_cast<__half*>(a.out_c_half);
+
+    prof_mark(st, "begin");
+    to_half_kernel<<<grid1d(xg * Bd / 4), 256, 0, st>>>(reinterpret_cast<const float4*>(a.x), reinterpret_cast<uint2*>(w.x_h), xg * Bd / 4);
+    prof_mark(st, "round_x");
+    {
+        dim3 grid(ceil_div(N, 8), M);
+        if (a.tied) prep_params_h_kernel<<<grid, 256, 0, st>>>(nullptr, nullptr, a.enc, w.D_h, w.inv_norm, N, d);
+        else prep_params_h_kernel<<<grid, 256, 0, st>>>(a.enc, w.enc_h, a.dec, w.D_h, w.inv_norm, N, d);
+        SC_CUDA(cudaGetLastError(), "prep launch");
+    }
+    prof_mark(st, "prep_params");
+    {   // G1
+        Seg s{kmajor_h(w.x_h, B, d, xg, Bd), kmajor_h(a.tied ? w.D_h : w.enc_h, N, d, M, Nd)};
+        EpiEncodeH::Params ep{};
+        SC_TRY(io_map_h(&ep.c_map, c_h, B, N, M, BN_));
+        ep.bias = a.bias; ep.l1_part = w.l1_part;
+        SC_TRY((run_gemm<false, false, EpiEncodeH, true>(B, N, M, &s, 1, ep, st)));
+    }
+    prof_mark(st, "G1_encode");
+    {   // G2
+        Seg s{kmajor_h(c_h, B, N, M, BN_), mnmajor_h(w.D_h, d, N, M, Nd)};
+        EpiDecodeH::Params ep{a.x, w.r_h, w.mse_part, a.x_per_member ? Bd : 0, Bd};
+        SC_TRY((run_gemm<false, true, EpiDecodeH, true>(B, d, M, &s, 1, ep, st)));
+    }
+    prof_mark(st, "G2_decode_mse");
+    {   // G3 (transposed)
+        Seg s{kmajor_h(w.D_h, N, d, M, Nd), kmajor_h(w.r_h, B, d, M, Bd)};
+        EpiBackCodeH::Params ep{c_h, w.dz_h, a.l1_alpha, a.bias, w.db_part, w.s_part, BN_, 0.5f * (float)d, a.tied, N};
+        SC_TRY((run_gemm<false, false, EpiBackCodeH, true>(N, B, M, &s, 1, ep, st)));
+    }
+    prof_mark(st, "G3_back_code");
+    {
+        EpiAdam::Params e{};
+        e.tiles_b = w.tiles_b; e.a = ad; e.g_scale = sc_;
+        auto fill = [&](EpiAdam::Sub& u, float* p, float* mu, float* nu, float* grad, bool projected) -> int {
+            SC_TRY(io_map(&u.p_map, p, N, d, M, Nd));
+            SC_TRY(io_map(&u.mu_map, mu, N, d, M, Nd));
+            SC_TRY(io_map(&u.nu_map, nu, N, d, M, Nd));
+            SC_TRY(io_map(&u.grad_map, grad ? grad : p, N, d, M, Nd));
+            u.s_part = projected ? w.s_part : nullptr;
+            u.inv_norm = projected ? w.inv_norm : nullptr;
+            u.projected = projected ? 1 : 0;
+            u.grad_only = grad ? 1 : 0;
+            return 0;
+        };
+        if (!a.tied) {
+            Seg s45[2] = {{mnmajor_h(w.dz_h, N, B, M, BN_), mnmajor_h(w.x_h, d, B, xg, Bd)},
+                          {mnmajor_h(c_h, N, B, M, BN_), mnmajor_h(w.r_h, d, B, M, Bd)}};
+            SC_TRY(fill(e.sub[0], a.enc, a.enc_mu, a.enc_nu, a.grad_enc, false));
+            SC_TRY(fill(e.sub[1], a.dec, a.dec_mu, a.dec_nu, grad_mode ? a.grad_dec : nullptr, true));
+            SC_TRY((run_gemm<true, true, EpiAdam, true>(N, d, M, s45, 2, e, st, true)));
+        } else {
+            Seg s[2] = {{mnmajor_h(c_h, N, B, M, BN_), mnmajor_h(w.r_h, d, B, M, Bd)},
+                        {mnmajor_h(w.dz_h, N, B, M, BN_), mnmajor_h(w.x_h, d, B, xg, Bd)}};
+            SC_TRY(fill(e.sub[0], a.enc, a.enc_mu, a.enc_nu, a.grad_enc, true));
+            e.sub[1] = e.sub[0];
+            SC_TRY((run_gemm<true, true, EpiAdam, true>(N, d, M, s, 2, e, st)));
+        }
+    }
+    prof_mark(st, "G45_dW_adam");
+    bias_norm_kernel<<<M, 256, 0, st>>>(a.bias, N, w.bnorm);
+    finalize_kernel<<<dim3(ceil_div(N, 256), M), 256, 0, st>>>(w.l1_part, w.n_l1, w.mse_part, w.n_mse, w.db_part, w.tiles_b,
+                                                             a.bias, a.bias_mu, a.bias_nu, a.l1_alpha, a.bias_decay,
+                                                             a.out_losses, M, Bn, d, N, a.tied, ad,
+                                                             grad_mode ? a.grad_bias : nullptr, w.bnorm, sc_);
+    SC_CUDA(cudaGetLastError(), "finalize launch");
+    prof_mark(st, "finalize");
+    if (a.out_c) {  // caller wants the fp32 aux tensor as well
+        half_to_float_kernel<<<grid1d(M * BN_ / 4), 256, 0, st>>>(reinterpret_cast<const uint2*>(c_h),
+                                                               reinterpret_cast<float4*>(a.out_c), M * BN_ / 4);
+        SC_CUDA(cudaGetLastError(), "c conversion launch");
+    }
+    return 0;
+}
+
+}  // namespace sc
+
+extern "C" int sc_sae_step_f16_supported(int32_t B, int32_t d, int32_t N) { return sc::f16_supported(B, d, N) ? 1 : 0; }

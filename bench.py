@@ -127,7 +127,7 @@ class ClockSampler:
                         self.reasons.add(nm)
             except Exception:
                 pass
-            time.sleep(0.05)
+            time.sleep(0.02)
 
     def __enter__(self):
         self.t.start()
@@ -194,11 +194,40 @@ def run_ours(args):
         s = i % n_slices
         return ens.step_batch(chunk[s * B:(s + 1) * B])
 
-    def e2e_step(i):
-        s = i % n_slices
-        x = host_chunk[s * B:(s + 1) * B].to(device, non_blocking=True)
-        losses, _ = ens.step_batch(x)
-        return losses["loss"].cpu()
+    # End-to-end loop as a user would write it: the batch lives in pinned host memory, is copied to the
+    # device on a side stream one step ahead (double buffered), and every step's loss vector is copied back
+    # to pinned host memory and read on the host one step late (so the host never stalls the GPU).
+    copy_stream = torch.cuda.Stream(device=device)
+    dev_batch = [torch.empty(B, D_ACT, device=device) for _ in range(2)]
+    host_loss = [torch.empty(M, dtype=torch.float32).pin_memory() for _ in range(2)]
+    ready = [torch.cuda.Event() for _ in range(2)]
+    done = [torch.cuda.Event() for _ in range(2)]
+    seen = {"sum": 0.0}
+
+    def e2e_prefetch(i):
+        s, b = i % n_slices, i % 2
+        with torch.cuda.stream(copy_stream):
+            copy_stream.wait_event(done[b])  # the step that last used this buffer has finished
+            dev_batch[b].copy_(host_chunk[s * B:(s + 1) * B], non_blocking=True)
+            ready[b].record(copy_stream)
+
+    def e2e_run(n):
+        cur = torch.cuda.current_stream(device)
+        for b in range(2):
+            done[b].record(cur)
+        e2e_prefetch(0)
+        for i in range(n):
+            b = i % 2
+            cur.wait_event(ready[b])
+            losses, _ = ens.step_batch(dev_batch[b])
+            host_loss[b].copy_(losses["loss"], non_blocking=True)
+            done[b].record(cur)
+            e2e_prefetch(i + 1)
+            if i > 0:
+                done[1 - b].synchronize()  # previous step's loss is on the host now
+                seen["sum"] += float(host_loss[1 - b].sum())
+        done[(n - 1) % 2].synchronize()
+        seen["sum"] += float(host_loss[(n - 1) % 2].sum())
 
     for i in range(args.warmup):
         device_step(i)
@@ -225,12 +254,10 @@ def run_ours(args):
         return
 
     # end to end: pinned host batch -> device, loss scalars -> host, every step
-    for i in range(min(args.warmup, 5)):
-        e2e_step(i)
+    e2e_run(min(args.warmup, 5))
     barrier()
     t0 = time.perf_counter()
-    for i in range(args.steps):
-        e2e_step(i)
+    e2e_run(args.steps)
     barrier()
     t = torch.tensor([time.perf_counter() - t0], device=device)
     if world > 1:
@@ -257,9 +284,12 @@ def run_ours(args):
     # per launch: G1/G2/G3 are one GEMM of 2*B*N*d*M flops, G45 batches the two weight-gradient GEMMs
     launch_flops = {k: gemm_flops * (2.0 if k.startswith("G45") else 1.0) for k in gemms}
     # algorithmic HBM bytes per launch: codes / dz / Adam state dominate
-    MBN, MNd, MBd, Bd = 4.0 * M * B * N_FEATS, 4.0 * M * N_FEATS * D_ACT, 4.0 * M * B * D_ACT, 4.0 * B * D_ACT
-    launch_bytes = {"G1_encode": MBN + MNd + Bd, "G2_decode_mse": MBN + MNd + MBd + Bd, "G3_back_code": 2 * MBN + MNd + MBd,
-                    "G45_dW_adam": 2 * MBN + 12 * MNd + MBd + Bd}
+    fmt = getattr(ens, "last_operand_format", "tf32")
+    eb = 2.0 if fmt == "f16" else 4.0  # bytes per element of the GEMM operands / intermediates c, r, dz
+    MBN, MNd, MBd, Bd = eb * M * B * N_FEATS, eb * M * N_FEATS * D_ACT, eb * M * B * D_ACT, eb * B * D_ACT
+    adam_bytes = 2 * 6 * 4.0 * M * N_FEATS * D_ACT  # encoder + decoder: read and write p, mu, nu in fp32
+    launch_bytes = {"G1_encode": MBN + MNd + Bd, "G2_decode_mse": MBN + MNd + MBd + 4.0 * B * D_ACT,
+                    "G3_back_code": 2 * MBN + MNd + MBd, "G45_dW_adam": 2 * MBN + adam_bytes + MBd + Bd}
     tf32_peak = measure_tf32_peak(device)
     peaks = {}
     try:
@@ -275,10 +305,17 @@ def run_ours(args):
             traffic = {}
     except Exception:
         pass
+    if fmt == "f16":
+        tensor_peak = float(peaks.get("bf16_tflops_sustained", peaks.get("bf16_tflops", 1400.0)))
+        tensor_src = ("MEASURED_PEAKS.json bf16_tflops_sustained (16-bit dense peak; kernels timed inside a long step, "
+                      "kind::f16)") if peaks else "1400 TFLOP/s 16-bit sustained (of fallback)"
+    else:
+        tensor_peak = tf32_peak
+        tensor_src = "measured here: torch.matmul TF32 8192^3 best of 10 (MEASURED_PEAKS.json has bf16 only; kind::tf32)"
     per_kernel = {}
     for k in gemms:
         t = gemms[k] * 1e-3
-        t_tensor = launch_flops[k] / (tf32_peak * 1e12)
+        t_tensor = launch_flops[k] / (tensor_peak * 1e12)
         t_hbm = launch_bytes.get(k, 0.0) / (hbm_peak * 1e9)
         bound = "tensor" if t_tensor >= t_hbm else "hbm"
         per_kernel[k] = {"ms": gemms[k], "tflops": launch_flops[k] / t / 1e12, "alg_GBps": launch_bytes.get(k, 0.0) / t / 1e9,
@@ -290,14 +327,13 @@ def run_ours(args):
     roofline = {
         "kernel": dom, "bound": dk["bound"],
         "achieved": dk["tflops"] if dk["bound"] == "tensor" else dk["alg_GBps"],
-        "peak": tf32_peak if dk["bound"] == "tensor" else hbm_peak,
+        "peak": tensor_peak if dk["bound"] == "tensor" else hbm_peak,
         "unit": "TFLOP/s" if dk["bound"] == "tensor" else "GB/s",
         "frac": dk["frac"], "traffic": dk["ncu_dram_bytes"],
-        "peak_source": ("tensor peak measured here: torch.matmul TF32 8192^3 best of 10 (MEASURED_PEAKS.json has bf16 only; "
-                        "the kernels run kind::tf32); hbm peak: " + hbm_src),
-        "tf32_peak_tflops": tf32_peak, "hbm_peak_GBps": hbm_peak, "bf16_peak_measured": peaks.get("bf16_tflops"),
+        "peak_source": "tensor peak: " + tensor_src + "; hbm peak: " + hbm_src,
+        "operand_format": fmt, "tensor_peak_tflops": tensor_peak, "tf32_peak_tflops": tf32_peak, "hbm_peak_GBps": hbm_peak, "bf16_peak_measured": peaks.get("bf16_tflops"),
         "step_tflops": step_flops / (ms_step * 1e-3) / 1e12,
-        "step_frac_of_tf32_peak": step_flops / (ms_step * 1e-3) / 1e12 / tf32_peak,
+        "step_frac_of_tensor_peak": step_flops / (ms_step * 1e-3) / 1e12 / tensor_peak,
         "kernels": per_kernel, "kernel_ms": kernel_ms,
     }
 
@@ -309,10 +345,12 @@ def run_ours(args):
 
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "tf32",
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": fmt,
         "data": "synthetic",
         "config": {"workload": "pythia70m_l2_untied_sae", "d": D_ACT, "n_feats": N_FEATS, "members_per_gpu": M,
-                   "batch": B, "optimizer": "adam lr=1e-3 (reference-faithful t=1)", "parallelism": f"ensemble-shard x{world}",
+                   "batch": B, "optimizer": "adam lr=1e-3 (reference-faithful t=1)",
+                   "precision": ("fp16 GEMM operands (11-bit significand, same as TF32), fp32 accumulate / weights / Adam"
+                                 if fmt == "f16" else "TF32 GEMM operands, fp32 accumulate / weights / Adam"), "parallelism": f"ensemble-shard x{world}",
                    "l2_policy": f"inputs larger than L2: {n_slices} batch slices = {n_slices * B * D_ACT * 4 >> 20} MiB chunk, "
                                 "working set per step > 1 GB"},
         "activations_per_sec": value / (M * world) ,
@@ -328,8 +366,8 @@ def run_ours(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=100)
-    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=400)
+    ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--batch", type=int, default=2048)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--quick", action="store_true", help="profiling runs: skip e2e, peak measurement and the CPU baseline")

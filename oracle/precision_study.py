@@ -28,13 +28,22 @@ def rn_bf16(t):
     return t.to(torch.bfloat16).to(torch.float32)
 
 
-FMT = {"fp32": lambda t: t, "tf32_rn": rn_tf32, "tf32_trunc": trunc_tf32, "bf16_rn": rn_bf16}
+def rn_fp16(t):
+    return t.to(torch.float16).to(torch.float32)
 
 
-def step(P, S, lam, x, lr, q):
+FMT = {"fp32": lambda t: t, "tf32_rn": rn_tf32, "tf32_trunc": trunc_tf32, "bf16_rn": rn_bf16, "fp16_rn": rn_fp16}
+# fp16 has a narrow exponent: the engine's fp16 mode stores the residual r (not R = 2r/(B d)) and the
+# correspondingly scaled dz, and applies 2/(B d) in fp32 afterwards - emulated the same way below.
+UNSCALED_RESIDUAL = {"fp16_rn"}
+
+
+def step(P, S, lam, x, lr, q, unscaled=False):
     """one untied member step with operand rounding q (explicit formulas of restated.sae_*)"""
     We, b, Wd = P
     B, d = x.shape
+    if unscaled:
+        return step_unscaled(P, S, lam, x, lr, q)
     z = q(x) @ q(We).T + b
     c = torch.clamp(z, min=0)
     D, cl = R.row_normalise(Wd)
@@ -48,6 +57,29 @@ def step(P, S, lam, x, lr, q):
     gb = dz.sum(0)
     gD = q(c).T @ q(Rm)
     s = (c * qq).sum(0)
+    gWd = (gD - s[:, None] * D) / cl[:, None]
+    for p, g, (mu, nu) in zip(P, (gWe, gb, gWd), S):
+        R.adam_step_(p, g, mu, nu, lr)
+    l0 = (c != 0).float().sum(-1).mean()
+    fvu = (r * r).mean() / ((x - x.mean(0)) ** 2).mean()
+    return float(l_rec + l_l1), float(l_rec), float(l_l1), float(l0), float(fvu)
+
+
+def step_unscaled(P, S, lam, x, lr, q):
+    We, b, Wd = P
+    B, d = x.shape
+    z = q(x) @ q(We).T + b
+    c = torch.clamp(z, min=0)
+    D, cl = R.row_normalise(Wd)
+    r = q(c) @ q(D) - x
+    l_rec = (r * r).mean(); l_l1 = lam * c.sum(-1).mean()
+    sc = 2.0 / (B * d)
+    qq = q(r) @ q(D).T                                   # q / sc
+    dz = (qq + lam / B / sc * (c > 0).float()) * (z >= 0).float()
+    gWe = (q(dz).T @ q(x)) * sc
+    gb = dz.sum(0) * sc
+    gD = (q(c).T @ q(r)) * sc
+    s = (c * qq).sum(0) * sc
     gWd = (gD - s[:, None] * D) / cl[:, None]
     for p, g, (mu, nu) in zip(P, (gWe, gb, gWd), S):
         R.adam_step_(p, g, mu, nu, lr)
@@ -77,7 +109,7 @@ def main(d=256, N=1024, B=1024, steps=100, lam=1e-3):
         g2 = torch.Generator().manual_seed(1)
         for i in range(steps):
             idx = torch.randint(0, data.shape[0], (B,), generator=g2)
-            out.append(step(P, S, lam, data[idx], 1e-3, q))
+            out.append(step(P, S, lam, data[idx], 1e-3, q, name in UNSCALED_RESIDUAL))
         traj[name] = np.array(out)
     ref = traj["fp32"]
     print(f"d={d} N={N} B={B} steps={steps} lam={lam}; final fp32: loss={ref[-1,0]:.5f} L0={ref[-1,3]:.1f} FVU={ref[-1,4]:.4f}")

@@ -342,6 +342,7 @@ class FunctionalEnsemble:
         f16 = fmt != "tf32" and bool(L.sc_sae_step_f16_supported(B, d, N))
         if fmt == "f16" and not f16:
             raise ValueError(f"operand_format 'f16' needs d, N multiples of 64 and >= 128 and B > 64 (got B={B} d={d} N={N})")
+        self.last_operand_format = "f16" if f16 else "tf32"
         losses = torch.empty((4, M), dtype=torch.float32, device=x.device)
         c = None if f16 else torch.empty((M, B, N), dtype=torch.float32, device=x.device)
         c_half = torch.empty((M, B, N), dtype=torch.float16, device=x.device) if f16 else None

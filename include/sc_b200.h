@@ -73,6 +73,10 @@ typedef struct {
      * (when given it is filled from the fp16 codes).  Inputs with |x| > 65504 overflow fp16: use format 0. */
     int32_t operand_format;
     void* out_c_half;
+    /* Masked ensembles (FunctionalMaskedSAE / FunctionalMaskedTiedSAE, sae_ensemble.py:307-442): member m only
+     * uses its first dict_size[m] features; the rest produce zero codes and zero gradients.  [M] int32 on the
+     * device, or NULL for unmasked. */
+    const int32_t* dict_size;
 } ScStepArgs;
 
 size_t sc_sae_step_workspace_bytes(int32_t M, int32_t B, int32_t d, int32_t N, int32_t tied, int32_t x_per_member);

@@ -39,10 +39,14 @@ def row_normalise(W: Tensor) -> Tuple[Tensor, Tensor]:
     return W / cl[:, None], cl
 
 
-def sae_forward(We: Tensor, b: Tensor, Wd: Tensor, lam, beta, x: Tensor):
-    """FunctionalSAE.loss forward, sae_ensemble.py:53-77."""
+def sae_forward(We: Tensor, b: Tensor, Wd: Tensor, lam, beta, x: Tensor, mask: Optional[Tensor] = None):
+    """FunctionalSAE.loss forward, sae_ensemble.py:53-77.  With `mask` ([N] bool, True = unused feature) it is
+    FunctionalMaskedSAE.loss, :409-438 (codes of unused features zeroed; that loss has no bias-decay term, so
+    callers pass beta = 0)."""
     z = x @ We.T + b                       # :54-55
     c = torch.clamp(z, min=0.0)            # :56
+    if mask is not None:
+        c = c.masked_fill(mask, 0.0)       # :425
     D, cl = row_normalise(Wd)              # :58-59
     x_hat = c @ D                          # :61
     r = x_hat - x
@@ -51,7 +55,7 @@ def sae_forward(We: Tensor, b: Tensor, Wd: Tensor, lam, beta, x: Tensor):
     bn = torch.sqrt((b * b).sum())
     l_bd = beta * bn                       # :64
     losses = {"loss": l_rec + l_l1 + l_bd, "l_reconstruction": l_rec, "l_l1": l_l1, "l_bias_decay": l_bd}
-    return losses, dict(z=z, c=c, D=D, cl=cl, r=r, bn=bn)
+    return losses, dict(z=z, c=c, D=D, cl=cl, r=r, bn=bn, mask=mask)
 
 
 def sae_backward(We, b, Wd, lam, beta, x, fw):
@@ -64,6 +68,8 @@ def sae_backward(We, b, Wd, lam, beta, x, fw):
     R = r * (2.0 / (B * d))
     q = R @ D.T                                               # dL/dc from the MSE term
     dz = (q + (lam / B) * (c > 0).to(x.dtype)) * (z >= 0).to(x.dtype)
+    if fw.get("mask") is not None:
+        dz = dz.masked_fill(fw["mask"], 0.0)                  # masked_fill_ blocks the gradient
     gWe = dz.T @ x
     gb = dz.sum(0)
     if float(fw["bn"]) > 0.0:
@@ -91,13 +97,15 @@ def tied_uncenter(rot, trans, scale, xc):
     return (xc / scale[None, :]) @ rot + trans[None, :]
 
 
-def tied_forward(W, b, lam, beta, x, rot=None, trans=None, scale=None):
+def tied_forward(W, b, lam, beta, x, rot=None, trans=None, scale=None, mask=None):
     """FunctionalTiedSAE.loss forward, sae_ensemble.py:134-160.  `loss_data` has
     no l_bias_decay key (:150-154) although the total includes it (:160)."""
     D, cl = row_normalise(W)                                   # :135-136
     xc = x if rot is None else tied_center(rot, trans, scale, x)  # :138
     z = xc @ D.T + b                                           # :140-141
     c = torch.clamp(z, min=0.0)                                # :142
+    if mask is not None:
+        c = c.masked_fill(mask, 0.0)                           # FunctionalMaskedTiedSAE, :356
     x_hat_c = c @ D                                            # :144
     r = x_hat_c - xc
     l_rec = (r * r).mean()                                     # :146
@@ -105,7 +113,7 @@ def tied_forward(W, b, lam, beta, x, rot=None, trans=None, scale=None):
     bn = torch.sqrt((b * b).sum())
     l_bd = beta * bn                                           # :148
     losses = {"loss": l_rec + l_l1 + l_bd, "l_reconstruction": l_rec, "l_l1": l_l1}
-    return losses, dict(z=z, c=c, D=D, cl=cl, r=r, bn=bn, xc=xc)
+    return losses, dict(z=z, c=c, D=D, cl=cl, r=r, bn=bn, xc=xc, mask=mask)
 
 
 def tied_backward(W, b, lam, beta, x, fw):
@@ -114,6 +122,8 @@ def tied_backward(W, b, lam, beta, x, fw):
     R = r * (2.0 / (B * d))
     q = R @ D.T
     dz = (q + (lam / B) * (c > 0).to(x.dtype)) * (z >= 0).to(x.dtype)
+    if fw.get("mask") is not None:
+        dz = dz.masked_fill(fw["mask"], 0.0)
     gD = c.T @ R + dz.T @ xc                                   # decode + encode use the same D
     s = (gD * D).sum(-1)
     gW = (gD - s[:, None] * D) / cl[:, None]
@@ -169,18 +179,27 @@ class EnsembleOracle:
         for m in range(self.M):
             xm = x if expand_dims else x[m]
             lam, beta = Bf["l1_alpha"][m], Bf["bias_decay"][m]
-            if self.tied:
+            mask = Bf["coef_mask"][m] if "coef_mask" in Bf else None
+            if mask is not None:
+                beta = 0.0  # the masked losses have no bias-decay term (sae_ensemble.py:360, :429)
+            if self.tied and mask is not None:
+                losses, fw = tied_forward(P["encoder"][m], P["encoder_bias"][m], lam, beta, xm, mask=mask)
+                gW, gb = tied_backward(P["encoder"][m], P["encoder_bias"][m], lam, beta, xm, fw)
+                grads = {"encoder": gW, "encoder_bias": gb}
+            elif self.tied:
                 ident = _is_identity_centering(Bf, m)
                 args = (None, None, None) if ident else (Bf["center_rot"][m], Bf["center_trans"][m], Bf["center_scale"][m])
                 losses, fw = tied_forward(P["encoder"][m], P["encoder_bias"][m], lam, beta, xm, *args)
                 gW, gb = tied_backward(P["encoder"][m], P["encoder_bias"][m], lam, beta, xm, fw)
                 grads = {"encoder": gW, "encoder_bias": gb}
             else:
-                losses, fw = sae_forward(P["encoder"][m], P["encoder_bias"][m], P["decoder"][m], lam, beta, xm)
+                losses, fw = sae_forward(P["encoder"][m], P["encoder_bias"][m], P["decoder"][m], lam, beta, xm, mask)
                 gWe, gb, gWd = sae_backward(P["encoder"][m], P["encoder_bias"][m], P["decoder"][m], lam, beta, xm, fw)
                 grads = {"encoder": gWe, "encoder_bias": gb, "decoder": gWd}
             for k, g in grads.items():
                 adam_step_(P[k][m], g, self.mu[k][m], self.nu[k][m], self.lr, self.b1, self.b2, self.eps, 0.0, t)
+            if mask is not None:
+                losses = {k: losses[k] for k in ("loss", "l_reconstruction", "l_l1")}
             for k, v in losses.items():
                 out.setdefault(k, []).append(v)
             cs.append(fw["c"])

@@ -12,12 +12,12 @@ from .autoencoders import ensemble, fista, learned_dict, sae_ensemble
 from .autoencoders.ensemble import FunctionalEnsemble
 from .autoencoders.fista import Fista, FunctionalFista
 from .autoencoders.learned_dict import LearnedDict, TiedSAE, UntiedSAE
-from .autoencoders.sae_ensemble import FunctionalSAE, FunctionalTiedSAE
+from .autoencoders.sae_ensemble import FunctionalMaskedSAE, FunctionalMaskedTiedSAE, FunctionalSAE, FunctionalTiedSAE
 from . import big_sweep, standard_metrics, torchopt_compat
 from .big_sweep import ensemble_train_loop, unstacked_to_learned_dicts
 
 __all__ = [
-    "FunctionalEnsemble", "FunctionalSAE", "FunctionalTiedSAE", "FunctionalFista", "Fista", "LearnedDict", "UntiedSAE",
+    "FunctionalEnsemble", "FunctionalSAE", "FunctionalTiedSAE", "FunctionalMaskedSAE", "FunctionalMaskedTiedSAE", "FunctionalFista", "Fista", "LearnedDict", "UntiedSAE",
     "TiedSAE", "ensemble_train_loop", "unstacked_to_learned_dicts", "standard_metrics", "torchopt_compat",
     "install_reference_aliases",
 ]

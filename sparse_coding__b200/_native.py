@@ -47,7 +47,7 @@ class ScStepArgs(C.Structure):
         ("stream", C.c_void_p),
         ("grad_enc", C.c_void_p), ("grad_bias", C.c_void_p), ("grad_dec", C.c_void_p),
         ("B_total", C.c_int32),
-        ("operand_format", C.c_int32), ("out_c_half", C.c_void_p),
+        ("operand_format", C.c_int32), ("out_c_half", C.c_void_p), ("dict_size", C.c_void_p),
     ]
 
 

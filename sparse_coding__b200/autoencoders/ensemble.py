@@ -53,11 +53,13 @@ def unstack_dict(params: Dict[str, torch.Tensor], n_models: int, device=None) ->
 def _sig_kind(sig) -> str:
     kind = getattr(sig, "_sc_kind", None)
     if kind is None:
-        kind = {"FunctionalSAE": "untied", "FunctionalFista": "untied", "FunctionalTiedSAE": "tied"}.get(
+        kind = {"FunctionalSAE": "untied", "FunctionalFista": "untied", "FunctionalTiedSAE": "tied",
+                "FunctionalMaskedSAE": "masked_untied", "FunctionalMaskedTiedSAE": "masked_tied"}.get(
             getattr(sig, "__name__", ""), None)
     if kind is None:
         raise NotImplementedError(
-            f"signature {sig!r}: the B200 engine implements FunctionalSAE, FunctionalFista and FunctionalTiedSAE; "
+            f"signature {sig!r}: the B200 engine implements FunctionalSAE, FunctionalFista, FunctionalTiedSAE and the "
+            "two Masked variants; "
             "other signatures have no fused path (and there is no generic fallback)")
     return kind
 
@@ -308,9 +310,10 @@ class FunctionalEnsemble:
             if x.dim() != 3 or x.shape[0] != M:
                 raise ValueError(f"expected an [M={M}, B, d] batch, got {tuple(x.shape)}")
         x = x.contiguous()
-        tied = self._kind == "tied"
+        masked = self._kind.startswith("masked")
+        tied = self._kind in ("tied", "masked_tied")
         per_member = not expand_dims
-        if tied:
+        if tied and not masked:  # the masked tied signature has no centering buffers (sae_ensemble.py:307-371)
             x, per_member = self._centered_batch(x, expand_dims)
         B, d = x.shape[-2], x.shape[-1]
         enc = self._contig(self.params, "encoder")
@@ -328,6 +331,11 @@ class FunctionalEnsemble:
             dec_mu, dec_nu = self._contig(st.mu, "decoder", enc.shape), self._contig(st.nu, "decoder", enc.shape)
         l1 = self._scalar_buffer("l1_alpha")
         bd = self._scalar_buffer("bias_decay") if bias_decay is None else bias_decay.to(torch.float32).contiguous()
+        dict_size = None
+        if masked:
+            # the masked losses carry no bias-decay term (sae_ensemble.py:360-361, :429-430)
+            bd = torch.zeros(M, dtype=torch.float32, device=x.device)
+            dict_size = self.buffers["dict_size"].to(device=x.device, dtype=torch.int32).contiguous()
 
         adam = self.adam_constants(advance=not grad_only)
         grads = None
@@ -360,12 +368,14 @@ class FunctionalEnsemble:
             grad_bias=nat.ptr(grads["encoder_bias"]) if grad_only else None,
             grad_dec=nat.ptr(grads.get("decoder")) if grad_only else None,
             B_total=int(batch_total),
-            operand_format=int(f16), out_c_half=nat.ptr(c_half),
+            operand_format=int(f16), out_c_half=nat.ptr(c_half), dict_size=nat.ptr(dict_size),
         )
         with torch.cuda.device(x.device):
             nat.check(L.sc_sae_step(C.byref(args)), "sc_sae_step")
         loss_dict = {"loss": losses[0], "l_reconstruction": losses[1], "l_l1": losses[2]}
-        if not tied:  # FunctionalTiedSAE's loss_data has no l_bias_decay key (sae_ensemble.py:150-154)
+        if masked:
+            pass  # loss, l_reconstruction, l_l1 only
+        elif not tied:  # FunctionalTiedSAE's loss_data has no l_bias_decay key (sae_ensemble.py:150-154)
             loss_dict["l_bias_decay"] = losses[3]
         elif grad_only:
             loss_dict["l_bias_decay"] = losses[3]

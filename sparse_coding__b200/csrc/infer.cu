@@ -167,7 +167,7 @@ static int encode_impl(const ScEncodeArgs& a) {
             const int rc = make_io_map(&ep.c_map, a.out_c, B, N, G, BN_, &err);
             if (rc != 0) return fail(rc, "%s", err ? err : "io tensor map creation failed");
         }
-        ep.bias = a.bias; ep.l1_part = nullptr; ep.signed_zero = 0;
+        ep.bias = a.bias; ep.l1_part = nullptr; ep.signed_zero = 0; ep.dict_size = nullptr;
         SC_TRY((run_gemm<false, false, EpiEncode>(B, N, G, &s, 1, ep, st)));
     }
     return 0;

@@ -82,7 +82,7 @@ static int encode_noalloc_impl(const float* x, const float* W, const float* bias
         const int rc = make_io_map(&ep.c_map, out_c, B, N, 1, (long long)B * N, &err);
         if (rc != 0) return fail(rc, "%s", err ? err : "io tensor map creation failed");
     }
-    ep.bias = bias; ep.l1_part = nullptr; ep.signed_zero = 0;
+    ep.bias = bias; ep.l1_part = nullptr; ep.signed_zero = 0; ep.dict_size = nullptr;
     return run_gemm<false, false, EpiEncode>(B, N, 1, &s, 1, ep, st);
 }
 

@@ -30,6 +30,7 @@ struct EpiEncode {
         const float* bias;  // [G][N] or nullptr
         float* l1_part;     // [G][tiles*8] or nullptr
         int signed_zero;    // 1 (training): TF32-rounded, z<0 -> -0.0f; 0 (inference API): plain fp32 relu
+        const int* dict_size;  // [G] or nullptr: features >= dict_size[g] are masked out (sae_ensemble.py:356, :425)
     };
     const Params& p;
     const RowCtx c;
@@ -50,9 +51,11 @@ struct EpiEncode {
         }
         const bool full = c.row < c.M && ncols >= 32;
         if (p.signed_zero) {
+            // masked features behave like z < 0: code -0.0, no L1 term, and the backward then gives dz = 0
+            const int live_cols = p.dict_size ? p.dict_size[c.g] - col : 32;
 #pragma unroll
             for (int j = 0; j < 32; ++j) {
-                const float z = v[j] + bv[j];
+                const float z = j < live_cols ? v[j] + bv[j] : -1.f;
                 if (full || (c.row < c.M && j < ncols)) sum += fmaxf(z, 0.f);
                 v[j] = (z >= 0.f) ? rn_tf32(z) : -0.0f;
             }

@@ -17,6 +17,7 @@ struct EpiEncodeH {
         CUtensorMap c_map;  // fp16 io map of c [G][B][N]
         const float* bias;  // [G][N]
         float* l1_part;
+        const int* dict_size;  // [G] or nullptr: features >= dict_size[g] are masked out
     };
     const Params& p;
     const RowCtx c;
@@ -36,9 +37,10 @@ struct EpiEncodeH {
             for (int j = 0; j < 32; ++j) bv[j] = 0.f;
         }
         const bool full = c.row < c.M && ncols >= 32;
+        const int live_cols = p.dict_size ? p.dict_size[c.g] - col : 32;
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
-            const float z = v[j] + bv[j];
+            const float z = j < live_cols ? v[j] + bv[j] : -1.f;
             if (full || (c.row < c.M && j < ncols)) sum += fmaxf(z, 0.f);
             v[j] = (z >= 0.f) ? z : -0.0f;
         }

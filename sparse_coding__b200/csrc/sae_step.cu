@@ -268,7 +268,7 @@ static int sae_step_impl(const ScStepArgs& a) {
         Seg s{kmajor(w.x_r, B, d, xg, Bd), kmajor(a.tied ? w.D_r : w.enc_r, N, d, M, Nd)};
         EpiEncode::Params ep{};
         SC_TRY(io_map(&ep.c_map, a.out_c, B, N, M, BN_));
-        ep.bias = a.bias; ep.l1_part = w.l1_part; ep.signed_zero = 1;
+        ep.bias = a.bias; ep.l1_part = w.l1_part; ep.signed_zero = 1; ep.dict_size = a.dict_size;
         SC_TRY((run_gemm<false, false, EpiEncode>(B, N, M, &s, 1, ep, st)));
     }
     prof_mark(st, "G1_encode");

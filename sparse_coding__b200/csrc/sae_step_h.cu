@@ -136,7 +136,7 @@ int sae_step_f16_impl(const ScStepArgs& a) {
         Seg s{kmajor_h(w.x_h, B, d, xg, Bd), kmajor_h(a.tied ? w.D_h : w.enc_h, N, d, M, Nd)};
         EpiEncodeH::Params ep{};
         SC_TRY(io_map_h(&ep.c_map, c_h, B, N, M, BN_));
-        ep.bias = a.bias; ep.l1_part = w.l1_part;
+        ep.bias = a.bias; ep.l1_part = w.l1_part; ep.dict_size = a.dict_size;
         SC_TRY((run_gemm<false, false, EpiEncodeH, true>(B, N, M, &s, 1, ep, st)));
     }
     prof_mark(st, "G1_encode");

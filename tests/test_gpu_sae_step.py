@@ -190,3 +190,55 @@ def test_gradient_only_then_adam_apply_equals_fused_step():
                 assert torch.allclose(la[k], lb[k], rtol=1e-5, atol=1e-8), (kind, s, k)
         for k in ens_a.params:
             assert float((ens_a.params[k] - ens_b.params[k]).abs().max()) < 1e-6, (kind, k)
+
+
+@pytest.mark.parametrize("tied", [False, True])
+@pytest.mark.parametrize("shape", [(256, 64, 256, (256, 100, 7)), (300, 128, 512, (512, 130, 384, 64))])
+def test_masked_mixed_dictionary_sizes(tied, shape):
+    """FunctionalMasked(Tied)SAE, sae_ensemble.py:307-442: members of different dictionary sizes stacked to one
+    width.  30 steps against the masked oracle; unused features stay exactly as initialised, their codes are 0."""
+    import sparse_coding__b200 as sc
+    B, d, stack, sizes = shape
+    sig = sc.FunctionalMaskedTiedSAE if tied else sc.FunctionalMaskedSAE
+    torch.manual_seed(21)
+    l1s = np.logspace(-3.5, -2.5, len(sizes))
+    models = [sig.init(d, n, stack, float(l1)) for n, l1 in zip(sizes, l1s)]
+    ens = sc.FunctionalEnsemble(models, sig, sc.torchopt_compat.adam, {"lr": 1e-3}, device="cuda")
+    params = {k: v.detach().cpu().clone() for k, v in ens.params.items()}
+    buffers = {k: v.detach().cpu().clone() for k, v in ens.buffers.items()}
+    p0 = {k: v.clone() for k, v in params.items()}
+    orc = R.EnsembleOracle(params, buffers, tied=tied, lr=1e-3)
+    data = make_sparse_data(8 * B, d, 2 * d, 8, seed=23)
+    g = torch.Generator().manual_seed(25)
+    for step in range(30):
+        x = data[torch.randint(0, data.shape[0], (B,), generator=g)]
+        l_gpu, a_gpu = ens.step_batch(x.cuda())
+        l_cpu, a_cpu = orc.step_batch(x)
+        assert set(l_gpu.keys()) == set(l_cpu.keys()) == {"loss", "l_reconstruction", "l_l1"}
+        for k in l_cpu:
+            assert rel_err(l_gpu[k].cpu(), l_cpu[k]) < 1e-3, (step, k)
+        for m in range(len(sizes)):
+            for k in l_cpu:
+                lg, lc = float(l_gpu[k][m]), float(l_cpu[k][m])
+                assert abs(lg - lc) <= 1e-3 * abs(lc) + 1e-9, (step, k, m)
+    c = a_gpu["c"].cpu()
+    l0g = (c != 0).float().sum(-1).mean(-1)
+    l0c = (a_cpu["c"] != 0).float().sum(-1).mean(-1)
+    assert float(((l0g - l0c).abs() / l0c.clamp_min(1.0)).max()) < 5e-3
+    for m, n in enumerate(sizes):
+        if n < stack:
+            assert float(c[m, :, n:].abs().max()) == 0.0
+        for k in p0:
+            assert torch.equal(ens.params[k][m, n:].cpu(), p0[k][m, n:]), (k, m)
+            assert not torch.equal(ens.params[k][m, :n].cpu(), p0[k][m, :n])
+    p_m = {k: v[1] for k, v in ens.params.items()}
+    b_m = {k: v[1] for k, v in ens.buffers.items()}
+    ld = sig.to_learned_dict(p_m, b_m)
+    assert ld.get_learned_dict().shape == (sizes[1], d)
+    # the per-member loss of the signature (not on the train path) agrees with the fused step's bookkeeping
+    total, (ld_losses, aux) = sig.loss(p_m, b_m, x.cuda())
+    orc_losses, _ = (R.tied_forward(orc.params["encoder"][1], orc.params["encoder_bias"][1], orc.buffers["l1_alpha"][1], 0.0, x,
+                                    mask=orc.buffers["coef_mask"][1]) if tied else
+                     R.sae_forward(orc.params["encoder"][1], orc.params["encoder_bias"][1], orc.params["decoder"][1],
+                                   orc.buffers["l1_alpha"][1], 0.0, x, orc.buffers["coef_mask"][1]))
+    assert abs(float(total) - float(orc_losses["loss"])) <= 2e-3 * abs(float(orc_losses["loss"]))

@@ -159,6 +159,34 @@ int sc_row_normalise(const float* W, float* out, int32_t G, int32_t N, int32_t d
  * sum_{b,j} (x[b][j] - mean_b x[b][j])^2 for x [B,d].  workspace: at least (d + 1) floats. */
 int sc_column_variance(const float* x, float* out_sum, int32_t B, int32_t d, void* workspace, void* stream);
 
+/* Batch assembly from an activation chunk resident in HBM - replaces `dataset[batch_idxs].to(device)` of
+ * the reference train loops (big_sweep.py:170, basic_l1_sweep.py:103, cluster_runs.py:37) and the chunk
+ * centring of big_sweep.py:402-407:  out[b][:] = float(chunk[idx[b]][:]) - mean[:].
+ * chunk is [n_rows][d] in its storage format: fp16 (elem_bytes 2, as activation_dataset.py:393-397 writes
+ * it; d % 8 == 0) or fp32 (elem_bytes 4; d % 4 == 0).  idx: B int64 row numbers on the device, negative
+ * values count from the end as in torch indexing.  mean: [d] fp32 or NULL.  A row number outside
+ * [-n_rows, n_rows) cannot raise from a kernel: that output row is zero-filled and *err_flag (device int,
+ * may be NULL) is OR-ed with 1 - the host mirror checks the flag and raises IndexError like the reference. */
+typedef struct {
+    const void* chunk;
+    int32_t elem_bytes;
+    int64_t n_rows;
+    int32_t d;
+    const int64_t* idx;
+    int32_t B;
+    const float* mean;
+    float* out; /* [B][d] fp32 */
+    int32_t* err_flag;
+    void* stream;
+} ScGatherArgs;
+int sc_gather_rows(const ScGatherArgs* args);
+
+/* Column means of a resident chunk (`chunk.mean(dim=0)`, big_sweep.py:402-405): out_mean[j] =
+ * (1/n_rows) sum_r float(chunk[r][j]), fp32 accumulation in a fixed order (deterministic). */
+size_t sc_column_mean_workspace_bytes(int32_t d);
+int sc_column_mean(const void* chunk, int32_t elem_bytes, int64_t n_rows, int32_t d, float* out_mean, void* workspace,
+                   void* stream);
+
 /* Encode for callers that cannot allocate device memory.  (No counterpart in the reference: it is
  * an addition of this library.)  Same result as sc_encode with G = 1 and only out_c requested -
  * c = relu(x W^T + bias), x [B,d], W [N,d], bias [N] or NULL, out_c [B,N] - but the TF32-rounded

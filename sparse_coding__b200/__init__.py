@@ -13,13 +13,15 @@ from .autoencoders.ensemble import FunctionalEnsemble
 from .autoencoders.fista import Fista, FunctionalFista
 from .autoencoders.learned_dict import LearnedDict, TiedSAE, UntiedSAE
 from .autoencoders.sae_ensemble import FunctionalMaskedSAE, FunctionalMaskedTiedSAE, FunctionalSAE, FunctionalTiedSAE
-from . import big_sweep, standard_metrics, torchopt_compat
+from . import big_sweep, chunks, standard_metrics, torchopt_compat
+from .chunks import DeviceBatchSampler, ResidentChunk, load_learned_dicts, save_learned_dicts, train_on_chunks
 from .big_sweep import ensemble_train_loop, unstacked_to_learned_dicts
 
 __all__ = [
     "FunctionalEnsemble", "FunctionalSAE", "FunctionalTiedSAE", "FunctionalMaskedSAE", "FunctionalMaskedTiedSAE", "FunctionalFista", "Fista", "LearnedDict", "UntiedSAE",
     "TiedSAE", "ensemble_train_loop", "unstacked_to_learned_dicts", "standard_metrics", "torchopt_compat",
-    "install_reference_aliases",
+    "install_reference_aliases", "ResidentChunk", "DeviceBatchSampler", "save_learned_dicts", "load_learned_dicts",
+    "train_on_chunks",
 ]
 
 _ALIASES = {

@@ -24,6 +24,7 @@ EXPORTS = [
     "sc_encode_workspace_bytes", "sc_encode", "sc_decode_workspace_bytes", "sc_decode",
     "sc_fista_workspace_bytes", "sc_fista", "sc_gemm_tf32", "sc_adam_apply", "sc_row_normalise", "sc_column_variance",
     "sc_profile_begin", "sc_profile_end", "sc_encode_noalloc", "sc_sae_step_f16_supported",
+    "sc_gather_rows", "sc_column_mean_workspace_bytes", "sc_column_mean",
 ]
 
 
@@ -82,6 +83,14 @@ class ScFistaArgs(C.Structure):
     ]
 
 
+class ScGatherArgs(C.Structure):
+    _fields_ = [
+        ("chunk", C.c_void_p), ("elem_bytes", C.c_int32), ("n_rows", C.c_int64), ("d", C.c_int32),
+        ("idx", C.c_void_p), ("B", C.c_int32), ("mean", C.c_void_p), ("out", C.c_void_p),
+        ("err_flag", C.c_void_p), ("stream", C.c_void_p),
+    ]
+
+
 def build(verbose: bool = False) -> None:
     """Compile libsc_b200.so (and the GEMM self-test) in-tree with nvcc for sm_100a."""
     r = subprocess.run(["make", "-C", CSRC, "-j4"], capture_output=True, text=True)
@@ -126,6 +135,10 @@ def lib() -> C.CDLL:
         L.sc_sae_step_f16_supported.restype = C.c_int
         L.sc_adam_apply.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(ScAdam), C.c_void_p]
         L.sc_adam_apply.restype = C.c_int
+        L.sc_gather_rows.argtypes = [C.POINTER(ScGatherArgs)]
+        L.sc_column_mean_workspace_bytes.restype = C.c_size_t
+        L.sc_column_mean_workspace_bytes.argtypes = [C.c_int32]
+        L.sc_column_mean.argtypes = [C.c_void_p, C.c_int32, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]
         for name in ("sc_sae_step", "sc_encode", "sc_decode", "sc_fista", "sc_gemm_tf32", "sc_row_normalise",
                      "sc_column_variance"):
             getattr(L, name).restype = C.c_int

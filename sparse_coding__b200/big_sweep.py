@@ -41,10 +41,14 @@ def ensemble_train_loop(ensemble, cfg, args, ensemble_name, sampler, dataset, pr
     if cfg.use_wandb:
         run = cfg.wandb_instance
 
+    from .chunks import ResidentChunk
+    resident = isinstance(dataset, ResidentChunk)  # fp16/fp32 chunk in HBM: gather + convert + centre on the device
     dataset_on_device = dataset.is_cuda
 
     for i, batch_idxs in enumerate(sampler):
-        if dataset_on_device:
+        if resident:
+            batch = dataset[batch_idxs]
+        elif dataset_on_device:
             batch = dataset[torch.as_tensor(batch_idxs, device=dataset.device)]
         else:
             batch = dataset[batch_idxs].to(args["device"])
@@ -89,6 +93,9 @@ def ensemble_train_loop(ensemble, cfg, args, ensemble_name, sampler, dataset, pr
             run.log(log, commit=True)
 
         progress_counter.value = i
+
+    if resident:
+        dataset.check()  # raises IndexError if a device-side index batch was out of range
 
 
 def unstacked_to_learned_dicts(ensemble, args, ensemble_hyperparams, buffer_hyperparams):

@@ -5,3 +5,4 @@
 #include "infer.cu"
 #include "fista.cu"
 #include "noalloc.cu"
+#include "gather.cu"

@@ -12,27 +12,27 @@
 namespace sc {
 
 constexpr int kIoTileBytes = 32 * 32 * 4;
+constexpr int kIoBars = 4;  // tile-load mbarriers per epilogue warp
 
 struct EpiIo {
     uint8_t* buf;     // this warp's staging tiles (Epi::kIoBufs x 4 KB, 1024-byte aligned)
-    uint64_t* bar;    // this warp's two mbarriers for tile loads (one per load slot)
-    uint32_t* phase;  // parity of the next completion on bar[0], bar[1] (lives across tiles)
+    uint64_t* bar;    // this warp's kIoBars mbarriers for tile loads (one per load slot)
+    uint32_t* phase;  // bit s = parity of the next completion on bar[s] (one word per warp, lives across tiles)
 };
 
 // element (r, c) of a staging tile sits at r*128 + ((c/4) ^ (r & 7))*16 + (c % 4)*4
 SC_DEVICE void io_read_row(const uint8_t* tile, int r, float (&v)[32]) {
-    const uint8_t* row = tile + r * 128;
+    const uint32_t row = smem_u32(tile) + r * 128;
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-        const float4 t = *reinterpret_cast<const float4*>(row + ((j ^ (r & 7)) << 4));
+        const float4 t = lds_128(row + ((j ^ (r & 7)) << 4));
         v[4 * j] = t.x; v[4 * j + 1] = t.y; v[4 * j + 2] = t.z; v[4 * j + 3] = t.w;
     }
 }
 SC_DEVICE void io_write_row(uint8_t* tile, int r, const float (&v)[32]) {
-    uint8_t* row = tile + r * 128;
+    const uint32_t row = smem_u32(tile) + r * 128;
 #pragma unroll
-    for (int j = 0; j < 8; ++j)
-        *reinterpret_cast<float4*>(row + ((j ^ (r & 7)) << 4)) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+    for (int j = 0; j < 8; ++j) sts_128(row + ((j ^ (r & 7)) << 4), v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
 }
 
 // Whole warp.  Make the rows just written visible to the async proxy, then lane 0 stores the tile.
@@ -50,6 +50,12 @@ SC_DEVICE void io_wait_stores_read() {
     if ((threadIdx.x & 31) == 0) tma_store_wait_read<0>();
     __syncwarp();
 }
+// Same, but the most recent N store groups may still be reading (staging tiles used in rotation).
+template <int N>
+SC_DEVICE void io_wait_stores_read_n() {
+    if ((threadIdx.x & 31) == 0) tma_store_wait_read<N>();
+    __syncwarp();
+}
 // Whole warp, before kernel exit: the stores themselves must be complete.
 SC_DEVICE void io_wait_stores_done() {
     if ((threadIdx.x & 31) == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
@@ -58,8 +64,8 @@ SC_DEVICE void io_wait_stores_done() {
 // Lane 0 arms the warp's barrier for `bytes` and the caller (lane 0) issues the tile loads.
 SC_DEVICE void io_expect(const EpiIo& io, uint32_t bytes, int slot = 0) { mbar_arrive_expect_tx(io.bar + slot, bytes); }
 SC_DEVICE void io_wait_loads(const EpiIo& io, int slot = 0) {
-    mbar_wait(io.bar + slot, io.phase[slot]);
-    io.phase[slot] ^= 1;
+    mbar_wait(io.bar + slot, (*io.phase >> slot) & 1u);
+    *io.phase ^= 1u << slot;
 }
 // element (r, c) of a staging tile (see io_read_row)
 SC_DEVICE uint32_t io_elem_offset(int r, int c) { return r * 128 + (((c >> 2) ^ (r & 7)) << 4) + ((c & 3) << 2); }
@@ -67,13 +73,16 @@ SC_DEVICE uint32_t io_elem_offset(int r, int c) { return r * 128 + (((c >> 2) ^ 
 // fp16 staging tile [32 rows][32 halves] = 64-byte rows, laid out as TMA's SWIZZLE_64B expects:
 // 16-byte chunk j of row r sits at r*64 + ((j ^ ((r >> 1) & 3)) << 4).  Conflict free for row writes.
 SC_DEVICE void io_write_row_h(uint8_t* tile, int r, const float (&v)[32]) {
-    uint8_t* row = tile + r * 64;
+    const uint32_t row = smem_u32(tile) + r * 64;
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-        __half2 h[4];
+        uint32_t h[4];
 #pragma unroll
-        for (int t = 0; t < 4; ++t) h[t] = __floats2half2_rn(v[8 * j + 2 * t], v[8 * j + 2 * t + 1]);
-        *reinterpret_cast<uint4*>(row + ((j ^ ((r >> 1) & 3)) << 4)) = *reinterpret_cast<uint4*>(h);
+        for (int t = 0; t < 4; ++t) {
+            const __half2 p = __floats2half2_rn(v[8 * j + 2 * t], v[8 * j + 2 * t + 1]);
+            h[t] = *reinterpret_cast<const uint32_t*>(&p);
+        }
+        sts_128u(row + ((j ^ ((r >> 1) & 3)) << 4), h[0], h[1], h[2], h[3]);
     }
 }
 

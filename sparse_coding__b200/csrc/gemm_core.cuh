@@ -58,7 +58,7 @@ struct GemmCfg {
     static constexpr int kStagesRaw = (227 * 1024 - 2048 - kIoBytes) / kStageBytes;
     static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
     static constexpr int kTmemCols = (2 * BN <= 32) ? 32 : (2 * BN <= 64) ? 64 : (2 * BN <= 128) ? 128 : (2 * BN <= 256) ? 256 : 512;
-    static constexpr int kBarrierBytes = (2 * kStages + 4 + 2 * kEpiWarps) * 8 + 16;
+    static constexpr int kBarrierBytes = (2 * kStages + 4 + kIoBars * kEpiWarps) * 8 + 16;
     static constexpr int kSmemBytes = kStages * kStageBytes + kIoBytes + kBarrierBytes + 1024;  // + alignment slack
     static_assert(BN % 32 == 0 && BN >= 32 && BN <= 256, "BN must be a multiple of 32 in [32,256]");
     static_assert(kStages >= 2, "not enough shared memory left for the operand pipeline");
@@ -76,6 +76,12 @@ struct RowCtx {
     int prob;    // problem index when the launch batches independent problems (else 0)
     int half;    // which of the kEpiHalves warps of that quarter (takes chunks half, half+2, ...)
     int part;    // warp_q + 4*half: slot for per-warp partial results (0..4*kEpiHalves-1)
+    // the tile this warp processes next (static schedule), for functors that prefetch across tiles:
+    int bn;         // tile width in columns
+    int first;      // 1 on the warp's first tile (nothing was prefetched for it)
+    int next_g;     // group of the next tile, -1 when this is the last one
+    int next_row0;  // first global row of this warp's 32-row slice in the next tile
+    int next_col0;  // first global column of the next tile
 };
 
 // One accumulator tile through an epilogue functor (shared by the single-CTA and the CTA-pair kernels).
@@ -120,7 +126,7 @@ gemm_tf32_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
     uint64_t* tmem_full = empty_bar + kStages;
     uint64_t* tmem_empty = tmem_full + 2;
     uint64_t* io_bar = tmem_empty + 2;
-    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(io_bar + 2 * kEpiWarps);
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(io_bar + kIoBars * kEpiWarps);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -140,7 +146,7 @@ gemm_tf32_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
             mbar_init(&tmem_full[i], 1);
             mbar_init(&tmem_empty[i], 128 * kEpiHalves);
         }
-        for (int i = 0; i < 2 * kEpiWarps; ++i) mbar_init(&io_bar[i], 1);
+        for (int i = 0; i < kIoBars * kEpiWarps; ++i) mbar_init(&io_bar[i], 1);
         fence_mbar_init();
     }
     if (warp == 2) {
@@ -248,8 +254,8 @@ gemm_tf32_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
         // ------------------------------------------------------------------ epilogue
         const int q = warp & 3;
         const int half = (warp - 4) >> 2;
-        uint32_t io_phase[2] = {0, 0};
-        EpiIo io{io_smem + (warp - 4) * (Epi::kIoBufs * kIoTileBytes), &io_bar[2 * (warp - 4)], io_phase};
+        uint32_t io_phase = 0;
+        EpiIo io{io_smem + (warp - 4) * (Epi::kIoBufs * kIoTileBytes), &io_bar[kIoBars * (warp - 4)], &io_phase};
         int it = 0;
         for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
             const int gg = tile / tiles_per_group;
@@ -263,6 +269,15 @@ gemm_tf32_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
             RowCtx ctx;
             ctx.g = g; ctx.row = tm * kBlockM + q * 32 + lane; ctx.col0 = tn * BN;
             ctx.M = shape.M; ctx.N = shape.N; ctx.tile_m = tm; ctx.tile_n = tn; ctx.tiles_m = shape.tiles_m; ctx.tiles_n = shape.tiles_n; ctx.warp_q = q; ctx.prob = prob; ctx.half = half; ctx.part = q + 4 * half;
+            ctx.bn = BN; ctx.first = it == 0;
+            ctx.next_g = -1; ctx.next_row0 = 0; ctx.next_col0 = 0;
+            if (tile + static_cast<int>(gridDim.x) < total_tiles) {
+                const int nt = tile + gridDim.x;
+                const int ngg = nt / tiles_per_group;
+                const int nrem = nt - ngg * tiles_per_group;
+                const int ntn = nrem / shape.tiles_m;
+                ctx.next_g = ngg % shape.G; ctx.next_row0 = (nrem - ntn * shape.tiles_m) * kBlockM + q * 32; ctx.next_col0 = ntn * BN;
+            }
             const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
             epilogue_tile<BN, Epi>(ep, ctx, io, &tmem_full[as], aph, taddr, [&] { mbar_arrive(&tmem_empty[as]); });
         }

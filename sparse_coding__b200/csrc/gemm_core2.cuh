@@ -28,7 +28,7 @@ struct GemmCfg2 {
     static constexpr int kStagesRaw = (227 * 1024 - 2048 - kIoBytes) / kStageBytes;
     static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
     static constexpr int kTmemCols = GemmCfg<BN>::kTmemCols;
-    static constexpr int kBarrierBytes = (2 * kStages + 4 + 2 * kEpiWarps) * 8 + 16;
+    static constexpr int kBarrierBytes = (2 * kStages + 4 + kIoBars * kEpiWarps) * 8 + 16;
     static constexpr int kSmemBytes = kStages * kStageBytes + kIoBytes + kBarrierBytes + 1024;
     static_assert(BN % 64 == 0 && BN >= 64 && BN <= 256, "paired kernel: BN multiple of 64 in [64,256]");
     static_assert(kStages >= 2, "not enough shared memory left for the operand pipeline");
@@ -56,7 +56,7 @@ gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape sha
     uint64_t* tmem_full = empty_bar + kStages;
     uint64_t* tmem_empty = tmem_full + 2;
     uint64_t* io_bar = tmem_empty + 2;
-    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(io_bar + 2 * kEpiWarps);
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(io_bar + kIoBars * kEpiWarps);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -79,7 +79,7 @@ gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape sha
             mbar_init(&tmem_full[i], 1);
             mbar_init(&tmem_empty[i], 2 * 128 * kEpiHalves);  // epilogue threads of BOTH CTAs (leader's copy is used)
         }
-        for (int i = 0; i < 2 * kEpiWarps; ++i) mbar_init(&io_bar[i], 1);
+        for (int i = 0; i < kIoBars * kEpiWarps; ++i) mbar_init(&io_bar[i], 1);
         fence_mbar_init();
     }
     if (warp == 2) {
@@ -199,8 +199,8 @@ gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape sha
         // ------------------------------------------------------------------ epilogue (both CTAs, own 128 rows)
         const int q = warp & 3;
         const int half = (warp - 4) >> 2;
-        uint32_t io_phase[2] = {0, 0};
-        EpiIo io{io_smem + (warp - 4) * (Epi::kIoBufs * kIoTileBytes), &io_bar[2 * (warp - 4)], io_phase};
+        uint32_t io_phase = 0;
+        EpiIo io{io_smem + (warp - 4) * (Epi::kIoBufs * kIoTileBytes), &io_bar[kIoBars * (warp - 4)], &io_phase};
         int it = 0;
         for (int tile = cluster_id; tile < total_tiles; tile += num_clusters, ++it) {
             const int gg = tile / tiles_per_group;
@@ -217,6 +217,17 @@ gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape sha
             // partial-sum slots are indexed by 128-row tile: report this CTA's half as its own row tile
             ctx.tile_m = tm * 2 + rank; ctx.tile_n = tn; ctx.tiles_m = shape.tiles_m * 2; ctx.tiles_n = shape.tiles_n;
             ctx.warp_q = q; ctx.prob = prob; ctx.half = half; ctx.part = q + 4 * half;
+            ctx.bn = BN; ctx.first = it == 0;
+            ctx.next_g = -1; ctx.next_row0 = 0; ctx.next_col0 = 0;
+            if (tile + num_clusters < total_tiles) {
+                const int nt = tile + num_clusters;
+                const int ngg = nt / tiles_per_group;
+                const int nrem = nt - ngg * tiles_per_group;
+                const int ntn = nrem / shape.tiles_m;
+                ctx.next_g = ngg % shape.G;
+                ctx.next_row0 = (nrem - ntn * shape.tiles_m) * (2 * kBlockM) + rank * kBlockM + q * 32;
+                ctx.next_col0 = ntn * BN;
+            }
             const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
             epilogue_tile<BN, Epi>(ep, ctx, io, &tmem_full[as], aph, taddr, [&] {
                 if (leader) mbar_arrive(&tmem_empty[as]);

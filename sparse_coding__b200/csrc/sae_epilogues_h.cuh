@@ -12,7 +12,7 @@ namespace sc {
 
 // G1: c = relu(x W^T + b) -> fp16 codes (z < 0 stored as -0), L1 partial sums
 struct EpiEncodeH {
-    static constexpr int kIoBufs = 1;
+    static constexpr int kIoBufs = 1;  // one 4 KB buffer = two 2 KB fp16 staging tiles, used alternately
     struct alignas(64) Params {
         CUtensorMap c_map;  // fp16 io map of c [G][B][N]
         const float* bias;  // [G][N]
@@ -23,7 +23,10 @@ struct EpiEncodeH {
     const RowCtx c;
     const EpiIo io;
     float sum;
-    SC_DEVICE EpiEncodeH(const Params& p_, const RowCtx& c_, const EpiIo& io_) : p(p_), c(c_), io(io_), sum(0.f) {}
+    int live_end;  // first column that does not count (N, or dict_size[g] when masked)
+    SC_DEVICE EpiEncodeH(const Params& p_, const RowCtx& c_, const EpiIo& io_) : p(p_), c(c_), io(io_), sum(0.f) {
+        live_end = p.dict_size ? min(p.dict_size[c.g], c.N) : c.N;
+    }
     SC_DEVICE void prefetch(int) {}
     SC_DEVICE void chunk(int co, float (&v)[32], int /*next_co*/) {
         const int col = c.col0 + co;
@@ -36,17 +39,26 @@ struct EpiEncodeH {
 #pragma unroll
             for (int j = 0; j < 32; ++j) bv[j] = 0.f;
         }
-        const bool full = c.row < c.M && ncols >= 32;
-        const int live_cols = p.dict_size ? p.dict_size[c.g] - col : 32;
+        const int live = live_end - col;
+        // max(z, -0.0) is z for z >= 0 (max(+0, -0) = +0) and -0.0 for z < 0; adding -0.0 to the L1 sum is a no-op
+        if (c.row < c.M && live >= 32) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-            const float z = j < live_cols ? v[j] + bv[j] : -1.f;
-            if (full || (c.row < c.M && j < ncols)) sum += fmaxf(z, 0.f);
-            v[j] = (z >= 0.f) ? z : -0.0f;
+            for (int j = 0; j < 32; ++j) {
+                v[j] = fmaxf(v[j] + bv[j], -0.0f);
+                sum += v[j];
+            }
+        } else {
+            const bool row_ok = c.row < c.M;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                v[j] = (row_ok && j < live) ? fmaxf(v[j] + bv[j], -0.0f) : -0.0f;  // masked features behave like z < 0
+                sum += v[j];
+            }
         }
-        io_wait_stores_read();
-        io_write_row_h(io.buf, lane, v);
-        io_store_tile(&p.c_map, io.buf, col, c.row - lane, c.g);
+        uint8_t* tile = io.buf + ((co >> 5) & 1) * 2048;
+        io_wait_stores_read_n<1>();  // the store issued two chunks ago has read this staging tile
+        io_write_row_h(tile, lane, v);
+        io_store_tile(&p.c_map, tile, col, c.row - lane, c.g);
         io_commit();
     }
     SC_DEVICE void finish() {
@@ -112,74 +124,92 @@ struct EpiDecodeH {
     }
 };
 
-// G3 (transposed: rows = feature n, cols = batch b): dz' from q' = r D^T and the fp16 codes
+// G3 (transposed: rows = feature n, cols = batch b): dz' from q' = r D^T and the fp16 codes.
+// The thread of an accumulator row owns ONE feature and walks along the batch, so c and dz ([B][N] in memory)
+// are touched column-wise: both go through 32 x 32 fp16 staging tiles moved by TMA (box = 32 features x 32 batch
+// rows).  The four c tiles a warp needs for a 256-column accumulator tile sit in four slots; as soon as a slot
+// has been read, the same chunk of the warp's NEXT tile is requested into it, so the loads fly during the rest
+// of this tile and the wait for the next accumulator - no register prefetch, no exposed load latency.
 struct EpiBackCodeH {
-    static constexpr int kIoBufs = 0;
-    struct Params {
-        const __half* c;      // [G][B][N]
-        __half* dz;           // [G][B][N]  (scaled by B d / 2)
+    static constexpr int kIoBufs = 3;  // 12 KB per warp: 4 c slots (2 KB) + 2 dz staging tiles (2 KB)
+    static constexpr int kSlots = 4;
+    static_assert(kSlots <= kIoBars, "one load barrier per c slot");
+    struct alignas(64) Params {
+        CUtensorMap c_map;    // fp16 io map of c  [G][B][N]
+        CUtensorMap dz_map;   // fp16 io map of dz [G][B][N]  (scaled by B d / 2)
         const float* l1;      // [G]
         const float* bias;    // [G][N] (tied only)
         float* db_part;       // [G][parts][N]  (scaled)
         float* s_part;        // [G][parts][N]  (scaled)
-        long long cb_gstride;
         float l1_scale;       // d / 2:  lam/B * (B d / 2)
         int tied;
         int feats;
     };
     const Params& p;
     const RowCtx c;
+    const EpiIo io;
     float db, s, l1_term, bn;
-    __half nxt[32];
-    SC_DEVICE EpiBackCodeH(const Params& p_, const RowCtx& c_, const EpiIo&) : p(p_), c(c_), db(0.f), s(0.f) {
+    uint32_t off[4];  // byte offset of this lane's element in rows j with ((j >> 1) & 3) == k (SWIZZLE_64B)
+    // chunk i of a tile covers accumulator columns (half + i * kEpiHalves) * 32 ...
+    SC_DEVICE void request(int slot, int g, int row0, int bcol) const {
+        io_expect(io, 2048, slot);
+        tma_load_3d(&p.c_map, io.bar + slot, io.buf + slot * 2048, row0, bcol, g);
+    }
+    SC_DEVICE EpiBackCodeH(const Params& p_, const RowCtx& c_, const EpiIo& io_) : p(p_), c(c_), io(io_), db(0.f), s(0.f) {
+        const int lane = threadIdx.x & 31;
         l1_term = p.l1[c.g] * p.l1_scale;
         bn = (p.tied && c.row < c.M) ? p.bias[(long long)c.g * p.feats + c.row] : 0.f;
-    }
-    SC_DEVICE void prefetch(int co) {
-        if (c.row >= c.M) return;
-        const int col = c.col0 + co;
-        const __half* cp = p.c + c.g * p.cb_gstride + (long long)col * p.feats + c.row;
-        const int nb = c.N - col;
-        if (nb >= 32) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) nxt[j] = cp[(long long)j * p.feats];
-        } else {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) nxt[j] = (j < nb) ? cp[(long long)j * p.feats] : __float2half(0.f);
-        }
-    }
-    template <bool FULL, bool TIED>
-    SC_DEVICE void body(const __half (&cvs)[32], const float (&v)[32], __half* dp, int nb) {
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {
-            if (FULL || j < nb) {
-                const bool neg = (__half_as_ushort(cvs[j]) & 0x8000u) != 0;  // sign bit set <=> z < 0
-                const float cv = __half2float(cvs[j]);
-                const float q = v[j];
-                const float t = q + (cv > 0.f ? l1_term : 0.f);
-                const float dzv = neg ? 0.f : t;
-                dp[(long long)j * p.feats] = __float2half_rn(dzv);
-                db += dzv;
-                s = fmaf(cv, q, s);
-                if (TIED) s = fmaf(dzv, cv - bn, s);
+        for (int k = 0; k < 4; ++k) off[k] = (((lane >> 3) ^ k) << 4) + ((lane & 7) << 1);
+        if (c.first && lane == 0) {
+            for (int i = 0; i < kSlots; ++i) {
+                const int bc = c.col0 + (c.half + i * kEpiHalves) * 32;
+                if (bc < c.N && (c.half + i * kEpiHalves) * 32 < c.bn) request(i, c.g, c.row, bc);
             }
         }
     }
-    SC_DEVICE void chunk(int co, float (&v)[32], int next_co) {
-        if (c.row >= c.M) return;
-        const int col = c.col0 + co;
-        __half* dp = p.dz + c.g * p.cb_gstride + (long long)col * p.feats + c.row;
-        const int nb = c.N - col;
-        __half cvs[32];
+    SC_DEVICE void prefetch(int) {}
+    template <bool TIED>
+    SC_DEVICE void body(const uint8_t* ct, uint8_t* dt, const float (&v)[32]) {
+        const uint32_t cs = smem_u32(ct), ds = smem_u32(dt);
+        uint32_t h[32];
 #pragma unroll
-        for (int j = 0; j < 32; ++j) cvs[j] = nxt[j];
-        if (next_co >= 0) prefetch(next_co);
-        if (nb >= 32) {
-            if (p.tied) body<true, true>(cvs, v, dp, nb);
-            else body<true, false>(cvs, v, dp, nb);
-        } else {
-            if (p.tied) body<false, true>(cvs, v, dp, nb);
-            else body<false, false>(cvs, v, dp, nb);
+        for (int j = 0; j < 32; ++j) h[j] = lds_u16(cs + j * 64 + off[(j >> 1) & 3]);  // all loads in flight first
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            const bool neg = (h[j] & 0x8000u) != 0;  // sign bit set <=> z < 0
+            const float cv = __half2float(__ushort_as_half(static_cast<unsigned short>(h[j])));
+            const float q = v[j];
+            const float t = q + (cv > 0.f ? l1_term : 0.f);
+            const float dzv = neg ? 0.f : t;
+            sts_u16(ds + j * 64 + off[(j >> 1) & 3], __half_as_ushort(__float2half_rn(dzv)));
+            db += dzv;
+            s = fmaf(cv, q, s);
+            if (TIED) s = fmaf(dzv, cv - bn, s);
+        }
+    }
+    SC_DEVICE void chunk(int co, float (&v)[32], int /*next_co*/) {
+        const int lane = threadIdx.x & 31;
+        const int i = (co >> 5) / kEpiHalves;  // slot of this chunk
+        const int bcol = c.col0 + co;
+        const bool live = bcol < c.N;          // else the whole chunk lies beyond the batch: nothing was requested
+        uint8_t* dt = io.buf + kSlots * 2048 + (i & 1) * 2048;
+        if (live) {
+            const uint8_t* ct = io.buf + i * 2048;
+            io_wait_loads(io, i);
+            io_wait_stores_read_n<1>();  // the dz tile stored two chunks ago has been read
+            if (p.tied) body<true>(ct, dt, v);
+            else body<false>(ct, dt, v);
+            fence_proxy_async_smem();
+        }
+        // every lane has read slot i (and written its dz column): store, and hand the slot to the next tile's chunk i
+        __syncwarp();
+        if (lane == 0) {
+            if (live) {
+                tma_store_3d(&p.dz_map, dt, c.row, bcol, c.g);
+                tma_store_commit();
+            }
+            if (c.next_g >= 0 && c.next_col0 + co < c.N) request(i, c.next_g, c.next_row0, c.next_col0 + co);
         }
     }
     SC_DEVICE void finish() {

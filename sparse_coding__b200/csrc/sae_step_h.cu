@@ -148,7 +148,11 @@ int sae_step_f16_impl(const ScStepArgs& a) {
     prof_mark(st, "G2_decode_mse");
     {   // G3 (transposed)
         Seg s{kmajor_h(w.D_h, N, d, M, Nd), kmajor_h(w.r_h, B, d, M, Bd)};
-        EpiBackCodeH::Params ep{c_h, w.dz_h, a.l1_alpha, a.bias, w.db_part, w.s_part, BN_, 0.5f * (float)d, a.tied, N};
+        EpiBackCodeH::Params ep{};
+        SC_TRY(io_map_h(&ep.c_map, c_h, B, N, M, BN_));
+        SC_TRY(io_map_h(&ep.dz_map, w.dz_h, B, N, M, BN_));
+        ep.l1 = a.l1_alpha; ep.bias = a.bias; ep.db_part = w.db_part; ep.s_part = w.s_part;
+        ep.l1_scale = 0.5f * (float)d; ep.tied = a.tied; ep.feats = N;
         SC_TRY((run_gemm<false, false, EpiBackCodeH, true>(N, B, M, &s, 1, ep, st)));
     }
     prof_mark(st, "G3_back_code");

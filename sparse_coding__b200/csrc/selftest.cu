@@ -55,6 +55,7 @@ template <int BN, bool A_MN, bool B_MN>
 static cudaError_t run(const GemmMaps& maps, const GemmShape& sh, const EpiStore::Params& ep, int sms) {
     if (g_null) {
         EpiNull::Params en{ep.C, ep.ld, ep.gstride};
+        if (g_eb == 2) return launch_gemm_2cta<BN, A_MN, B_MN, EpiNull, 2>(maps, sh, en, sms, 0);
         if (g_cg == 2) return launch_gemm_2cta<BN, A_MN, B_MN, EpiNull>(maps, sh, en, sms, 0);
         return launch_gemm<BN, A_MN, B_MN, EpiNull>(maps, sh, en, sms, 0);
     }
@@ -142,7 +143,7 @@ int main(int argc, char** argv) {
     // timing (only meaningful for big shapes)
     cudaEvent_t e0, e1;
     CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
-    const int reps = 5;
+    const int reps = 20;
     CK(cudaEventRecord(e0));
     for (int r = 0; r < reps; ++r) { DISPATCH(64) DISPATCH(128) DISPATCH(256) }
     CK(cudaEventRecord(e1));

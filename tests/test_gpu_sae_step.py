@@ -242,3 +242,31 @@ def test_masked_mixed_dictionary_sizes(tied, shape):
                      R.sae_forward(orc.params["encoder"][1], orc.params["encoder_bias"][1], orc.params["decoder"][1],
                                    orc.buffers["l1_alpha"][1], 0.0, x, orc.buffers["coef_mask"][1]))
     assert abs(float(total) - float(orc_losses["loss"])) <= 2e-3 * abs(float(orc_losses["loss"]))
+
+
+@pytest.mark.parametrize("kind", ["untied", "tied"])
+def test_zero_preactivation_passes_gradient(kind):
+    """clamp(z, min=0) passes the gradient at z == 0 exactly (SURVEY a3 edge semantics).  An all-zero activation
+    row with zero bias gives z == +0 for every feature: its codes must be +0 (not the -0 that marks z < 0), and
+    the encoder-bias gradient must include that row's dz = q."""
+    M, B, d, N = 2, 192, 128, 256
+    ens, orc = _pair(kind, d, N, [1e-3, 1e-2], seed=3)
+    x = make_sparse_data(B, d, 2 * d, 6, seed=8)
+    x[5] = 0.0
+    x[77] = 0.0
+    grads, losses, aux = ens.compute_grads(x.cuda())
+    c = aux["c"].cpu()
+    assert not torch.signbit(c[:, [5, 77], :]).any()
+    assert torch.signbit(c).any()  # negative pre-activations elsewhere are marked
+    for m in range(M):
+        lam, beta = orc.buffers["l1_alpha"][m], orc.buffers["bias_decay"][m]
+        P = orc.params
+        if kind == "tied":
+            ls, fw = R.tied_forward(P["encoder"][m], P["encoder_bias"][m], lam, beta, x)
+            gb = R.tied_backward(P["encoder"][m], P["encoder_bias"][m], lam, beta, x, fw)[1]
+        else:
+            ls, fw = R.sae_forward(P["encoder"][m], P["encoder_bias"][m], P["decoder"][m], lam, beta, x)
+            gb = R.sae_backward(P["encoder"][m], P["encoder_bias"][m], P["decoder"][m], lam, beta, x, fw)[1]
+        assert rel_err(grads["encoder_bias"][m], gb) < 1e-2
+        # without the two zero rows' contribution the bias gradient is clearly different
+        assert float((fw["z"][[5, 77]] == 0).float().mean()) == 1.0

@@ -23,6 +23,8 @@ namespace sc {
 // v -> (hi, lo) TF32 pair, optionally also a plain copy
 __global__ void split_kernel(const float4* __restrict__ in, float4* __restrict__ hi, float4* __restrict__ lo,
                              float4* __restrict__ copy, long long n4) {
+    pdl_launch_dependents();
+    pdl_wait();
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
         const float4 v = in[i];
         float4 h, l;
@@ -140,6 +142,8 @@ struct EpiFistaStep {
 constexpr int kSquarings = 14;
 
 __global__ void normalise_split_kernel(const float* __restrict__ T, int d, float* __restrict__ hi, float* __restrict__ lo) {
+    pdl_launch_dependents();
+    pdl_wait();
     __shared__ float sh[8];
     float acc = 0.f;
     for (int i = threadIdx.x; i < d; i += blockDim.x) acc += T[(long long)i * d + i];
@@ -156,6 +160,8 @@ __global__ void normalise_split_kernel(const float* __restrict__ T, int d, float
 // One CTA: v <- T v (iters times, normalised), then eta = (v.v) / (v.G v).
 __global__ void top_eigen_kernel(const float* __restrict__ T, const float* __restrict__ G, int d, float* __restrict__ v0,
                                  float* __restrict__ v1, float* __restrict__ out_eta, int iters) {
+    pdl_launch_dependents();
+    pdl_wait();
     __shared__ float sh[8];
     const int tid = threadIdx.x, nthreads = blockDim.x, warp = tid >> 5, lane = tid & 31, nwarps = nthreads >> 5;
     for (int i = tid; i < d; i += nthreads) v0[i] = 1.0f + 0.25f * (float)((i * 37) % 101) / 101.f;
@@ -188,7 +194,9 @@ __global__ void top_eigen_kernel(const float* __restrict__ T, const float* __res
     }
 }
 
-__global__ void set_scalar_kernel(float* p, float v) { *p = v; }
+__global__ void set_scalar_kernel(float* p, float v) {
+    pdl_launch_dependents();
+    pdl_wait(); *p = v; }
 
 struct FistaWs {
     float *D_hi, *D_lo, *y, *y_hi, *y_lo, *res_hi, *res_lo, *gram, *pw, *pw_hi, *pw_lo, *v0, *v1, *eta;
@@ -211,7 +219,7 @@ static FistaWs carve_fista(void* base, int B, int d, int N) {
 static int split(const float* in, float* hi, float* lo, float* copy, long long n, cudaStream_t st) {
     const long long n4 = n / 4;
     const int grid = static_cast<int>(n4 / 256 + 1 < 4096 ? n4 / 256 + 1 : 4096);
-    split_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const float4*>(in), reinterpret_cast<float4*>(hi),
+    launch_k(split_kernel, dim3(grid), dim3(256), 0, st, reinterpret_cast<const float4*>(in), reinterpret_cast<float4*>(hi),
                                        reinterpret_cast<float4*>(lo), reinterpret_cast<float4*>(copy), n4);
     SC_CUDA(cudaGetLastError(), "split launch");
     return 0;
@@ -233,7 +241,7 @@ static int fista_impl(const ScFistaArgs& a) {
     SC_CUDA(cudaMemcpyAsync(a.out_a, a.a0, BN_ * sizeof(float), cudaMemcpyDeviceToDevice, st), "copy a0");
 
     if (a.eta > 0.f) {
-        set_scalar_kernel<<<1, 1, 0, st>>>(w.eta, a.eta);
+        launch_k(set_scalar_kernel, dim3(1), dim3(1), 0, st, w.eta, a.eta);
     } else {
         // G = D^T D in 3xTF32: both operands MN-major views of D (mn = d, k = N)
         Seg s[3] = {{mnmajor(w.D_hi, d, N, 1, 0), mnmajor(w.D_lo, d, N, 1, 0)},
@@ -250,10 +258,10 @@ static int fista_impl(const ScFistaArgs& a) {
         EpiStore::Params eq{w.pw, d, 0};
         const int ngrid = ceil_div((long long)d * d, 256 * 4) < 148 ? ceil_div((long long)d * d, 256 * 4) : 148;
         for (int k = 0; k < kSquarings; ++k) {
-            normalise_split_kernel<<<ngrid, 256, 0, st>>>(k == 0 ? w.gram : w.pw, d, w.pw_hi, w.pw_lo);
+            launch_k(normalise_split_kernel, dim3(ngrid), dim3(256), 0, st, k == 0 ? w.gram : w.pw, d, w.pw_hi, w.pw_lo);
             SC_TRY((launch_plan<false, false, EpiStore>(sq, eq, st)));
         }
-        top_eigen_kernel<<<1, 256, 0, st>>>(w.pw, w.gram, d, w.v0, w.v1, w.eta, 6);
+        launch_k(top_eigen_kernel, dim3(1), dim3(256), 0, st, w.pw, w.gram, d, w.v0, w.v1, w.eta, 6);
     }
     SC_CUDA(cudaGetLastError(), "eta launch");
 

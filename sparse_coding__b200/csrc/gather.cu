@@ -18,6 +18,8 @@ template <bool HALF>
 __global__ void __launch_bounds__(256) gather_rows_kernel(const void* __restrict__ chunk, const int64_t* __restrict__ idx,
                                                           const float* __restrict__ mean, float* __restrict__ out,
                                                           long long n_rows, int d, int B, int* __restrict__ err_flag) {
+    pdl_launch_dependents();
+    pdl_wait();
     const int lane = threadIdx.x & 31;
     const int warps = (blockDim.x >> 5) * gridDim.x;
     for (int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); b < B; b += warps) {
@@ -73,6 +75,8 @@ constexpr int kMeanSlabs = 1024;
 template <bool HALF>
 __global__ void __launch_bounds__(256) column_partial_kernel(const void* __restrict__ chunk, float* __restrict__ part,
                                                              long long n_rows, int d) {
+    pdl_launch_dependents();
+    pdl_wait();
     const long long per = (n_rows + kMeanSlabs - 1) / kMeanSlabs;
     const long long r0 = blockIdx.x * per, r1 = (r0 + per < n_rows) ? r0 + per : n_rows;
     for (int j = threadIdx.x; j < d; j += blockDim.x) {
@@ -84,6 +88,8 @@ __global__ void __launch_bounds__(256) column_partial_kernel(const void* __restr
 }
 
 __global__ void column_mean_finish_kernel(const float* __restrict__ part, float* __restrict__ out, long long n_rows, int d) {
+    pdl_launch_dependents();
+    pdl_wait();
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= d) return;
     float acc = 0.f;

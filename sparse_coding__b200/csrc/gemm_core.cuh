@@ -19,6 +19,7 @@
 // Group (member) index g lets one launch cover every SAE of the ensemble; an operand that all
 // members share (the activation batch) has gmul = 0 and is fetched from the same address by all.
 #pragma once
+#include <stdlib.h>
 #include "epi_io.cuh"
 #include "sm100_ptx.cuh"
 
@@ -131,6 +132,7 @@ gemm_tf32_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
 
+    pdl_launch_dependents();
     if (warp == 0 && lane == 0) {
         for (int s = 0; s < shape.nseg; ++s) {
             tma_prefetch_desc(&maps.a[s]);
@@ -157,6 +159,7 @@ gemm_tf32_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr;
+    pdl_wait();  // everything above touched only shared memory / TMEM; global memory from here on
 
     const int tiles_per_group = shape.tiles_m * shape.tiles_n;
     const int nprob = shape.nprob > 1 ? shape.nprob : 1;
@@ -292,6 +295,19 @@ gemm_tf32_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
     }
 }
 
+// SC_B200_PDL=0 switches programmatic dependent launch off (every kernel then waits for its predecessor to drain);
+// 1 / 2 enable it for the plain / the GEMM kernels only, 3 (default) for both.
+inline int pdl_mask() {  // bit 0: plain kernels, bit 1: GEMM kernels
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("SC_B200_PDL");
+        v = e ? atoi(e) : 3;
+    }
+    return v;
+}
+inline bool use_pdl() { return (pdl_mask() & 2) != 0; }
+inline bool use_pdl_plain() { return (pdl_mask() & 1) != 0; }
+
 // Host-side launcher: grid = min(#tiles, #SMs) persistent CTAs.
 template <int BN, bool A_MN, bool B_MN, class Epi>
 cudaError_t launch_gemm(const GemmMaps& maps, GemmShape shape, const typename Epi::Params& ep, int num_sms,
@@ -311,8 +327,17 @@ cudaError_t launch_gemm(const GemmMaps& maps, GemmShape shape, const typename Ep
     const long long total = 1LL * shape.tiles_m * shape.tiles_n * shape.G * (shape.nprob > 1 ? shape.nprob : 1);
     if (total <= 0) return cudaSuccess;
     const int grid = static_cast<int>(total < num_sms ? total : num_sms);
-    kern<<<grid, kGemmThreads, Cfg::kSmemBytes, stream>>>(maps, shape, ep);
-    return cudaGetLastError();
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(kGemmThreads);
+    cfg.dynamicSmemBytes = Cfg::kSmemBytes;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = use_pdl() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, maps, shape, ep);
 }
 
 }  // namespace sc

@@ -63,6 +63,7 @@ gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape sha
     const uint32_t rank = cluster_ctarank();
     const bool leader = rank == 0;
 
+    pdl_launch_dependents();
     cluster_sync_all();  // both CTAs resident before any cross-CTA state is touched
     if (warp == 0 && lane == 0) {
         for (int s = 0; s < shape.nseg; ++s) {
@@ -90,6 +91,7 @@ gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape sha
     cluster_sync_all();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr;
+    pdl_wait();  // everything above touched only shared memory / TMEM; global memory from here on
 
     const int nprob = shape.nprob > 1 ? shape.nprob : 1;
     const int tiles_per_group = shape.tiles_m * shape.tiles_n;  // tiles_m counts 256-row tiles here
@@ -270,13 +272,15 @@ cudaError_t launch_gemm_2cta(const GemmMaps& maps, GemmShape shape, const typena
     cfg.blockDim = dim3(kGemmThreads);
     cfg.dynamicSmemBytes = Cfg::kSmemBytes;
     cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = 2;
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
-    cfg.numAttrs = 1;
+    cfg.numAttrs = use_pdl() ? 2 : 1;
     return cudaLaunchKernelEx(&cfg, kern, maps, shape, ep);
 }
 

@@ -80,6 +80,23 @@ inline void prof_mark(cudaStream_t st, const char* name) {
     ++g_prof.n;
 }
 
+// Plain (non-GEMM) kernels of a step are launched with the programmatic-stream-serialization attribute so that
+// their launch latency overlaps the tail of the previous kernel; each of them starts with pdl_wait().
+template <class... KArgs, class... Args>
+inline cudaError_t launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = use_pdl_plain() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
 // Bump allocator over the caller's workspace; every block is 1024-byte aligned.
 struct Carver {
     uint8_t* base;

@@ -75,6 +75,8 @@ struct EpiEncodeT {
 
 // out = W / max(||W||_2, 1e-8) per row, fp32 exact division (get_learned_dict); warp per row.
 __global__ void row_normalise_kernel(const float* __restrict__ W, float* __restrict__ out, int N, int d) {
+    pdl_launch_dependents();
+    pdl_wait();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n = blockIdx.x * 8 + warp;
     if (n >= N) return;
@@ -88,6 +90,8 @@ __global__ void row_normalise_kernel(const float* __restrict__ W, float* __restr
 
 // column sums of x [B,d]: blockDim (32,8), grid (ceil(d/32), row_blocks)
 __global__ void column_sum_kernel(const float* __restrict__ x, float* __restrict__ colsum, int B, int d) {
+    pdl_launch_dependents();
+    pdl_wait();
     __shared__ float sh[8][33];
     const int j = blockIdx.x * 32 + threadIdx.x;
     float acc = 0.f;
@@ -105,6 +109,8 @@ __global__ void column_sum_kernel(const float* __restrict__ x, float* __restrict
 // sum over all elements of (x - colmean)^2
 __global__ void column_sqdev_kernel(const float* __restrict__ x, const float* __restrict__ colsum, float* __restrict__ out,
                                     int B, int d) {
+    pdl_launch_dependents();
+    pdl_wait();
     __shared__ float sh[8];
     const int j = blockIdx.x * 32 + threadIdx.x;
     float acc = 0.f;
@@ -126,6 +132,8 @@ __global__ void column_sqdev_kernel(const float* __restrict__ x, const float* __
 }
 
 __global__ void sum_parts_kernel(const float* __restrict__ part, int n, float* __restrict__ out) {
+    pdl_launch_dependents();
+    pdl_wait();
     __shared__ float sh[8];
     float acc = 0.f;
     for (int i = threadIdx.x; i < n; i += blockDim.x) acc += part[(long long)blockIdx.x * n + i];

@@ -22,30 +22,40 @@ struct EpiEncodeH {
     const Params& p;
     const RowCtx c;
     const EpiIo io;
-    float sum;
+    float sum, sum1, sum2, sum3;  // four chains: the L1 sum is not a 32-long dependent add per chunk
     int live_end;  // first column that does not count (N, or dict_size[g] when masked)
-    SC_DEVICE EpiEncodeH(const Params& p_, const RowCtx& c_, const EpiIo& io_) : p(p_), c(c_), io(io_), sum(0.f) {
+    SC_DEVICE EpiEncodeH(const Params& p_, const RowCtx& c_, const EpiIo& io_)
+        : p(p_), c(c_), io(io_), sum(0.f), sum1(0.f), sum2(0.f), sum3(0.f) {
         live_end = p.dict_size ? min(p.dict_size[c.g], c.N) : c.N;
     }
-    SC_DEVICE void prefetch(int) {}
-    SC_DEVICE void chunk(int co, float (&v)[32], int /*next_co*/) {
+    float nxt[32];  // bias of the next chunk, loaded while the current one is processed
+    SC_DEVICE void prefetch(int co) {
         const int col = c.col0 + co;
         const int ncols = c.N - col;
-        const int lane = threadIdx.x & 31;
-        float bv[32];
         if (ncols > 0) {
-            load_row32(p.bias + (long long)c.g * c.N + col, bv, ncols);
+            load_row32(p.bias + (long long)c.g * c.N + col, nxt, ncols);
         } else {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) bv[j] = 0.f;
+            for (int j = 0; j < 32; ++j) nxt[j] = 0.f;
         }
+    }
+    SC_DEVICE void chunk(int co, float (&v)[32], int next_co) {
+        const int col = c.col0 + co;
+        const int lane = threadIdx.x & 31;
+        float bv[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) bv[j] = nxt[j];
+        if (next_co >= 0) prefetch(next_co);
         const int live = live_end - col;
         // max(z, -0.0) is z for z >= 0 (max(+0, -0) = +0) and -0.0 for z < 0; adding -0.0 to the L1 sum is a no-op
         if (c.row < c.M && live >= 32) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
+            for (int j = 0; j < 32; j += 4) {
                 v[j] = fmaxf(v[j] + bv[j], -0.0f);
-                sum += v[j];
+                v[j + 1] = fmaxf(v[j + 1] + bv[j + 1], -0.0f);
+                v[j + 2] = fmaxf(v[j + 2] + bv[j + 2], -0.0f);
+                v[j + 3] = fmaxf(v[j + 3] + bv[j + 3], -0.0f);
+                sum += v[j]; sum1 += v[j + 1]; sum2 += v[j + 2]; sum3 += v[j + 3];
             }
         } else {
             const bool row_ok = c.row < c.M;
@@ -55,14 +65,14 @@ struct EpiEncodeH {
                 sum += v[j];
             }
         }
-        uint8_t* tile = io.buf + ((co >> 5) & 1) * 2048;
+        uint8_t* tile = io.buf + (((co >> 5) / kEpiHalves) & 1) * 2048;  // this warp's chunks alternate between the two tiles
         io_wait_stores_read_n<1>();  // the store issued two chunks ago has read this staging tile
         io_write_row_h(tile, lane, v);
         io_store_tile(&p.c_map, tile, col, c.row - lane, c.g);
         io_commit();
     }
     SC_DEVICE void finish() {
-        const float s = warp_sum(sum);
+        const float s = warp_sum((sum + sum1) + (sum2 + sum3));
         if ((threadIdx.x & 31) == 0) {
             const int tiles = c.tiles_m * c.tiles_n;
             p.l1_part[((long long)c.g * tiles + c.tile_n * c.tiles_m + c.tile_m) * (4 * kEpiHalves) + c.part] = s;
@@ -90,7 +100,7 @@ struct EpiDecodeH {
         const int ncols = c.N - col;
         const long long off = (long long)c.row * c.N + col;
         float xv[32];
-        load_row32(p.x + c.g * p.x_gstride + off, xv, ncols);
+        load_row32_cg(p.x + c.g * p.x_gstride + off, xv, ncols);
         __half* dst = p.r + c.g * p.out_gstride + off;
         if (ncols >= 32) {
 #pragma unroll
@@ -172,16 +182,16 @@ struct EpiBackCodeH {
     template <bool TIED>
     SC_DEVICE void body(const uint8_t* ct, uint8_t* dt, const float (&v)[32]) {
         const uint32_t cs = smem_u32(ct), ds = smem_u32(dt);
-        uint32_t h[32];
+        int32_t h[32];
 #pragma unroll
-        for (int j = 0; j < 32; ++j) h[j] = lds_u16(cs + j * 64 + off[(j >> 1) & 3]);  // all loads in flight first
+        for (int j = 0; j < 32; ++j) h[j] = lds_s16(cs + j * 64 + off[(j >> 1) & 3]);  // all loads in flight first
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
-            const bool neg = (h[j] & 0x8000u) != 0;  // sign bit set <=> z < 0
-            const float cv = __half2float(__ushort_as_half(static_cast<unsigned short>(h[j])));
+            // fp16 bit pattern, sign-extended: < 0 <=> sign bit set <=> z < 0;  > 0 <=> c > 0
+            const float cv = __half2float(__ushort_as_half(static_cast<unsigned short>(h[j] & 0xffff)));
             const float q = v[j];
-            const float t = q + (cv > 0.f ? l1_term : 0.f);
-            const float dzv = neg ? 0.f : t;
+            const float t = h[j] > 0 ? q + l1_term : q;
+            const float dzv = h[j] < 0 ? 0.f : t;
             sts_u16(ds + j * 64 + off[(j >> 1) & 3], __half_as_ushort(__float2half_rn(dzv)));
             db += dzv;
             s = fmaf(cv, q, s);

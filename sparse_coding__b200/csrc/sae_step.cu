@@ -16,6 +16,8 @@ Profiler g_prof;
 // out = rn_tf32(in), elementwise (the activation batch; n multiple of 4, 16-byte aligned)
 // ------------------------------------------------------------------------------------------------
 __global__ void round_copy_kernel(const float4* __restrict__ in, float4* __restrict__ out, long long n4) {
+    pdl_launch_dependents();
+    pdl_wait();
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
         float4 v = in[i];
         v.x = rn_tf32(v.x); v.y = rn_tf32(v.y); v.z = rn_tf32(v.z); v.w = rn_tf32(v.w);
@@ -32,6 +34,8 @@ __global__ void round_copy_kernel(const float4* __restrict__ in, float4* __restr
 __global__ void prep_params_kernel(const float* __restrict__ enc, float* __restrict__ enc_r,
                                    const float* __restrict__ W, float* __restrict__ D_r,
                                    float* __restrict__ inv_norm, int N, int d, int normalise) {
+    pdl_launch_dependents();
+    pdl_wait();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n = blockIdx.x * 8 + warp;
     if (n >= N) return;
@@ -88,6 +92,8 @@ SC_DEVICE float block_sum(float v, float* sh) {
 // elementwise Adam for the data-parallel path (gradients all-reduced by the caller)
 __global__ void adam_apply_kernel(float4* __restrict__ p, float4* __restrict__ mu, float4* __restrict__ nu,
                                   const float4* __restrict__ g, long long n4, AdamConst a) {
+    pdl_launch_dependents();
+    pdl_wait();
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
         float4 pv = p[i], mv = mu[i], nv = nu[i];
         const float4 gv = g[i];
@@ -105,6 +111,8 @@ __global__ void finalize_kernel(const float* __restrict__ l1_part, int n_l1, con
                                 const float* __restrict__ l1_alpha, const float* __restrict__ bias_decay,
                                 float* __restrict__ out_losses, int M, int B, int d, int N, int tied, AdamConst a,
                                 float* __restrict__ grad_bias, float* __restrict__ bnorm_ws, float db_scale) {
+    pdl_launch_dependents();
+    pdl_wait();
     // grid (ceil(N/256), M).  Every block needs ||b|| of the PRE-update bias: block x == 0 of each member
     // computed it into bnorm_ws in bias_norm_kernel (launched before), so no block reads a bias another
     // block already updated.
@@ -150,6 +158,8 @@ __global__ void finalize_kernel(const float* __restrict__ l1_part, int n_l1, con
 
 // ||b||_2 per member (sae_ensemble.py:64), one block per member
 __global__ void bias_norm_kernel(const float* __restrict__ bias, int N, float* __restrict__ out) {
+    pdl_launch_dependents();
+    pdl_wait();
     __shared__ float sh[8];
     float acc = 0.f;
     for (int n = threadIdx.x; n < N; n += blockDim.x) {
@@ -252,14 +262,14 @@ static int sae_step_impl(const ScStepArgs& a) {
     {
         const long long n4 = (long long)xg * Bd / 4;
         const int grid = static_cast<int>(n4 / 256 + 1 < 2048 ? n4 / 256 + 1 : 2048);
-        round_copy_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const float4*>(a.x), reinterpret_cast<float4*>(w.x_r), n4);
+        launch_k(round_copy_kernel, dim3(grid), dim3(256), 0, st, reinterpret_cast<const float4*>(a.x), reinterpret_cast<float4*>(w.x_r), n4);
     }
     prof_mark(st, "round_x");
     // 2. enc_r, D_r, 1/||W||
     {
         dim3 grid(ceil_div(N, 8), M);
-        if (a.tied) prep_params_kernel<<<grid, 256, 0, st>>>(nullptr, nullptr, a.enc, w.D_r, w.inv_norm, N, d, 1);
-        else prep_params_kernel<<<grid, 256, 0, st>>>(a.enc, w.enc_r, a.dec, w.D_r, w.inv_norm, N, d, 1);
+        if (a.tied) launch_k(prep_params_kernel, dim3(grid), dim3(256), 0, st, nullptr, nullptr, a.enc, w.D_r, w.inv_norm, N, d, 1);
+        else launch_k(prep_params_kernel, dim3(grid), dim3(256), 0, st, a.enc, w.enc_r, a.dec, w.D_r, w.inv_norm, N, d, 1);
         SC_CUDA(cudaGetLastError(), "prep launch");
     }
     prof_mark(st, "prep_params");
@@ -319,8 +329,8 @@ static int sae_step_impl(const ScStepArgs& a) {
     }
     prof_mark(st, "G45_dW_adam");
     // 8. loss scalars + bias Adam
-    bias_norm_kernel<<<M, 256, 0, st>>>(a.bias, N, w.bnorm);
-    finalize_kernel<<<dim3(ceil_div(N, 256), M), 256, 0, st>>>(w.l1_part, w.n_l1, w.mse_part, w.n_mse, w.db_part, w.tiles_b,
+    launch_k(bias_norm_kernel, dim3(M), dim3(256), 0, st, a.bias, N, w.bnorm);
+    launch_k(finalize_kernel, dim3(dim3(ceil_div(N, 256), M)), dim3(256), 0, st, w.l1_part, w.n_l1, w.mse_part, w.n_mse, w.db_part, w.tiles_b,
                                                              a.bias, a.bias_mu, a.bias_nu, a.l1_alpha, a.bias_decay,
                                                              a.out_losses, M, Bn, d, N, a.tied, ad,
                                                              grad_mode ? a.grad_bias : nullptr, w.bnorm, 1.0f);
@@ -370,7 +380,7 @@ int sc_adam_apply(float* p, float* mu, float* nu, const float* g, int64_t n, con
     if (!p || !mu || !nu || !g || !adam || n <= 0 || (n & 3)) return fail(-1, "bad sc_adam_apply argument");
     const long long n4 = n / 4;
     const int grid = static_cast<int>(n4 / 256 + 1 < 148 * 16 ? n4 / 256 + 1 : 148 * 16);
-    adam_apply_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+    launch_k(adam_apply_kernel, dim3(grid), dim3(256), 0, static_cast<cudaStream_t>(stream), 
         reinterpret_cast<float4*>(p), reinterpret_cast<float4*>(mu), reinterpret_cast<float4*>(nu),
         reinterpret_cast<const float4*>(g), n4, make_adam(*adam));
     SC_CUDA(cudaGetLastError(), "adam_apply launch");

@@ -9,6 +9,8 @@
 namespace sc {
 
 __global__ void to_half_kernel(const float4* __restrict__ in, uint2* __restrict__ out, long long n4) {
+    pdl_launch_dependents();
+    pdl_wait();
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
         const float4 v = in[i];
         __half2 h[2] = {__floats2half2_rn(v.x, v.y), __floats2half2_rn(v.z, v.w)};
@@ -17,6 +19,8 @@ __global__ void to_half_kernel(const float4* __restrict__ in, uint2* __restrict_
 }
 
 __global__ void half_to_float_kernel(const uint2* __restrict__ in, float4* __restrict__ out, long long n4) {
+    pdl_launch_dependents();
+    pdl_wait();
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
         uint2 u = in[i];
         const __half2* h = reinterpret_cast<const __half2*>(&u);
@@ -29,6 +33,8 @@ __global__ void half_to_float_kernel(const uint2* __restrict__ in, float4* __res
 __global__ void prep_params_h_kernel(const float* __restrict__ enc, __half* __restrict__ enc_h,
                                      const float* __restrict__ W, __half* __restrict__ D_h,
                                      float* __restrict__ inv_norm, int N, int d) {
+    pdl_launch_dependents();
+    pdl_wait();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n = blockIdx.x * 8 + warp;
     if (n >= N) return;
@@ -123,12 +129,12 @@ int sae_step_f16_impl(const ScStepArgs& a) {
     __half* c_h = static_cast<__half*>(a.out_c_half);
 
     prof_mark(st, "begin");
-    to_half_kernel<<<grid1d(xg * Bd / 4), 256, 0, st>>>(reinterpret_cast<const float4*>(a.x), reinterpret_cast<uint2*>(w.x_h), xg * Bd / 4);
+    launch_k(to_half_kernel, dim3(grid1d(xg * Bd / 4)), dim3(256), 0, st, reinterpret_cast<const float4*>(a.x), reinterpret_cast<uint2*>(w.x_h), xg * Bd / 4);
     prof_mark(st, "round_x");
     {
         dim3 grid(ceil_div(N, 8), M);
-        if (a.tied) prep_params_h_kernel<<<grid, 256, 0, st>>>(nullptr, nullptr, a.enc, w.D_h, w.inv_norm, N, d);
-        else prep_params_h_kernel<<<grid, 256, 0, st>>>(a.enc, w.enc_h, a.dec, w.D_h, w.inv_norm, N, d);
+        if (a.tied) launch_k(prep_params_h_kernel, dim3(grid), dim3(256), 0, st, nullptr, nullptr, a.enc, w.D_h, w.inv_norm, N, d);
+        else launch_k(prep_params_h_kernel, dim3(grid), dim3(256), 0, st, a.enc, w.enc_h, a.dec, w.D_h, w.inv_norm, N, d);
         SC_CUDA(cudaGetLastError(), "prep launch");
     }
     prof_mark(st, "prep_params");
@@ -185,15 +191,15 @@ int sae_step_f16_impl(const ScStepArgs& a) {
         }
     }
     prof_mark(st, "G45_dW_adam");
-    bias_norm_kernel<<<M, 256, 0, st>>>(a.bias, N, w.bnorm);
-    finalize_kernel<<<dim3(ceil_div(N, 256), M), 256, 0, st>>>(w.l1_part, w.n_l1, w.mse_part, w.n_mse, w.db_part, w.tiles_b,
+    launch_k(bias_norm_kernel, dim3(M), dim3(256), 0, st, a.bias, N, w.bnorm);
+    launch_k(finalize_kernel, dim3(dim3(ceil_div(N, 256), M)), dim3(256), 0, st, w.l1_part, w.n_l1, w.mse_part, w.n_mse, w.db_part, w.tiles_b,
                                                              a.bias, a.bias_mu, a.bias_nu, a.l1_alpha, a.bias_decay,
                                                              a.out_losses, M, Bn, d, N, a.tied, ad,
                                                              grad_mode ? a.grad_bias : nullptr, w.bnorm, sc_);
     SC_CUDA(cudaGetLastError(), "finalize launch");
     prof_mark(st, "finalize");
     if (a.out_c) {  // caller wants the fp32 aux tensor as well
-        half_to_float_kernel<<<grid1d(M * BN_ / 4), 256, 0, st>>>(reinterpret_cast<const uint2*>(c_h),
+        launch_k(half_to_float_kernel, dim3(grid1d(M * BN_ / 4)), dim3(256), 0, st, reinterpret_cast<const uint2*>(c_h),
                                                                reinterpret_cast<float4*>(a.out_c), M * BN_ / 4);
         SC_CUDA(cudaGetLastError(), "c conversion launch");
     }

@@ -74,6 +74,14 @@ SC_DEVICE void tma_store_3d(const CUtensorMap* m, const void* smem_src, int c0, 
 SC_DEVICE void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 template <int N>
 SC_DEVICE void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
+// Programmatic dependent launch: a kernel launched with the programmatic-stream-serialization attribute may
+// start (prologue: barrier init, TMEM allocation, descriptor prefetch) while its predecessor in the stream is
+// still draining; pdl_wait() blocks until the predecessor has completed and its writes are visible, so it
+// must precede the first access to global memory.  pdl_launch_dependents() lets the successor do the same.
+// Both are no-ops for a kernel launched the ordinary way.
+SC_DEVICE void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+SC_DEVICE void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // Explicit shared-space accesses by 32-bit shared address.  The epilogue staging tiles are reached through
 // pointers the compiler cannot prove to be shared memory; left to itself it emits generic LD/ST with 64-bit
 // address arithmetic and orders every load behind the previous (possibly aliasing) store.
@@ -91,6 +99,11 @@ SC_DEVICE void sts_128u(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint3
 SC_DEVICE uint32_t lds_u16(uint32_t addr) {
     uint16_t v;
     asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(addr));
+    return v;
+}
+SC_DEVICE int32_t lds_s16(uint32_t addr) {  // sign-extended
+    int32_t v;
+    asm volatile("ld.shared.s16 %0, [%1];" : "=r"(v) : "r"(addr));
     return v;
 }
 SC_DEVICE void sts_u16(uint32_t addr, uint16_t v) { asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "h"(v) : "memory"); }

@@ -270,3 +270,38 @@ def test_zero_preactivation_passes_gradient(kind):
         assert rel_err(grads["encoder_bias"][m], gb) < 1e-2
         # without the two zero rows' contribution the bias gradient is clearly different
         assert float((fw["z"][[5, 77]] == 0).float().mean()) == 1.0
+
+
+@pytest.mark.parametrize("kind,fmt", [("tied", "auto"), ("untied", "auto"), ("untied", "tf32")])
+def test_back_to_back_steps_equal_synchronised_steps(kind, fmt):
+    """Steps enqueued back to back with no host synchronisation, every aux kept alive (so each step's code
+    buffer is a fresh allocation, whose first touch is slow) must give bit-identical losses to the same steps run
+    one at a time.  Guards the asynchronous staging-tile / TMA-store hand-offs inside the epilogues: a staging
+    tile reused before its store had read it only shows up when stores are slow and nothing waits in between."""
+    import sparse_coding__b200 as sc
+    M, B, d, N = 4, 1024, 256, 512
+    data = make_sparse_data(8 * B, d, 2 * d, 8, seed=9).cuda()
+    g = torch.Generator().manual_seed(11)
+    idxs = [torch.randint(0, data.shape[0], (B,), generator=g).cuda() for _ in range(12)]
+
+    def run(synchronise):
+        models, sig = _models(kind, d, N, np.logspace(-4, -2.5, M), seed=7)
+        ens = sc.FunctionalEnsemble(models, sig, sc.torchopt_compat.adam, {"lr": 1e-3}, device="cuda")
+        ens.operand_format = fmt
+        out, keep = [], []
+        for i in range(len(idxs)):
+            losses, aux = ens.step_batch(data[idxs[i]])
+            if synchronise:
+                torch.cuda.synchronize()
+            else:
+                keep.append(aux)
+            out.append(torch.stack([losses["loss"], losses["l_reconstruction"], losses["l_l1"]]))
+        torch.cuda.synchronize()
+        return torch.stack(out).cpu(), ens
+
+    torch.cuda.empty_cache()  # the asynchronous run below starts without cached blocks to recycle
+    got, ens_a = run(False)
+    want, ens_s = run(True)
+    assert torch.equal(got, want)
+    for k in ens_a.params:
+        assert torch.equal(ens_a.params[k], ens_s.params[k]), k

@@ -45,6 +45,44 @@ def ensemble_case(name, sig, M, d, N, B, out):
     torch.cuda.empty_cache()
 
 
+def input_pipeline_case(M=8, d=512, N=4096, B=2048, rows=1 << 20):
+    """ensemble_train_loop fed (a) the reference way - fp32 chunk in host memory, torch BatchSampler, per-step host
+    gather + H2D (big_sweep.py:170) - and (b) from a ResidentChunk (fp16 in HBM, sc_gather_rows, device sampler)."""
+    class Cfg:
+        use_wandb = False
+
+    class Counter:
+        value = 0
+
+    torch.manual_seed(0)
+    chunk_h = torch.randn(rows, d).half()
+    res = {}
+    for mode in ("host_fp32_chunk", "resident_fp16_chunk"):
+        models = [sc.FunctionalSAE.init(d, N, float(l1), device="cuda") for l1 in np.logspace(-4, -2, M)]
+        ens = sc.FunctionalEnsemble(models, sc.FunctionalSAE, sc.torchopt_compat.adam, {"lr": 1e-3}, device="cuda")
+        if mode == "host_fp32_chunk":
+            ds = chunk_h.to(torch.float32)
+            n_batches = 40
+            sampler = [b for _, b in zip(range(n_batches), torch.utils.data.BatchSampler(
+                torch.utils.data.RandomSampler(range(rows)), batch_size=B, drop_last=False))]
+        else:
+            ds = sc.ResidentChunk(chunk_h, device="cuda")
+            n_batches = 400
+            sampler = [b for _, b in zip(range(n_batches), sc.DeviceBatchSampler(rows, B, device="cuda", seed=0))]
+        sc.ensemble_train_loop(ens, Cfg(), {"device": "cuda"}, "e", sampler[:5], ds, Counter(), torch.float32,
+                               fista_dictionary_update=False)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        sc.ensemble_train_loop(ens, Cfg(), {"device": "cuda"}, "e", sampler, ds, Counter(), torch.float32,
+                               fista_dictionary_update=False)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        res[mode] = {"batches": n_batches, "ms_per_step": dt / n_batches * 1e3, "member_act_per_s": M * B * n_batches / dt}
+        del ens, ds
+        torch.cuda.empty_cache()
+    return res
+
+
 def main():
     out = {}
     for B in (1024, 2048, 4096, 8192):
@@ -84,6 +122,7 @@ def main():
         "mean_nonzero_ms": timed(lambda: sm.mean_nonzero_activations(ld, xs), 2, 5),
         "encode_ms": timed(lambda: ld.encode(xs[:65536]), 2, 5),
     }
+    out["train_loop_input_pipeline"] = input_pipeline_case()
     print(json.dumps(out, indent=1))
 
 

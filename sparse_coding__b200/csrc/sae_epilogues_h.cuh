@@ -100,7 +100,7 @@ struct EpiDecodeH {
         const int ncols = c.N - col;
         const long long off = (long long)c.row * c.N + col;
         float xv[32];
-        load_row32_cg(p.x + c.g * p.x_gstride + off, xv, ncols);
+        load_row32(p.x + c.g * p.x_gstride + off, xv, ncols);
         __half* dst = p.r + c.g * p.out_gstride + off;
         if (ncols >= 32) {
 #pragma unroll

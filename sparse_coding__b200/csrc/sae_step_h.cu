@@ -1,4 +1,5 @@
-// fp16-operand mode of sc_sae_step (ScStepArgs.operand_format == 1): same eight launches, GEMM operands
+// fp16-operand mode of sc_sae_step (ScStepArgs.operand_format == 1): six launches (prologue, G1, G2, G3, G4+G5,
+// finalize), GEMM operands
 // and the intermediate tensors c / r / dz in fp16 (see sae_epilogues_h.cuh for the scaling), master
 // weights, Adam state, accumulators and all loss arithmetic in fp32.  Needs the CTA-pair kernel, d and N
 // multiples of 64 and >= 128, B > 64 (sc_sae_step_f16_supported); other shapes use the TF32 mode.
@@ -59,6 +60,75 @@ __global__ void prep_params_h_kernel(const float* __restrict__ enc, __half* __re
     const float nrm = sqrtf(ss);
     const float inv = 1.f / fmaxf(nrm, 1e-8f);
     if (lane == 0) inv_norm[(long long)blockIdx.y * N + n] = nrm < 1e-8f ? -inv : inv;
+    uint2* dst = reinterpret_cast<uint2*>(D_h + row);
+    for (int i = lane; i < d4; i += 32) {
+        const float4 v = src[i];
+        __half2 h[2] = {__floats2half2_rn(v.x * inv, v.y * inv), __floats2half2_rn(v.z * inv, v.w * inv)};
+        dst[i] = *reinterpret_cast<uint2*>(h);
+    }
+}
+
+// One launch for everything a step needs before its first GEMM (three launches and two kernel boundaries less):
+//   blocks [0, M)                  ||b||_2 of member m (pre-update bias, for the bias-decay term in finalize)
+//   blocks [M, M + x_blocks)       x_h = half(x)
+//   the rest, ceil(N/8) per member operand preparation, one warp per dictionary row (prep_params_h_kernel)
+// The long-latency single-block jobs come first so that they are scheduled first.
+__global__ void __launch_bounds__(256) step_prologue_h_kernel(const float* __restrict__ bias, float* __restrict__ bnorm, int M,
+                                                              const float4* __restrict__ x, uint2* __restrict__ x_h,
+                                                              long long x_n4, int x_blocks, const float* __restrict__ enc,
+                                                              __half* __restrict__ enc_h, const float* __restrict__ W,
+                                                              __half* __restrict__ D_h, float* __restrict__ inv_norm, int N,
+                                                              int d) {
+    pdl_launch_dependents();
+    pdl_wait();
+    __shared__ float sh[8];
+    int blk = blockIdx.x;
+    if (blk < M) {
+        float acc = 0.f;
+        for (int n = threadIdx.x; n < N; n += blockDim.x) {
+            const float b = bias[(long long)blk * N + n];
+            acc = fmaf(b, b, acc);
+        }
+        const float t = block_sum(acc, sh);
+        if (threadIdx.x == 0) bnorm[blk] = sqrtf(t);
+        return;
+    }
+    blk -= M;
+    if (blk < x_blocks) {
+        for (long long i = blk * (long long)blockDim.x + threadIdx.x; i < x_n4; i += (long long)x_blocks * blockDim.x) {
+            const float4 v = x[i];
+            __half2 h[2] = {__floats2half2_rn(v.x, v.y), __floats2half2_rn(v.z, v.w)};
+            x_h[i] = *reinterpret_cast<uint2*>(h);
+        }
+        return;
+    }
+    blk -= x_blocks;
+    const int row_blocks = (N + 7) >> 3;
+    const int m = blk / row_blocks;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n = (blk - m * row_blocks) * 8 + warp;
+    if (n >= N) return;
+    const long long row = ((long long)m * N + n) * d;
+    const int d4 = d >> 2;
+    if (enc_h) {
+        const float4* src = reinterpret_cast<const float4*>(enc + row);
+        uint2* dst = reinterpret_cast<uint2*>(enc_h + row);
+        for (int i = lane; i < d4; i += 32) {
+            const float4 v = src[i];
+            __half2 h[2] = {__floats2half2_rn(v.x, v.y), __floats2half2_rn(v.z, v.w)};
+            dst[i] = *reinterpret_cast<uint2*>(h);
+        }
+    }
+    const float4* src = reinterpret_cast<const float4*>(W + row);
+    float ss = 0.f;
+    for (int i = lane; i < d4; i += 32) {
+        const float4 v = src[i];
+        ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+    }
+    ss = warp_sum(ss);
+    const float nrm = sqrtf(ss);
+    const float inv = 1.f / fmaxf(nrm, 1e-8f);
+    if (lane == 0) inv_norm[(long long)m * N + n] = nrm < 1e-8f ? -inv : inv;
     uint2* dst = reinterpret_cast<uint2*>(D_h + row);
     for (int i = lane; i < d4; i += 32) {
         const float4 v = src[i];
@@ -129,15 +199,19 @@ int sae_step_f16_impl(const ScStepArgs& a) {
     __half* c_h = static_cast<__half*>(a.out_c_half);
 
     prof_mark(st, "begin");
-    launch_k(to_half_kernel, dim3(grid1d(xg * Bd / 4)), dim3(256), 0, st, reinterpret_cast<const float4*>(a.x), reinterpret_cast<uint2*>(w.x_h), xg * Bd / 4);
-    prof_mark(st, "round_x");
     {
-        dim3 grid(ceil_div(N, 8), M);
-        if (a.tied) launch_k(prep_params_h_kernel, dim3(grid), dim3(256), 0, st, nullptr, nullptr, a.enc, w.D_h, w.inv_norm, N, d);
-        else launch_k(prep_params_h_kernel, dim3(grid), dim3(256), 0, st, a.enc, w.enc_h, a.dec, w.D_h, w.inv_norm, N, d);
-        SC_CUDA(cudaGetLastError(), "prep launch");
+        const long long x_n4 = xg * Bd / 4;
+        const int x_blocks = static_cast<int>(x_n4 / 1024 + 1 < 1024 ? x_n4 / 1024 + 1 : 1024);
+        const int blocks = M + x_blocks + ceil_div(N, 8) * M;
+        if (a.tied)
+            launch_k(step_prologue_h_kernel, dim3(blocks), dim3(256), 0, st, a.bias, w.bnorm, M, reinterpret_cast<const float4*>(a.x),
+                     reinterpret_cast<uint2*>(w.x_h), x_n4, x_blocks, nullptr, nullptr, a.enc, w.D_h, w.inv_norm, N, d);
+        else
+            launch_k(step_prologue_h_kernel, dim3(blocks), dim3(256), 0, st, a.bias, w.bnorm, M, reinterpret_cast<const float4*>(a.x),
+                     reinterpret_cast<uint2*>(w.x_h), x_n4, x_blocks, a.enc, w.enc_h, a.dec, w.D_h, w.inv_norm, N, d);
+        SC_CUDA(cudaGetLastError(), "prologue launch");
     }
-    prof_mark(st, "prep_params");
+    prof_mark(st, "prologue");
     {   // G1
         Seg s{kmajor_h(w.x_h, B, d, xg, Bd), kmajor_h(a.tied ? w.D_h : w.enc_h, N, d, M, Nd)};
         EpiEncodeH::Params ep{};
@@ -191,7 +265,6 @@ int sae_step_f16_impl(const ScStepArgs& a) {
         }
     }
     prof_mark(st, "G45_dW_adam");
-    launch_k(bias_norm_kernel, dim3(M), dim3(256), 0, st, a.bias, N, w.bnorm);
     launch_k(finalize_kernel, dim3(dim3(ceil_div(N, 256), M)), dim3(256), 0, st, w.l1_part, w.n_l1, w.mse_part, w.n_mse, w.db_part, w.tiles_b,
                                                              a.bias, a.bias_mu, a.bias_nu, a.l1_alpha, a.bias_decay,
                                                              a.out_losses, M, Bn, d, N, a.tied, ad,

@@ -355,7 +355,9 @@ def run_ours(args):
                                 "working set per step > 1 GB"},
         "activations_per_sec": value / (M * world) ,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": B * D_ACT * 4, "d2h_bytes_per_step": M * 4},
-        "gpu_launches": 8 * args.steps,
+        # our kernels per step: one launch mark each in the library (fp16 mode: prologue, G1, G2, G3, G4+G5,
+        # finalize = 6); the TF32 mode's last mark covers two launches (bias norm + finalize)
+        "gpu_launches": (len(marks) // prof_steps + (0 if fmt == "f16" else 1)) * args.steps,
         "roofline": roofline, "cpu_baseline": cpu_baseline, "clocks": clocks.summary(),
     }
     print(json.dumps(line))

@@ -65,6 +65,13 @@ struct GemmCfg {
     static_assert(kStages >= 2, "not enough shared memory left for the operand pipeline");
 };
 
+// Epilogue warps per 32-row quarter of the tile: kEpiHalves unless the functor asks for more (Epi::kHalves; only
+// the CTA-pair kernel honours it).  More warps = more issue slots for instruction-bound epilogues, fewer chunks each.
+template <class E, class = void>
+struct EpiHalvesOf { static constexpr int v = kEpiHalves; };
+template <class E>
+struct EpiHalvesOf<E, decltype((void)E::kHalves)> { static constexpr int v = E::kHalves; };
+
 // Context handed to an epilogue functor for one accumulator row of one tile.
 struct RowCtx {
     int g;       // group / ensemble member
@@ -75,8 +82,9 @@ struct RowCtx {
     int tiles_m, tiles_n;
     int warp_q;  // which 32-row quarter of the tile this warp owns (0..3)
     int prob;    // problem index when the launch batches independent problems (else 0)
-    int half;    // which of the kEpiHalves warps of that quarter (takes chunks half, half+2, ...)
-    int part;    // warp_q + 4*half: slot for per-warp partial results (0..4*kEpiHalves-1)
+    int half;    // which of the `halves` warps of that quarter (takes chunks half, half+halves, ...)
+    int halves;  // epilogue warps per quarter in this launch (EpiHalvesOf<Epi>)
+    int part;    // warp_q + 4*half: slot for per-warp partial results (0..4*halves-1)
     // the tile this warp processes next (static schedule), for functors that prefetch across tiles:
     int bn;         // tile width in columns
     int first;      // 1 on the warp's first tile (nothing was prefetched for it)
@@ -92,7 +100,8 @@ template <int BN, class Epi, class Release>
 SC_DEVICE void epilogue_tile(const typename Epi::Params& ep, const RowCtx& ctx, const EpiIo& io, uint64_t* full_bar,
                              uint32_t parity, uint32_t taddr, Release release) {
     Epi epi(ep, ctx, io);
-    constexpr int kChunks = (BN / 32 + kEpiHalves - 1) / kEpiHalves;
+    constexpr int kH = EpiHalvesOf<Epi>::v;
+    constexpr int kChunks = (BN / 32 + kH - 1) / kH;
     // global loads the functor needs for its first chunk do not depend on the accumulator: issue them
     // before waiting for the MMAs, and the next chunk's while the current one is processed
     if (ctx.half < BN / 32) epi.prefetch(ctx.half * 32);
@@ -100,12 +109,12 @@ SC_DEVICE void epilogue_tile(const typename Epi::Params& ep, const RowCtx& ctx, 
     tc_fence_after();
 #pragma unroll 1  // keep the (large) functor body in the instruction cache
     for (int i = 0; i < kChunks; ++i) {
-        const int c = ctx.half + i * kEpiHalves;
+        const int c = ctx.half + i * kH;
         if (c < BN / 32) {
             float v[32];
             tmem_ld32(taddr + c * 32, v);
             tmem_ld_wait();
-            epi.chunk(c * 32, v, (c + kEpiHalves < BN / 32) ? (c + kEpiHalves) * 32 : -1);
+            epi.chunk(c * 32, v, (c + kH < BN / 32) ? (c + kH) * 32 : -1);
         }
     }
     tc_fence_before();
@@ -118,6 +127,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tf32_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
                  const __grid_constant__ typename Epi::Params ep) {
     using Cfg = GemmCfg<BN, Epi::kIoBufs>;
+    static_assert(EpiHalvesOf<Epi>::v == kEpiHalves, "the single-CTA kernel runs kEpiHalves epilogue warps per quarter");
     constexpr int kStages = Cfg::kStages;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -271,7 +281,7 @@ gemm_tf32_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
             const uint32_t aph = (it >> 1) & 1;
             RowCtx ctx;
             ctx.g = g; ctx.row = tm * kBlockM + q * 32 + lane; ctx.col0 = tn * BN;
-            ctx.M = shape.M; ctx.N = shape.N; ctx.tile_m = tm; ctx.tile_n = tn; ctx.tiles_m = shape.tiles_m; ctx.tiles_n = shape.tiles_n; ctx.warp_q = q; ctx.prob = prob; ctx.half = half; ctx.part = q + 4 * half;
+            ctx.M = shape.M; ctx.N = shape.N; ctx.tile_m = tm; ctx.tile_n = tn; ctx.tiles_m = shape.tiles_m; ctx.tiles_n = shape.tiles_n; ctx.warp_q = q; ctx.prob = prob; ctx.half = half; ctx.halves = kEpiHalves; ctx.part = q + 4 * half;
             ctx.bn = BN; ctx.first = it == 0;
             ctx.next_g = -1; ctx.next_row0 = 0; ctx.next_col0 = 0;
             if (tile + static_cast<int>(gridDim.x) < total_tiles) {

@@ -19,16 +19,18 @@
 
 namespace sc {
 
-template <int BN, int IO = 0>
+template <int BN, int IO = 0, int H = kEpiHalves>
 struct GemmCfg2 {
+    static constexpr int kWarpsEpi = 4 * H;
+    static constexpr int kThreads = 128 + 32 * kWarpsEpi;
     static constexpr int kBHalf = BN / 2;
     static constexpr int kBTileBytes = kBHalf * kBlockK * 4;
     static constexpr int kStageBytes = kATileBytes + kBTileBytes;
-    static constexpr int kIoBytes = kEpiWarps * IO * kIoTileBytes;
+    static constexpr int kIoBytes = kWarpsEpi * IO * kIoTileBytes;
     static constexpr int kStagesRaw = (227 * 1024 - 2048 - kIoBytes) / kStageBytes;
     static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
     static constexpr int kTmemCols = GemmCfg<BN>::kTmemCols;
-    static constexpr int kBarrierBytes = (2 * kStages + 4 + kIoBars * kEpiWarps) * 8 + 16;
+    static constexpr int kBarrierBytes = (2 * kStages + 4 + kIoBars * kWarpsEpi) * 8 + 16;
     static constexpr int kSmemBytes = kStages * kStageBytes + kIoBytes + kBarrierBytes + 1024;
     static_assert(BN % 64 == 0 && BN >= 64 && BN <= 256, "paired kernel: BN multiple of 64 in [64,256]");
     static_assert(kStages >= 2, "not enough shared memory left for the operand pipeline");
@@ -38,10 +40,11 @@ struct GemmCfg2 {
 // 2 (fp16, .kind::f16, 64 elements).  Tile bytes, stage bytes and the four MMAs per k-block are the same.
 // MN-major fp16 tiles use the plain 128-byte swizzle: chunks of 64 m/n x 64 k (8 KB), 8-row groups 1 KB apart.
 template <int BN, bool A_MN, bool B_MN, class Epi, int EB = 4>
-__global__ void __launch_bounds__(kGemmThreads, 1)
+__global__ void __launch_bounds__(128 + 128 * EpiHalvesOf<Epi>::v, 1)
 gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
                       const __grid_constant__ typename Epi::Params ep) {
-    using Cfg = GemmCfg2<BN, Epi::kIoBufs>;
+    constexpr int kH = EpiHalvesOf<Epi>::v;
+    using Cfg = GemmCfg2<BN, Epi::kIoBufs, kH>;
     constexpr int kStages = Cfg::kStages;
     constexpr int kBHalf = Cfg::kBHalf;
     constexpr int kKElems = 128 / EB;            // operand elements per k-block
@@ -56,7 +59,7 @@ gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape sha
     uint64_t* tmem_full = empty_bar + kStages;
     uint64_t* tmem_empty = tmem_full + 2;
     uint64_t* io_bar = tmem_empty + 2;
-    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(io_bar + kIoBars * kEpiWarps);
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(io_bar + kIoBars * Cfg::kWarpsEpi);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -78,9 +81,9 @@ gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape sha
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(&tmem_full[i], 1);
-            mbar_init(&tmem_empty[i], 2 * 128 * kEpiHalves);  // epilogue threads of BOTH CTAs (leader's copy is used)
+            mbar_init(&tmem_empty[i], 2 * 128 * kH);  // epilogue threads of BOTH CTAs (leader's copy is used)
         }
-        for (int i = 0; i < kIoBars * kEpiWarps; ++i) mbar_init(&io_bar[i], 1);
+        for (int i = 0; i < kIoBars * Cfg::kWarpsEpi; ++i) mbar_init(&io_bar[i], 1);
         fence_mbar_init();
     }
     if (warp == 2) {
@@ -218,7 +221,7 @@ gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape sha
             ctx.M = shape.M; ctx.N = shape.N;
             // partial-sum slots are indexed by 128-row tile: report this CTA's half as its own row tile
             ctx.tile_m = tm * 2 + rank; ctx.tile_n = tn; ctx.tiles_m = shape.tiles_m * 2; ctx.tiles_n = shape.tiles_n;
-            ctx.warp_q = q; ctx.prob = prob; ctx.half = half; ctx.part = q + 4 * half;
+            ctx.warp_q = q; ctx.prob = prob; ctx.half = half; ctx.halves = kH; ctx.part = q + 4 * half;
             ctx.bn = BN; ctx.first = it == 0;
             ctx.next_g = -1; ctx.next_row0 = 0; ctx.next_col0 = 0;
             if (tile + num_clusters < total_tiles) {
@@ -251,7 +254,7 @@ gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape sha
 template <int BN, bool A_MN, bool B_MN, class Epi, int EB = 4>
 cudaError_t launch_gemm_2cta(const GemmMaps& maps, GemmShape shape, const typename Epi::Params& ep, int num_sms,
                              cudaStream_t stream) {
-    using Cfg = GemmCfg2<BN, Epi::kIoBufs>;
+    using Cfg = GemmCfg2<BN, Epi::kIoBufs, EpiHalvesOf<Epi>::v>;
     auto kern = gemm_tf32_2cta_kernel<BN, A_MN, B_MN, Epi, EB>;
     static bool attr_set[64] = {};
     int dev = 0;
@@ -269,7 +272,7 @@ cudaError_t launch_gemm_2cta(const GemmMaps& maps, GemmShape shape, const typena
     const int clusters = static_cast<int>(total < pairs ? total : pairs);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(2 * clusters);
-    cfg.blockDim = dim3(kGemmThreads);
+    cfg.blockDim = dim3(Cfg::kThreads);
     cfg.dynamicSmemBytes = Cfg::kSmemBytes;
     cfg.stream = stream;
     cudaLaunchAttribute attr[2];

@@ -186,26 +186,27 @@ inline int plan_gemm(GemmPlan* pl, int M, int N, int G, const Seg* segs, int nse
 template <bool A_MN, bool B_MN, class Epi, bool F16 = false>
 int launch_plan(const GemmPlan& pl, const typename Epi::Params& ep, cudaStream_t stream) {
     cudaError_t e;
-    if (F16) {
+    if constexpr (F16) {  // fp16 epilogues exist for the CTA-pair kernel only
         if (pl.eb != 2 || pl.bn < 128) return fail(-3, "fp16 operand path needs bn >= 128");
         if (pl.bn == 256) e = launch_gemm_2cta<256, A_MN, B_MN, Epi, 2>(pl.maps, pl.sh, ep, pl.sms, stream);
         else e = launch_gemm_2cta<128, A_MN, B_MN, Epi, 2>(pl.maps, pl.sh, ep, pl.sms, stream);
         if (e != cudaSuccess) return cuda_fail(e, "gemm (fp16, CTA pair) launch");
         return 0;
-    }
-    if (pl.eb != 4) return fail(-3, "fp16 operands given to a TF32 launch");
-    if (pl.cta2) {
-        if (pl.bn == 256) e = launch_gemm_2cta<256, A_MN, B_MN, Epi>(pl.maps, pl.sh, ep, pl.sms, stream);
-        else if (pl.bn == 128) e = launch_gemm_2cta<128, A_MN, B_MN, Epi>(pl.maps, pl.sh, ep, pl.sms, stream);
-        else e = launch_gemm_2cta<64, A_MN, B_MN, Epi>(pl.maps, pl.sh, ep, pl.sms, stream);
-        if (e != cudaSuccess) return cuda_fail(e, "gemm (CTA pair) launch");
+    } else {
+        if (pl.eb != 4) return fail(-3, "fp16 operands given to a TF32 launch");
+        if (pl.cta2) {
+            if (pl.bn == 256) e = launch_gemm_2cta<256, A_MN, B_MN, Epi>(pl.maps, pl.sh, ep, pl.sms, stream);
+            else if (pl.bn == 128) e = launch_gemm_2cta<128, A_MN, B_MN, Epi>(pl.maps, pl.sh, ep, pl.sms, stream);
+            else e = launch_gemm_2cta<64, A_MN, B_MN, Epi>(pl.maps, pl.sh, ep, pl.sms, stream);
+            if (e != cudaSuccess) return cuda_fail(e, "gemm (CTA pair) launch");
+            return 0;
+        }
+        if (pl.bn == 256) e = launch_gemm<256, A_MN, B_MN, Epi>(pl.maps, pl.sh, ep, pl.sms, stream);
+        else if (pl.bn == 128) e = launch_gemm<128, A_MN, B_MN, Epi>(pl.maps, pl.sh, ep, pl.sms, stream);
+        else e = launch_gemm<64, A_MN, B_MN, Epi>(pl.maps, pl.sh, ep, pl.sms, stream);
+        if (e != cudaSuccess) return cuda_fail(e, "gemm launch");
         return 0;
     }
-    if (pl.bn == 256) e = launch_gemm<256, A_MN, B_MN, Epi>(pl.maps, pl.sh, ep, pl.sms, stream);
-    else if (pl.bn == 128) e = launch_gemm<128, A_MN, B_MN, Epi>(pl.maps, pl.sh, ep, pl.sms, stream);
-    else e = launch_gemm<64, A_MN, B_MN, Epi>(pl.maps, pl.sh, ep, pl.sms, stream);
-    if (e != cudaSuccess) return cuda_fail(e, "gemm launch");
-    return 0;
 }
 
 // ACC[g] = sum_seg A_seg[g] B_seg[g]^T over G groups, epilogue Epi.  Operand majors are compile-time.

@@ -140,9 +140,12 @@ struct EpiDecodeH {
 // rows).  The four c tiles a warp needs for a 256-column accumulator tile sit in four slots; as soon as a slot
 // has been read, the same chunk of the warp's NEXT tile is requested into it, so the loads fly during the rest
 // of this tile and the wait for the next accumulator - no register prefetch, no exposed load latency.
-struct EpiBackCodeH {
-    static constexpr int kIoBufs = 3;  // 12 KB per warp: 4 c slots (2 KB) + 2 dz staging tiles (2 KB)
-    static constexpr int kSlots = 4;
+template <int H>
+struct EpiBackCodeHT {
+    // H warps per row quarter (4 H epilogue warps): 8 / H chunks of 32 columns per warp and 256-wide tile.
+    static constexpr int kHalves = H;
+    static constexpr int kSlots = 8 / H;
+    static constexpr int kIoBufs = (kSlots + 2 + 1) / 2;  // per warp: kSlots c slots + 2 dz staging tiles of 2 KB
     static_assert(kSlots <= kIoBars, "one load barrier per c slot");
     struct alignas(64) Params {
         CUtensorMap c_map;    // fp16 io map of c  [G][B][N]
@@ -160,12 +163,12 @@ struct EpiBackCodeH {
     const EpiIo io;
     float db, s, l1_term, bn;
     uint32_t off[4];  // byte offset of this lane's element in rows j with ((j >> 1) & 3) == k (SWIZZLE_64B)
-    // chunk i of a tile covers accumulator columns (half + i * kEpiHalves) * 32 ...
+    // chunk i of a tile covers accumulator columns (half + i * halves) * 32 ...
     SC_DEVICE void request(int slot, int g, int row0, int bcol) const {
         io_expect(io, 2048, slot);
         tma_load_3d(&p.c_map, io.bar + slot, io.buf + slot * 2048, row0, bcol, g);
     }
-    SC_DEVICE EpiBackCodeH(const Params& p_, const RowCtx& c_, const EpiIo& io_) : p(p_), c(c_), io(io_), db(0.f), s(0.f) {
+    SC_DEVICE EpiBackCodeHT(const Params& p_, const RowCtx& c_, const EpiIo& io_) : p(p_), c(c_), io(io_), db(0.f), s(0.f) {
         const int lane = threadIdx.x & 31;
         l1_term = p.l1[c.g] * p.l1_scale;
         bn = (p.tied && c.row < c.M) ? p.bias[(long long)c.g * p.feats + c.row] : 0.f;
@@ -173,8 +176,8 @@ struct EpiBackCodeH {
         for (int k = 0; k < 4; ++k) off[k] = (((lane >> 3) ^ k) << 4) + ((lane & 7) << 1);
         if (c.first && lane == 0) {
             for (int i = 0; i < kSlots; ++i) {
-                const int bc = c.col0 + (c.half + i * kEpiHalves) * 32;
-                if (bc < c.N && (c.half + i * kEpiHalves) * 32 < c.bn) request(i, c.g, c.row, bc);
+                const int bc = c.col0 + (c.half + i * c.halves) * 32;
+                if (bc < c.N && (c.half + i * c.halves) * 32 < c.bn) request(i, c.g, c.row, bc);
             }
         }
     }
@@ -200,7 +203,7 @@ struct EpiBackCodeH {
     }
     SC_DEVICE void chunk(int co, float (&v)[32], int /*next_co*/) {
         const int lane = threadIdx.x & 31;
-        const int i = (co >> 5) / kEpiHalves;  // slot of this chunk
+        const int i = (co >> 5) / c.halves;  // slot of this chunk
         const int bcol = c.col0 + co;
         const bool live = bcol < c.N;          // else the whole chunk lies beyond the batch: nothing was requested
         uint8_t* dt = io.buf + kSlots * 2048 + (i & 1) * 2048;
@@ -224,10 +227,14 @@ struct EpiBackCodeH {
     }
     SC_DEVICE void finish() {
         if (c.row >= c.M) return;
-        const long long o = ((long long)c.g * c.tiles_n * kEpiHalves + c.tile_n * kEpiHalves + c.half) * p.feats + c.row;
+        const long long o = ((long long)c.g * c.tiles_n * c.halves + c.tile_n * c.halves + c.half) * p.feats + c.row;
         p.db_part[o] = db;
         p.s_part[o] = s;
     }
 };
+// Measured on the headline shape: H = 4 (16 epilogue warps, 640 threads, 96-register cap, 3 pipeline stages) is
+// 2.5 % slower per step than H = 2 - the epilogue and the mainloop are already balanced, more warps only add
+// per-tile overhead.
+using EpiBackCodeH = EpiBackCodeHT<2>;
 
 }  // namespace sc

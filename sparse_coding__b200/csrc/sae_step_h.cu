@@ -157,7 +157,7 @@ static StepWsH carve_step_h(void* base, int M, int B, int d, int N, int tied, in
     w.dz_h = halves(Mz * Bz * Nz);
     w.n_l1 = row_tiles128(B) * ceil_div(N, pick_bn(N)) * 4 * kEpiHalves;
     w.n_mse = row_tiles128(B) * ceil_div(d, pick_bn(d)) * 4 * kEpiHalves;
-    w.tiles_b = ceil_div(B, pick_bn(B)) * kEpiHalves;
+    w.tiles_b = ceil_div(B, pick_bn(B)) * EpiHalvesOf<EpiBackCodeH>::v;  // partial slots per feature
     w.l1_part = c.floats(Mz * w.n_l1);
     w.mse_part = c.floats(Mz * w.n_mse);
     w.db_part = c.floats(Mz * w.tiles_b * Nz);
@@ -166,6 +166,8 @@ static StepWsH carve_step_h(void* base, int M, int B, int d, int N, int tied, in
     w.bytes = c.off;
     return w;
 }
+
+size_t step_h_workspace_bytes(int M, int B, int d, int N, int tied, int xpm) { return carve_step_h(nullptr, M, B, d, N, tied, xpm).bytes; }
 
 static bool f16_supported(int B, int d, int N) {
     return use_cta_pairs() && d >= 128 && N >= 128 && (d % 64) == 0 && (N % 64) == 0 && B > 64;

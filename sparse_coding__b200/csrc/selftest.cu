@@ -48,6 +48,12 @@ struct EpiNull {
     }
     SC_DEVICE void finish() { if (acc == 123.456f) out[0] = acc; }
 };
+// same with shared memory taken away from the operand pipeline, as an epilogue with staging tiles does
+template <int IO>
+struct EpiNullIo : EpiNull {
+    static constexpr int kIoBufs = IO;
+    SC_DEVICE EpiNullIo(const Params& p, const RowCtx& c, const EpiIo& io) : EpiNull(p, c, io) {}
+};
 static int g_null = 0;
 static int g_cg = 1;
 static int g_eb = 4;
@@ -55,6 +61,9 @@ template <int BN, bool A_MN, bool B_MN>
 static cudaError_t run(const GemmMaps& maps, const GemmShape& sh, const EpiStore::Params& ep, int sms) {
     if (g_null) {
         EpiNull::Params en{ep.C, ep.ld, ep.gstride};
+        if (g_eb == 2 && g_null == 3) return launch_gemm_2cta<BN, A_MN, B_MN, EpiNullIo<3>, 2>(maps, sh, en, sms, 0);
+        if (g_eb == 2 && g_null == 4) return launch_gemm_2cta<BN, A_MN, B_MN, EpiNullIo<4>, 2>(maps, sh, en, sms, 0);
+        if (g_eb == 2 && g_null == 5) return launch_gemm_2cta<BN, A_MN, B_MN, EpiNullIo<5>, 2>(maps, sh, en, sms, 0);
         if (g_eb == 2) return launch_gemm_2cta<BN, A_MN, B_MN, EpiNull, 2>(maps, sh, en, sms, 0);
         if (g_cg == 2) return launch_gemm_2cta<BN, A_MN, B_MN, EpiNull>(maps, sh, en, sms, 0);
         return launch_gemm<BN, A_MN, B_MN, EpiNull>(maps, sh, en, sms, 0);
@@ -72,7 +81,7 @@ int main(int argc, char** argv) {
     const int M = atoi(argv[1]), N = atoi(argv[2]), K = atoi(argv[3]), G = atoi(argv[4]);
     const int a_mn = atoi(argv[5]), b_mn = atoi(argv[6]), BN = atoi(argv[7]), nseg = atoi(argv[8]);
     g_cg = argc > 9 ? atoi(argv[9]) : 1;
-    g_null = getenv("SC_SELFTEST_NULL_EPI") != nullptr;
+    g_null = getenv("SC_SELFTEST_NULL_EPI") ? atoi(getenv("SC_SELFTEST_NULL_EPI")) : 0;
     g_eb = argc > 10 ? atoi(argv[10]) : 4;
     if (g_eb == 2) g_cg = 2;
     g_eb = argc > 10 ? atoi(argv[10]) : 4;

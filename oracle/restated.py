@@ -209,7 +209,7 @@ class EnsembleOracle:
 def _is_identity_centering(buffers, m) -> bool:
     rot, tr, sc = buffers["center_rot"][m], buffers["center_trans"][m], buffers["center_scale"][m]
     d = rot.shape[0]
-    return bool(torch.equal(rot, torch.eye(d, dtype=rot.dtype)) and not tr.any() and torch.equal(sc, torch.ones_like(sc)))
+    return bool(torch.equal(rot, torch.eye(d, dtype=rot.dtype, device=rot.device)) and not tr.any() and torch.equal(sc, torch.ones_like(sc)))
 
 
 # --------------------------------------------------------------------------- #

@@ -305,3 +305,48 @@ def test_back_to_back_steps_equal_synchronised_steps(kind, fmt):
     assert torch.equal(got, want)
     for k in ens_a.params:
         assert torch.equal(ens_a.params[k], ens_s.params[k]), k
+
+
+@pytest.mark.parametrize("name,kind,shape", [
+    ("C2 pythia70m_l2_untied_sae", "untied", (8, 2048, 512, 4096)),
+    ("C3 gpt2 share, tied", "tied", (4, 2048, 768, 6144)),
+    ("C1 toy, tied", "tied", (4, 4096, 256, 512)),
+])
+def test_full_size_configs_against_fp32_restatement_on_gpu(name, kind, shape):
+    """BASELINE.json's configurations at FULL size.  The CPU oracle would need minutes per step here, so the same
+    restated formulas (oracle/restated.py, plain torch) are evaluated in fp32 on the GPU (TF32 off) and the fused
+    step must stay inside the gates over 25 steps: loss / FVU 1e-3 relative, mean L0 0.5 %."""
+    M, B, d, N = shape
+    old = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        ens, _ = _pair(kind, d, N, np.logspace(-4, -2, M), seed=13)
+        params = {k: v.detach().clone() for k, v in ens.params.items()}
+        buffers = {k: v.detach().clone() for k, v in ens.buffers.items()}
+        params0 = {k: v.clone() for k, v in params.items()}
+        orc = R.EnsembleOracle(params, buffers, tied=(kind == "tied"), lr=1e-3)
+        data = make_sparse_data(6 * B, d, 2 * d, 10, seed=15).cuda()
+        g = torch.Generator().manual_seed(17)
+        worst = {"loss": 0.0, "fvu": 0.0, "l0": 0.0}
+        for step in range(25):
+            x = data[torch.randint(0, data.shape[0], (B,), generator=g).cuda()]
+            l_gpu, a_gpu = ens.step_batch(x)
+            l_ref, a_ref = orc.step_batch(x)
+            for k, w in (("loss", "loss"), ("l_reconstruction", "fvu")):
+                dev = float(((l_gpu[k] - l_ref[k]).abs() / l_ref[k].abs()).max())
+                worst[w] = max(worst[w], dev)
+            if step % 8 == 0 or step == 24:
+                l0g = (a_gpu["c"] != 0).float().sum(-1).mean(-1)
+                l0r = (a_ref["c"] != 0).float().sum(-1).mean(-1)
+                worst["l0"] = max(worst["l0"], float(((l0g - l0r).abs() / l0r.clamp_min(1.0)).max()))
+        print(name, "worst relative deviations over 25 full-size steps:", worst)
+        assert worst["loss"] < 1e-3 and worst["fvu"] < 1e-3 and worst["l0"] < 5e-3
+        # parameters: Adam's first steps are sign-like (+-lr per step), so noise-level gradient entries may walk
+        # apart; the mean distance must stay a small fraction of the distance travelled (25 steps x lr)
+        for k in orc.params:
+            apart = float((ens.params[k] - orc.params[k]).abs().mean())
+            moved = float((orc.params[k] - params0[k]).abs().mean())
+            print("   ", k, "mean |gpu - ref|", apart, "mean |ref - init|", moved)
+            assert apart < 0.05 * moved + 1e-7, k
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = old

@@ -104,6 +104,8 @@ typedef struct {
     void* workspace;
     size_t workspace_bytes;
     void* stream;
+    int32_t operand_format; /* 0: TF32 operands; 1: fp16 operands (same 11-bit significand, twice the MMA rate);
+                               needs sc_infer_f16_supported(B, d, N, transposed = statistics requested) */
 } ScEncodeArgs;
 size_t sc_encode_workspace_bytes(int32_t G, int32_t B, int32_t d, int32_t N, int32_t x_per_group);
 int sc_encode(const ScEncodeArgs* args);
@@ -123,8 +125,12 @@ typedef struct {
     void* workspace;
     size_t workspace_bytes;
     void* stream;
+    int32_t operand_format; /* as in ScEncodeArgs; the codes are converted to fp16 (|c| <= 65504) */
 } ScDecodeArgs;
 size_t sc_decode_workspace_bytes(int32_t G, int32_t B, int32_t d, int32_t N);
+/* 1 when sc_encode / sc_decode can run with fp16 operands for this shape (d, N multiples of 64 and >= 128;
+ * the transposed statistics variant of sc_encode also needs B > 64). */
+int sc_infer_f16_supported(int32_t B, int32_t d, int32_t N, int32_t transposed);
 int sc_decode(const ScDecodeArgs* args);
 
 /* FunctionalFista.fista (fista.py:99-128; method twin :274-301): num_iter FISTA iterations of

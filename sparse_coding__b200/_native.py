@@ -24,7 +24,7 @@ EXPORTS = [
     "sc_encode_workspace_bytes", "sc_encode", "sc_decode_workspace_bytes", "sc_decode",
     "sc_fista_workspace_bytes", "sc_fista", "sc_gemm_tf32", "sc_adam_apply", "sc_row_normalise", "sc_column_variance",
     "sc_profile_begin", "sc_profile_end", "sc_encode_noalloc", "sc_sae_step_f16_supported",
-    "sc_gather_rows", "sc_column_mean_workspace_bytes", "sc_column_mean",
+    "sc_gather_rows", "sc_column_mean_workspace_bytes", "sc_column_mean", "sc_infer_f16_supported",
 ]
 
 
@@ -59,6 +59,7 @@ class ScEncodeArgs(C.Structure):
         ("x", C.c_void_p), ("W", C.c_void_p), ("bias", C.c_void_p),
         ("out_c", C.c_void_p), ("out_nonzero", C.c_void_p), ("out_moments", C.c_void_p),
         ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t), ("stream", C.c_void_p),
+        ("operand_format", C.c_int32),
     ]
 
 
@@ -69,6 +70,7 @@ class ScDecodeArgs(C.Structure):
         ("c", C.c_void_p), ("Wd", C.c_void_p), ("target", C.c_void_p),
         ("out_x_hat", C.c_void_p), ("out_sq_err", C.c_void_p),
         ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t), ("stream", C.c_void_p),
+        ("operand_format", C.c_int32),
     ]
 
 
@@ -136,6 +138,8 @@ def lib() -> C.CDLL:
         L.sc_adam_apply.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(ScAdam), C.c_void_p]
         L.sc_adam_apply.restype = C.c_int
         L.sc_gather_rows.argtypes = [C.POINTER(ScGatherArgs)]
+        L.sc_infer_f16_supported.argtypes = [C.c_int32] * 4
+        L.sc_infer_f16_supported.restype = C.c_int
         L.sc_column_mean_workspace_bytes.restype = C.c_size_t
         L.sc_column_mean_workspace_bytes.argtypes = [C.c_int32]
         L.sc_column_mean.argtypes = [C.c_void_p, C.c_int32, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]

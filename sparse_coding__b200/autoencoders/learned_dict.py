@@ -26,6 +26,13 @@ def _prep(t: torch.Tensor, name: str) -> torch.Tensor:
     return t
 
 
+def _operand_format():
+    """GEMM operand format of the inference kernels: fp16 (same 11-bit significand as the TF32 mode, twice the
+    tensor-core rate) whenever the shape allows it, unless SC_B200_OPERANDS=tf32."""
+    import os
+    return os.environ.get("SC_B200_OPERANDS", "auto")
+
+
 def _encode_native(batch, encoder, bias, want_counts=False, want_moments=False, want_c=True):
     """c = relu(batch @ encoder^T + bias) (learned_dict.py:127-131).  encoder may be [N,d] or a
     stack [G,N,d]; optional per-feature statistics come from the same GEMM's epilogue."""
@@ -46,9 +53,11 @@ def _encode_native(batch, encoder, bias, want_counts=False, want_moments=False, 
     mom = torch.zeros((G, 4, N), dtype=torch.float32, device=dev) if want_moments else None
     need = L.sc_encode_workspace_bytes(G, B, d, N, int(per_group))
     ws_ptr, ws_bytes = _ws.aligned(need, dev)
+    f16 = _operand_format() != "tf32" and bool(L.sc_infer_f16_supported(B, d, N, int(nz is not None)))
     args = nat.ScEncodeArgs(G=G, B=B, d=d, N=N, x_per_group=int(per_group), x=nat.ptr(x), W=nat.ptr(W), bias=nat.ptr(b),
                             out_c=nat.ptr(c), out_nonzero=nat.ptr(nz), out_moments=nat.ptr(mom),
-                            workspace=ws_ptr, workspace_bytes=ws_bytes, stream=nat.stream_ptr(dev))
+                            workspace=ws_ptr, workspace_bytes=ws_bytes, stream=nat.stream_ptr(dev),
+                            operand_format=int(f16))
     with torch.cuda.device(dev):
         nat.check(L.sc_encode(C.byref(args)), "sc_encode")
     stats = {}
@@ -80,11 +89,12 @@ def _decode_native(code, decoder, normalise=True, target=None, want_x_hat=True):
     sq = torch.empty((G,), dtype=torch.float32, device=dev) if tgt is not None else None
     need = L.sc_decode_workspace_bytes(G, B, d, N)
     ws_ptr, ws_bytes = _ws.aligned(need, dev)
+    f16 = _operand_format() != "tf32" and bool(L.sc_infer_f16_supported(B, d, N, 0))
     args = nat.ScDecodeArgs(G=G, B=B, d=d, N=N, normalise=int(normalise),
                             target_per_group=int(tgt is not None and tgt.dim() == 3),
                             c=nat.ptr(c), Wd=nat.ptr(W), target=nat.ptr(tgt), out_x_hat=nat.ptr(x_hat),
                             out_sq_err=nat.ptr(sq), workspace=ws_ptr, workspace_bytes=ws_bytes,
-                            stream=nat.stream_ptr(dev))
+                            stream=nat.stream_ptr(dev), operand_format=int(f16))
     with torch.cuda.device(dev):
         nat.check(L.sc_decode(C.byref(args)), "sc_decode")
     if not stacked:

@@ -147,6 +147,24 @@ __global__ void sum_parts_kernel(const float* __restrict__ part, int n, float* _
     }
 }
 
+// fp16 operand copies for the inference entry points (kernels of sae_step_h.cu)
+__global__ void to_half_kernel(const float4* __restrict__ in, uint2* __restrict__ out, long long n4);
+__global__ void prep_params_h_kernel(const float* __restrict__ enc, __half* __restrict__ enc_h,
+                                     const float* __restrict__ W, __half* __restrict__ D_h,
+                                     float* __restrict__ inv_norm, int N, int d);
+
+static int to_half(const float* in, __half* out, long long n, cudaStream_t st) {
+    const long long n4 = n / 4;
+    const int grid = static_cast<int>(n4 / 256 + 1 < 4096 ? n4 / 256 + 1 : 4096);
+    launch_k(to_half_kernel, dim3(grid), dim3(256), 0, st, reinterpret_cast<const float4*>(in), reinterpret_cast<uint2*>(out), n4);
+    SC_CUDA(cudaGetLastError(), "to_half launch");
+    return 0;
+}
+
+static bool infer_f16_supported(int B, int d, int N, int transposed) {
+    return use_cta_pairs() && d >= 128 && N >= 128 && (d % 64) == 0 && (N % 64) == 0 && (!transposed || B > 64);
+}
+
 static int encode_impl(const ScEncodeArgs& a) {
     const int G = a.G, B = a.B, d = a.d, N = a.N;
     if (G <= 0 || B <= 0 || d <= 0 || N <= 0) return fail(-1, "G, B, d, N must be positive");
@@ -159,11 +177,33 @@ static int encode_impl(const ScEncodeArgs& a) {
     Carver cv(a.workspace);
     const int xg = a.x_per_group ? G : 1;
     const long long Bd = (long long)B * d, Nd = (long long)N * d, BN_ = (long long)B * N;
+    const bool stats = a.out_nonzero || a.out_moments;
+    if (a.operand_format == 1) {
+        if (!infer_f16_supported(B, d, N, stats))
+            return fail(-1, "fp16 operand mode needs d, N multiples of 64 and >= 128%s (got B=%d d=%d N=%d)",
+                        stats ? " and B > 64" : "", B, d, N);
+        __half* x_h = reinterpret_cast<__half*>(cv.floats(((size_t)xg * Bd + 1) / 2));
+        __half* W_h = reinterpret_cast<__half*>(cv.floats(((size_t)G * Nd + 1) / 2));
+        SC_TRY(to_half(a.x, x_h, xg * Bd, st));
+        SC_TRY(to_half(a.W, W_h, G * Nd, st));
+        if (stats) {
+            Seg s{kmajor_h(W_h, N, d, G, Nd), kmajor_h(x_h, B, d, xg, Bd)};
+            EpiEncodeT::Params ep{a.bias, a.out_c, a.out_nonzero, a.out_moments, BN_, N};
+            return run_gemm<false, false, EpiEncodeT, true>(N, B, G, &s, 1, ep, st);
+        }
+        Seg s{kmajor_h(x_h, B, d, xg, Bd), kmajor_h(W_h, N, d, G, Nd)};
+        EpiEncode::Params ep{};
+        const char* err = nullptr;
+        const int rc = make_io_map(&ep.c_map, a.out_c, B, N, G, BN_, &err);
+        if (rc != 0) return fail(rc, "%s", err ? err : "io tensor map creation failed");
+        ep.bias = a.bias; ep.l1_part = nullptr; ep.signed_zero = 0; ep.dict_size = nullptr;
+        return run_gemm<false, false, EpiEncode, true>(B, N, G, &s, 1, ep, st);
+    }
     float* x_r = cv.floats((size_t)xg * Bd);
     float* W_r = cv.floats((size_t)G * Nd);
     SC_TRY(round_copy(a.x, x_r, xg * Bd, st));
     SC_TRY(round_copy(a.W, W_r, G * Nd, st));
-    if (a.out_nonzero || a.out_moments) {
+    if (stats) {
         Seg s{kmajor(W_r, N, d, G, Nd), kmajor(x_r, B, d, xg, Bd)};
         EpiEncodeT::Params ep{a.bias, a.out_c, a.out_nonzero, a.out_moments, BN_, N};
         SC_TRY((run_gemm<false, false, EpiEncodeT>(N, B, G, &s, 1, ep, st)));
@@ -192,9 +232,31 @@ static int decode_impl(const ScDecodeArgs& a) {
     cudaStream_t st = static_cast<cudaStream_t>(a.stream);
     Carver cv(a.workspace);
     const long long Bd = (long long)B * d, Nd = (long long)N * d, BN_ = (long long)B * N;
+    const int n_part = row_tiles128(B) * ceil_div(d, pick_bn(d)) * 4 * kEpiHalves;
+    if (a.operand_format == 1) {
+        if (!infer_f16_supported(B, d, N, 0))
+            return fail(-1, "fp16 operand mode needs d, N multiples of 64 and >= 128 (got d=%d N=%d)", d, N);
+        __half* c_h = reinterpret_cast<__half*>(cv.floats(((size_t)G * BN_ + 1) / 2));
+        __half* D_h = reinterpret_cast<__half*>(cv.floats(((size_t)G * Nd + 1) / 2));
+        float* part = cv.floats((size_t)G * n_part);
+        SC_TRY(to_half(a.c, c_h, G * BN_, st));
+        if (a.normalise) {
+            launch_k(prep_params_h_kernel, dim3(ceil_div(N, 8), G), dim3(256), 0, st, nullptr, nullptr, a.Wd, D_h, nullptr, N, d);
+            SC_CUDA(cudaGetLastError(), "prep launch");
+        } else {
+            SC_TRY(to_half(a.Wd, D_h, G * Nd, st));
+        }
+        Seg s{kmajor_h(c_h, B, N, G, BN_), mnmajor_h(D_h, d, N, G, Nd)};
+        EpiDecode::Params ep{a.target, nullptr, a.out_x_hat, a.out_sq_err ? part : nullptr, a.target_per_group ? Bd : 0, Bd, 1.f};
+        SC_TRY((run_gemm<false, true, EpiDecode, true>(B, d, G, &s, 1, ep, st)));
+        if (a.out_sq_err) {
+            launch_k(sum_parts_kernel, dim3(G), dim3(256), 0, st, part, n_part, a.out_sq_err);
+            SC_CUDA(cudaGetLastError(), "sum_parts launch");
+        }
+        return 0;
+    }
     float* c_r = cv.floats((size_t)G * BN_);
     float* D_r = cv.floats((size_t)G * Nd);
-    const int n_part = row_tiles128(B) * ceil_div(d, pick_bn(d)) * 4 * kEpiHalves;
     float* part = cv.floats((size_t)G * n_part);
     SC_TRY(round_copy(a.c, c_r, G * BN_, st));
     dim3 grid(ceil_div(N, 8), G);
@@ -232,6 +294,10 @@ size_t sc_decode_workspace_bytes(int32_t G, int32_t B, int32_t d, int32_t N) {
     cv.floats((size_t)G * N * d);
     cv.floats((size_t)G * sc::row_tiles128(B) * sc::ceil_div(d, sc::pick_bn(d)) * 4 * sc::kEpiHalves);
     return cv.off;
+}
+
+int sc_infer_f16_supported(int32_t B, int32_t d, int32_t N, int32_t transposed) {
+    return sc::infer_f16_supported(B, d, N, transposed) ? 1 : 0;
 }
 
 int sc_decode(const ScDecodeArgs* args) {

@@ -59,7 +59,7 @@ __global__ void prep_params_h_kernel(const float* __restrict__ enc, __half* __re
     ss = warp_sum(ss);
     const float nrm = sqrtf(ss);
     const float inv = 1.f / fmaxf(nrm, 1e-8f);
-    if (lane == 0) inv_norm[(long long)blockIdx.y * N + n] = nrm < 1e-8f ? -inv : inv;
+    if (lane == 0 && inv_norm) inv_norm[(long long)blockIdx.y * N + n] = nrm < 1e-8f ? -inv : inv;
     uint2* dst = reinterpret_cast<uint2*>(D_h + row);
     for (int i = lane; i < d4; i += 32) {
         const float4 v = src[i];

@@ -40,8 +40,10 @@ def _run_noalloc(x, W, b):
     return out
 
 
-def test_noalloc_encode_matches_regular_encode_twice():
+def test_noalloc_encode_matches_regular_encode_twice(monkeypatch):
     from sparse_coding__b200.autoencoders.learned_dict import _encode_native
+    # sc_encode_noalloc runs the TF32-operand kernels; compare with sc_encode in the same operand format
+    monkeypatch.setenv("SC_B200_OPERANDS", "tf32")
     torch.manual_seed(0)
     # two calls in a row, second one smaller: stale bytes of the first call stay behind it in the array
     for (B, d, N) in [(700, 256, 1024), (130, 64, 200)]:

@@ -77,6 +77,21 @@ typedef struct {
      * uses its first dict_size[m] features; the rest produce zero codes and zero gradients.  [M] int32 on the
      * device, or NULL for unmasked. */
     const int32_t* dict_size;
+    /* Fused reduce-scatter for data-parallel training of ONE dictionary (M == 1; replaces the NCCL all-reduce of
+     * the gradient-only mode; reference analogue: DDP in experiments/huge_batch_size.py:259-335).  rs_world > 0:
+     * rank r owns dictionary rows [r * rs_rows, (r + 1) * rs_rows), rs_rows = N / rs_world a multiple of 32.  The
+     * weight-gradient kernel adds every 32 x 32 tile of this rank's gradient straight into the OWNER's
+     * accumulation buffer over NVLink (TMA reduce-add to peer memory): rs_grad_enc[r] / rs_grad_dec[r] point at rank
+     * r's [rs_rows, d] buffers, rs_grad_bias[r] at its [rs_rows] buffer, rs_losses[r] at its [3] buffer (sum over
+     * ranks of l_reconstruction, l_l1, l_bias_decay; every rank adds to every rank's).  All must be zero before
+     * the step, peer-mapped in this process, and every rank must pass the same lists.  No Adam update happens here:
+     * after a cross-rank barrier the owner calls sc_dp_adam_broadcast on its slice.  grad_* are ignored. */
+    int32_t rs_world;
+    int32_t rs_rows;
+    float* rs_grad_enc[8];
+    float* rs_grad_dec[8];
+    float* rs_grad_bias[8];
+    float* rs_losses[8];
 } ScStepArgs;
 
 size_t sc_sae_step_workspace_bytes(int32_t M, int32_t B, int32_t d, int32_t N, int32_t tied, int32_t x_per_member);
@@ -192,6 +207,13 @@ int sc_gather_rows(const ScGatherArgs* args);
 size_t sc_column_mean_workspace_bytes(int32_t d);
 int sc_column_mean(const void* chunk, int32_t elem_bytes, int64_t n_rows, int32_t d, float* out_mean, void* workspace,
                    void* stream);
+
+/* Owner-side half of the fused data-parallel step: Adam on n contiguous elements whose summed gradient sits in
+ * `grad` (zeroed afterwards for the next step), moments updated in place, and the NEW parameter values stored to
+ * `n_peers` destinations - this rank's own copy and every peer's copy of the same slice (peer-mapped pointers), so
+ * no all-gather follows.  n must be a multiple of 4, pointers 16-byte aligned. */
+int sc_dp_adam_broadcast(float* grad, float* mu, float* nu, const float* p_local, float* const* p_dst, int32_t n_peers,
+                         int64_t n, const ScAdam* adam, void* stream);
 
 /* Encode for callers that cannot allocate device memory.  (No counterpart in the reference: it is
  * an addition of this library.)  Same result as sc_encode with G = 1 and only out_c requested -

@@ -24,7 +24,7 @@ EXPORTS = [
     "sc_encode_workspace_bytes", "sc_encode", "sc_decode_workspace_bytes", "sc_decode",
     "sc_fista_workspace_bytes", "sc_fista", "sc_gemm_tf32", "sc_adam_apply", "sc_row_normalise", "sc_column_variance",
     "sc_profile_begin", "sc_profile_end", "sc_encode_noalloc", "sc_sae_step_f16_supported",
-    "sc_gather_rows", "sc_column_mean_workspace_bytes", "sc_column_mean", "sc_infer_f16_supported",
+    "sc_gather_rows", "sc_column_mean_workspace_bytes", "sc_column_mean", "sc_infer_f16_supported", "sc_dp_adam_broadcast",
 ]
 
 
@@ -49,6 +49,9 @@ class ScStepArgs(C.Structure):
         ("grad_enc", C.c_void_p), ("grad_bias", C.c_void_p), ("grad_dec", C.c_void_p),
         ("B_total", C.c_int32),
         ("operand_format", C.c_int32), ("out_c_half", C.c_void_p), ("dict_size", C.c_void_p),
+        ("rs_world", C.c_int32), ("rs_rows", C.c_int32),
+        ("rs_grad_enc", C.c_void_p * 8), ("rs_grad_dec", C.c_void_p * 8),
+        ("rs_grad_bias", C.c_void_p * 8), ("rs_losses", C.c_void_p * 8),
     ]
 
 
@@ -138,6 +141,8 @@ def lib() -> C.CDLL:
         L.sc_adam_apply.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(ScAdam), C.c_void_p]
         L.sc_adam_apply.restype = C.c_int
         L.sc_gather_rows.argtypes = [C.POINTER(ScGatherArgs)]
+        L.sc_dp_adam_broadcast.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p), C.c_int32,
+                                           C.c_int64, C.POINTER(ScAdam), C.c_void_p]
         L.sc_infer_f16_supported.argtypes = [C.c_int32] * 4
         L.sc_infer_f16_supported.restype = C.c_int
         L.sc_column_mean_workspace_bytes.restype = C.c_size_t

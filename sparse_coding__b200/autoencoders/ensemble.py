@@ -295,7 +295,16 @@ class FunctionalEnsemble:
                 nat.check(L.sc_adam_apply(nat.ptr(p), nat.ptr(mu), nat.ptr(nu), nat.ptr(g), p.numel(), C.byref(adam),
                                           nat.stream_ptr(p.device)), "sc_adam_apply")
 
-    def _run(self, minibatches, expand_dims, grad_only, batch_total=0, bias_decay=None):
+    def scatter_grads(self, minibatches, reduce_scatter, expand_dims=True, batch_total=0, bias_decay=None):
+        """Fused reduce-scatter twin of compute_grads for ONE dictionary trained data-parallel (dist.FusedDataParallel):
+        the gradients are not returned but ADDED, tile by tile, into their owner rank's accumulation buffers
+        (`reduce_scatter`: {"world", "rows", "grad_enc", "grad_dec", "grad_bias", "losses"} with one device address
+        per rank each - ScStepArgs.rs_*).  Returns (loss_dict of this rank's share, aux)."""
+        _, losses, aux = self._run(minibatches, expand_dims, grad_only=True, batch_total=batch_total, bias_decay=bias_decay,
+                                   reduce_scatter=reduce_scatter)
+        return losses, aux
+
+    def _run(self, minibatches, expand_dims, grad_only, batch_total=0, bias_decay=None, reduce_scatter=None):
         L = nat.lib()
         M = self.n_models
         x = minibatches
@@ -339,7 +348,7 @@ class FunctionalEnsemble:
 
         adam = self.adam_constants(advance=not grad_only)
         grads = None
-        if grad_only:
+        if grad_only and reduce_scatter is None:
             grads = {"encoder": torch.empty_like(enc), "encoder_bias": torch.empty_like(bias)}
             if not tied:
                 grads["decoder"] = torch.empty_like(dec)
@@ -364,12 +373,21 @@ class FunctionalEnsemble:
             l1_alpha=nat.ptr(l1), bias_decay=nat.ptr(bd), adam=adam,
             out_losses=nat.ptr(losses), out_c=nat.ptr(c),
             workspace=ws_ptr, workspace_bytes=ws_bytes, stream=nat.stream_ptr(x.device),
-            grad_enc=nat.ptr(grads["encoder"]) if grad_only else None,
-            grad_bias=nat.ptr(grads["encoder_bias"]) if grad_only else None,
-            grad_dec=nat.ptr(grads.get("decoder")) if grad_only else None,
+            grad_enc=nat.ptr(grads["encoder"]) if grads else None,
+            grad_bias=nat.ptr(grads["encoder_bias"]) if grads else None,
+            grad_dec=nat.ptr(grads.get("decoder")) if grads else None,
             B_total=int(batch_total),
             operand_format=int(f16), out_c_half=nat.ptr(c_half), dict_size=nat.ptr(dict_size),
         )
+        if reduce_scatter is not None:
+            rs = reduce_scatter
+            args.rs_world, args.rs_rows = int(rs["world"]), int(rs["rows"])
+            for r in range(args.rs_world):
+                args.rs_grad_enc[r] = rs["grad_enc"][r]
+                args.rs_grad_bias[r] = rs["grad_bias"][r]
+                args.rs_losses[r] = rs["losses"][r]
+                if not tied:
+                    args.rs_grad_dec[r] = rs["grad_dec"][r]
         with torch.cuda.device(x.device):
             nat.check(L.sc_sae_step(C.byref(args)), "sc_sae_step")
         loss_dict = {"loss": losses[0], "l_reconstruction": losses[1], "l_l1": losses[2]}

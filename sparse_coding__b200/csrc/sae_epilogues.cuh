@@ -264,6 +264,10 @@ struct EpiAdam {
         int tiles_b;  // partial slots per feature in s_part
         float g_scale;  // applied to the accumulator and to s (fp16 mode keeps them scaled by B d / 2; else 1)
         AdamConst a;
+        // fused reduce-scatter (ScStepArgs.rs_world > 0): gradient tiles are ADDED into their owner's buffer
+        int rs_world;                  // 0: off
+        int rs_rows;                   // dictionary rows per owner (multiple of 32)
+        CUtensorMap rs_map[2][8];      // [problem][owner]: io map of the owner's [1][rs_rows][d] accumulation buffer
     };
     const Params& p;
     const Sub& u;
@@ -315,7 +319,16 @@ struct EpiAdam {
         }
         if (u.grad_only) {
             io_write_row(b, lane, v);
-            io_store_tile(&u.grad_map, b, col, row0, c.g);
+            if (p.rs_world > 0) {
+                // the warp's 32 rows belong to one owner (rs_rows is a multiple of 32); rows past M are clipped by
+                // the map of the last owner
+                const int owner = min(row0 / p.rs_rows, p.rs_world - 1);
+                fence_proxy_async_smem();
+                __syncwarp();
+                if (lane == 0) tma_reduce_add_3d(&p.rs_map[c.prob][owner], b, col, row0 - owner * p.rs_rows, 0);
+            } else {
+                io_store_tile(&u.grad_map, b, col, row0, c.g);
+            }
         } else {
             float mv[32], nv[32];
             io_read_row(b + kIoTileBytes, lane, mv);

@@ -105,12 +105,43 @@ __global__ void adam_apply_kernel(float4* __restrict__ p, float4* __restrict__ m
     }
 }
 
+// destinations of the fused reduce-scatter mode (ScStepArgs.rs_*): per owner, its bias-gradient and loss buffers
+struct RsFinal {
+    int world, rows;
+    float* bias[8];
+    float* losses[8];
+};
+
+// Owner's Adam on its slice, new parameters stored to every rank's copy (peer-mapped), gradient buffer re-zeroed
+struct PeerDst {
+    float4* p[8];
+    int n;
+};
+__global__ void dp_adam_broadcast_kernel(float4* __restrict__ g, float4* __restrict__ mu, float4* __restrict__ nu,
+                                         const float4* __restrict__ p_local, PeerDst dst, long long n4, AdamConst a) {
+    pdl_launch_dependents();
+    pdl_wait();
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+        float4 pv = p_local[i], mv = mu[i], nv = nu[i];
+        const float4 gv = g[i];
+        adam_update(pv.x, mv.x, nv.x, gv.x, a);
+        adam_update(pv.y, mv.y, nv.y, gv.y, a);
+        adam_update(pv.z, mv.z, nv.z, gv.z, a);
+        adam_update(pv.w, mv.w, nv.w, gv.w, a);
+        mu[i] = mv; nu[i] = nv;
+        g[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int r = 0; r < 8; ++r)
+            if (r < dst.n) dst.p[r][i] = pv;
+    }
+}
+
 __global__ void finalize_kernel(const float* __restrict__ l1_part, int n_l1, const float* __restrict__ mse_part, int n_mse,
                                 const float* __restrict__ db_part, int tiles_b, float* __restrict__ bias,
                                 float* __restrict__ bias_mu, float* __restrict__ bias_nu,
                                 const float* __restrict__ l1_alpha, const float* __restrict__ bias_decay,
                                 float* __restrict__ out_losses, int M, int B, int d, int N, int tied, AdamConst a,
-                                float* __restrict__ grad_bias, float* __restrict__ bnorm_ws, float db_scale) {
+                                float* __restrict__ grad_bias, float* __restrict__ bnorm_ws, float db_scale, RsFinal rs) {
     pdl_launch_dependents();
     pdl_wait();
     // grid (ceil(N/256), M).  Every block needs ||b|| of the PRE-update bias: block x == 0 of each member
@@ -135,6 +166,12 @@ __global__ void finalize_kernel(const float* __restrict__ l1_part, int n_l1, con
             out_losses[1 * M + m] = l_rec;
             out_losses[2 * M + m] = l_l1;
             out_losses[3 * M + m] = l_bd;
+            // fused data-parallel mode (M == 1): every rank adds its share of the loss terms to every rank's buffer
+            for (int r = 0; r < rs.world; ++r) {
+                atomicAdd(rs.losses[r] + 0, l_rec);
+                atomicAdd(rs.losses[r] + 1, l_l1);
+                atomicAdd(rs.losses[r] + 2, l_bd);
+            }
         }
     }
     const float bscale = bnorm > 0.f ? beta / bnorm : 0.f;
@@ -146,7 +183,10 @@ __global__ void finalize_kernel(const float* __restrict__ l1_part, int n_l1, con
         const long long o = (long long)m * N + n;
         float p = bias[o];
         g += bscale * p;
-        if (grad_bias) {
+        if (rs.world > 0) {
+            const int owner = n / rs.rows;  // M == 1: o == n
+            atomicAdd(rs.bias[owner] + (n - owner * rs.rows), g);
+        } else if (grad_bias) {
             grad_bias[o] = g;
         } else {
             float mu = bias_mu[o], nu = bias_nu[o];
@@ -229,6 +269,39 @@ static int check_ptr(const void* p, const char* name) {
     return 0;
 }
 
+int check_rs(const ScStepArgs& a) {
+    if (a.rs_world == 0) return 0;
+    if (a.rs_world < 0 || a.rs_world > 8) return fail(-1, "rs_world must be in [0, 8] (got %d)", a.rs_world);
+    if (a.M != 1) return fail(-1, "the fused reduce-scatter mode trains ONE dictionary (M == 1, got %d)", a.M);
+    if (a.rs_rows <= 0 || (a.rs_rows & 31) || (long long)a.rs_rows * a.rs_world != a.N)
+        return fail(-1, "rs_rows must be N / rs_world and a multiple of 32 (N=%d rs_world=%d rs_rows=%d)", a.N, a.rs_world, a.rs_rows);
+    for (int r = 0; r < a.rs_world; ++r) {
+        SC_TRY(check_ptr(a.rs_grad_enc[r], "rs_grad_enc[r]"));
+        SC_TRY(check_ptr(a.rs_grad_bias[r], "rs_grad_bias[r]"));
+        SC_TRY(check_ptr(a.rs_losses[r], "rs_losses[r]"));
+        if (!a.tied) SC_TRY(check_ptr(a.rs_grad_dec[r], "rs_grad_dec[r]"));
+    }
+    return 0;
+}
+
+// reduce-scatter destinations of the weight-gradient kernel and of finalize
+int fill_rs(EpiAdam::Params& e, const ScStepArgs& a) {
+    e.rs_world = a.rs_world;
+    e.rs_rows = a.rs_rows;
+    for (int r = 0; r < a.rs_world; ++r) {
+        SC_TRY(io_map(&e.rs_map[0][r], a.rs_grad_enc[r], a.rs_rows, a.d, 1, 0));
+        if (!a.tied) SC_TRY(io_map(&e.rs_map[1][r], a.rs_grad_dec[r], a.rs_rows, a.d, 1, 0));
+    }
+    return 0;
+}
+RsFinal make_rs_final(const ScStepArgs& a) {
+    RsFinal f{};
+    f.world = a.rs_world;
+    f.rows = a.rs_rows;
+    for (int r = 0; r < a.rs_world; ++r) { f.bias[r] = a.rs_grad_bias[r]; f.losses[r] = a.rs_losses[r]; }
+    return f;
+}
+
 int sae_step_f16_impl(const ScStepArgs& a);
 
 static int sae_step_impl(const ScStepArgs& a) {
@@ -243,6 +316,7 @@ static int sae_step_impl(const ScStepArgs& a) {
     SC_TRY(check_ptr(a.workspace, "workspace"));
     if (!a.l1_alpha || !a.bias_decay || !a.out_losses) return fail(-1, "l1_alpha / bias_decay / out_losses is NULL");
     if (reinterpret_cast<uintptr_t>(a.workspace) & 1023) return fail(-1, "workspace must be 1024-byte aligned");
+    SC_TRY(check_rs(a));
     if (a.operand_format == 1) return sae_step_f16_impl(a);
     if (a.operand_format != 0) return fail(-1, "unknown operand_format %d", a.operand_format);
     const StepWs w = carve_step(a.workspace, M, B, d, N, a.tied, a.x_per_member);
@@ -252,8 +326,8 @@ static int sae_step_impl(const ScStepArgs& a) {
     const AdamConst ad = make_adam(a.adam);
     const int xg = a.x_per_member ? M : 1;
     const int Bn = a.B_total > 0 ? a.B_total : B;  // normalising batch size
-    const bool grad_mode = a.grad_enc != nullptr;
-    if (grad_mode) {
+    const bool grad_mode = a.grad_enc != nullptr || a.rs_world > 0;
+    if (grad_mode && a.rs_world == 0) {
         SC_TRY(check_ptr(a.grad_enc, "grad_enc")); SC_TRY(check_ptr(a.grad_bias, "grad_bias"));
         if (!a.tied) SC_TRY(check_ptr(a.grad_dec, "grad_dec"));
     }
@@ -311,9 +385,10 @@ static int sae_step_impl(const ScStepArgs& a) {
             u.s_part = projected ? w.s_part : nullptr;
             u.inv_norm = projected ? w.inv_norm : nullptr;
             u.projected = projected ? 1 : 0;
-            u.grad_only = grad ? 1 : 0;
+            u.grad_only = (grad || a.rs_world > 0) ? 1 : 0;
             return 0;
         };
+        SC_TRY(fill_rs(e, a));
         if (!a.tied) {
             // one launch, two independent problems: dW_e = dz^T x (plain) and dW_d = c^T R (projected)
             Seg s45[2] = {{mnmajor(w.dz, N, B, M, BN_), mnmajor(w.x_r, d, B, xg, Bd)},
@@ -335,7 +410,7 @@ static int sae_step_impl(const ScStepArgs& a) {
     launch_k(finalize_kernel, dim3(dim3(ceil_div(N, 256), M)), dim3(256), 0, st, w.l1_part, w.n_l1, w.mse_part, w.n_mse, w.db_part, w.tiles_b,
                                                              a.bias, a.bias_mu, a.bias_nu, a.l1_alpha, a.bias_decay,
                                                              a.out_losses, M, Bn, d, N, a.tied, ad,
-                                                             grad_mode ? a.grad_bias : nullptr, w.bnorm, 1.0f);
+                                                             grad_mode ? a.grad_bias : nullptr, w.bnorm, 1.0f, make_rs_final(a));
     SC_CUDA(cudaGetLastError(), "finalize launch");
     prof_mark(st, "finalize");
     return 0;
@@ -377,6 +452,26 @@ int sc_profile_end(const char** names, float* ms, int cap) {
     for (int i = 0; i < g_prof.n; ++i) cudaEventDestroy(g_prof.ev[i]);
     g_prof.n = 0;
     return out;
+}
+
+int sc_dp_adam_broadcast(float* grad, float* mu, float* nu, const float* p_local, float* const* p_dst, int32_t n_peers,
+                         int64_t n, const ScAdam* adam, void* stream) {
+    using namespace sc;
+    if (!grad || !mu || !nu || !p_local || !p_dst || !adam || n <= 0 || (n & 3) || n_peers < 1 || n_peers > 8)
+        return fail(-1, "bad sc_dp_adam_broadcast argument");
+    PeerDst dst{};
+    dst.n = n_peers;
+    for (int r = 0; r < n_peers; ++r) {
+        if (!p_dst[r] || (reinterpret_cast<uintptr_t>(p_dst[r]) & 15)) return fail(-1, "p_dst[%d] is NULL or not 16-byte aligned", r);
+        dst.p[r] = reinterpret_cast<float4*>(p_dst[r]);
+    }
+    const long long n4 = n / 4;
+    const int grid = static_cast<int>(n4 / 256 + 1 < 148 * 16 ? n4 / 256 + 1 : 148 * 16);
+    launch_k(dp_adam_broadcast_kernel, dim3(grid), dim3(256), 0, static_cast<cudaStream_t>(stream), reinterpret_cast<float4*>(grad),
+             reinterpret_cast<float4*>(mu), reinterpret_cast<float4*>(nu), reinterpret_cast<const float4*>(p_local), dst, n4,
+             make_adam(*adam));
+    SC_CUDA(cudaGetLastError(), "dp_adam_broadcast launch");
+    return 0;
 }
 
 int sc_adam_apply(float* p, float* mu, float* nu, const float* g, int64_t n, const ScAdam* adam, void* stream) {

@@ -195,7 +195,7 @@ int sae_step_f16_impl(const ScStepArgs& a) {
     const AdamConst ad = make_adam(a.adam);
     const int xg = a.x_per_member ? M : 1;
     const int Bn = a.B_total > 0 ? a.B_total : B;
-    const bool grad_mode = a.grad_enc != nullptr;
+    const bool grad_mode = a.grad_enc != nullptr || a.rs_world > 0;
     const long long Bd = (long long)B * d, BN_ = (long long)B * N, Nd = (long long)N * d;
     const float sc_ = 2.0f / ((float)Bn * (float)d);
     __half* c_h = static_cast<__half*>(a.out_c_half);
@@ -249,9 +249,10 @@ int sae_step_f16_impl(const ScStepArgs& a) {
             u.s_part = projected ? w.s_part : nullptr;
             u.inv_norm = projected ? w.inv_norm : nullptr;
             u.projected = projected ? 1 : 0;
-            u.grad_only = grad ? 1 : 0;
+            u.grad_only = (grad || a.rs_world > 0) ? 1 : 0;
             return 0;
         };
+        SC_TRY(fill_rs(e, a));
         if (!a.tied) {
             Seg s45[2] = {{mnmajor_h(w.dz_h, N, B, M, BN_), mnmajor_h(w.x_h, d, B, xg, Bd)},
                           {mnmajor_h(c_h, N, B, M, BN_), mnmajor_h(w.r_h, d, B, M, Bd)}};
@@ -270,7 +271,7 @@ int sae_step_f16_impl(const ScStepArgs& a) {
     launch_k(finalize_kernel, dim3(dim3(ceil_div(N, 256), M)), dim3(256), 0, st, w.l1_part, w.n_l1, w.mse_part, w.n_mse, w.db_part, w.tiles_b,
                                                              a.bias, a.bias_mu, a.bias_nu, a.l1_alpha, a.bias_decay,
                                                              a.out_losses, M, Bn, d, N, a.tied, ad,
-                                                             grad_mode ? a.grad_bias : nullptr, w.bnorm, sc_);
+                                                             grad_mode ? a.grad_bias : nullptr, w.bnorm, sc_, make_rs_final(a));
     SC_CUDA(cudaGetLastError(), "finalize launch");
     prof_mark(st, "finalize");
     if (a.out_c) {  // caller wants the fp32 aux tensor as well

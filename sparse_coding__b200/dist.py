@@ -89,3 +89,124 @@ class DataParallelEnsemble:
         if "l_bias_decay" in losses and not getattr(eng, "_kind", "") == "tied":
             out["l_bias_decay"] = parts[2]
         return out, aux
+
+
+class _SymmetricFabric:
+    """Peer-mapped buffers and cross-rank barriers from torch.distributed._symmetric_memory (plumbing only: the
+    data moves in this library's kernels, through the peer addresses handed out here)."""
+
+    def __init__(self, group=None):
+        import torch.distributed._symmetric_memory as symm
+        self._symm = symm
+        self.group = group if group is not None else dist.group.WORLD
+        self.world = dist.get_world_size(self.group)
+        self.rank = dist.get_rank(self.group)
+        self._handles = []
+
+    def empty(self, shape, device):
+        """-> (local tensor, [device address of every rank's tensor, usable from THIS rank's kernels])"""
+        t = self._symm.empty(*shape, dtype=torch.float32, device=device)
+        h = self._symm.rendezvous(t, self.group)
+        self._handles.append(h)
+        return t, [int(p) for p in h.buffer_ptrs]
+
+    def barrier(self):
+        self._handles[0].barrier()  # on the current stream: signals exchanged with system-scope release / acquire
+
+
+class FusedDataParallel:
+    """Data-parallel training of ONE dictionary with the gradient collective fused into the kernels (SURVEY 8e:
+    reduce-scatter + sharded Adam + parameter broadcast, overlapped with the weight-gradient GEMMs) - no NCCL call
+    on the data path.
+
+    Rank r owns dictionary rows [r N/W, (r+1) N/W).  Per step every rank runs the fused step on its batch rows in
+    scatter mode: the weight-gradient kernel's epilogue ADDS each 32 x 32 gradient tile straight into the owner's
+    accumulation buffer over NVLink (TMA reduce-add on peer memory), so the reduction traffic is spread under the
+    GEMMs; after one barrier the owner runs Adam on its slice and stores the new values into every rank's parameter
+    copy (`sc_dp_adam_broadcast`), after a second barrier all copies agree.  Summation order across ranks is not
+    fixed, so results agree with the all-reduce path to fp32 rounding, not bitwise.
+
+    `engine`: a FunctionalEnsemble with one member; its parameters are moved into peer-mapped memory.  Every rank must
+    pass the same number of batch rows.  `fabric` (tests): anything with world / rank / empty() / barrier().
+    """
+
+    def __init__(self, engine, group=None, fabric=None):
+        if engine.n_models != 1:
+            raise ValueError("FusedDataParallel trains one dictionary (n_models == 1); shard ensembles by member instead")
+        self.engine = engine
+        self.fabric = fabric if fabric is not None else _SymmetricFabric(group)
+        self.world, self.rank = self.fabric.world, self.fabric.rank
+        enc = engine.params["encoder"]
+        _, N, d = enc.shape
+        if N % (32 * self.world):
+            raise ValueError(f"dictionary size {N} must be a multiple of 32 * world ({32 * self.world})")
+        self.rows, self.d, self.N = N // self.world, d, N
+        dev = enc.device
+        self.keys = [k for k in ("encoder", "decoder") if k in engine.params]
+        self._peer_params = {}
+        for k in list(engine.params):  # parameters live in peer-mapped memory from here on
+            t, ptrs = self.fabric.empty(tuple(engine.params[k].shape), dev)
+            t.copy_(engine.params[k])
+            engine.params[k] = t
+            self._peer_params[k] = ptrs
+        # this rank's accumulation buffers: summed gradient of its rows of each matrix, of its bias slice, loss terms
+        self._off = {}
+        n = 0
+        for k in self.keys:
+            self._off[k] = n
+            n += self.rows * d
+        self._off["encoder_bias"] = n
+        n += self.rows
+        self._off["losses"] = n
+        n += 4
+        self.acc, self._peer_acc = self.fabric.empty((n,), dev)
+        self.acc.zero_()
+        torch.cuda.synchronize(dev)
+        self.fabric.barrier()
+
+    def _rs_args(self):
+        a = lambda key: [p + 4 * self._off[key] for p in self._peer_acc]
+        rs = {"world": self.world, "rows": self.rows, "grad_enc": a("encoder"), "grad_bias": a("encoder_bias"),
+              "losses": a("losses")}
+        if "decoder" in self._off:
+            rs["grad_dec"] = a("decoder")
+        return rs
+
+    def scatter(self, local_rows, expand_dims=True):
+        """Phase 1: forward, backward, gradients added into their owners' buffers.  Returns aux."""
+        eng = self.engine
+        bd = eng.buffers["bias_decay"].to(torch.float32) / self.world  # each rank contributes 1/W of the bias-decay term
+        _, aux = eng.scatter_grads(local_rows, self._rs_args(), expand_dims=expand_dims,
+                                   batch_total=local_rows.shape[-2] * self.world, bias_decay=bd)
+        return aux
+
+    def update(self):
+        """Phase 2 (after every rank finished phase 1): Adam on the owned slices, broadcast into all copies."""
+        import ctypes as C
+        from . import _native as nat
+        eng, L = self.engine, nat.lib()
+        adam = eng.adam_constants(advance=True)
+        st = eng.optim_states[0]
+        parts = self.acc[self._off["losses"]:self._off["losses"] + 3].clone()
+        self.acc[self._off["losses"]:].zero_()
+        lo, hi = self.rank * self.rows, (self.rank + 1) * self.rows
+        for k in self.keys + ["encoder_bias"]:
+            per_row = self.d if k != "encoder_bias" else 1
+            n = self.rows * per_row
+            g = self.acc[self._off[k]:self._off[k] + n]
+            p, mu, nu = eng.params[k][0, lo:hi], st.mu[k][0, lo:hi], st.nu[k][0, lo:hi]
+            dst = (C.c_void_p * self.world)(*[ptr + 4 * lo * per_row for ptr in self._peer_params[k]])
+            with torch.cuda.device(p.device):
+                nat.check(L.sc_dp_adam_broadcast(nat.ptr(g), nat.ptr(mu), nat.ptr(nu), nat.ptr(p), dst, self.world, n,
+                                                 C.byref(adam), nat.stream_ptr(p.device)), "sc_dp_adam_broadcast")
+        out = {"loss": parts.sum(0, keepdim=True), "l_reconstruction": parts[0:1], "l_l1": parts[1:2]}
+        if getattr(eng, "_kind", "") != "tied":
+            out["l_bias_decay"] = parts[2:3]
+        return out
+
+    def step_batch(self, local_rows, expand_dims=True):
+        aux = self.scatter(local_rows, expand_dims)
+        self.fabric.barrier()   # every contribution has landed in its owner's buffer
+        out = self.update()
+        self.fabric.barrier()   # every copy of the parameters is complete before anyone's next step reads it
+        return out, aux

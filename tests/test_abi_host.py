@@ -56,7 +56,7 @@ def test_struct_layouts_match_the_header_field_order():
             if not decl:
                 continue
             decl = re.sub(r"^(const\s+)?(float|int32_t|size_t|void|ScAdam|char)\s*\**", "", decl)
-            names += [n.strip().lstrip("*") for n in decl.split(",")]
+            names += [re.sub(r"\[\d+\]$", "", n.strip().lstrip("*")) for n in decl.split(",")]
         assert names == [f[0] for f in cls._fields_], cname
 
 

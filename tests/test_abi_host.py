@@ -114,3 +114,16 @@ def test_separate_tensors_and_unstack_errors_match_reference():
         separate_tensors({"a": torch.zeros(3, 2)}, 2)
     out = separate_tensors({"a": torch.arange(6.).reshape(3, 2)}, 3)
     assert len(out) == 3 and torch.equal(out[1]["a"], torch.tensor([2., 3.]))
+
+
+def test_integration_stub_struct_matches_the_binding():
+    """The ctypes stub printed in INTEGRATION.md (what a reference maintainer would paste) must describe the same
+    ScStepArgs as the package's own binding: same field names in the same order, same size."""
+    from sparse_coding__b200 import _native as nat
+    src = open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    code = src[src.index("class ScAdam(C.Structure):"):src.index("L.sc_sae_step_workspace_bytes.restype")]
+    ns = {"C": ctypes}
+    exec(code, ns)
+    stub = ns["ScStepArgs"]
+    assert [f[0] for f in stub._fields_] == [f[0] for f in nat.ScStepArgs._fields_]
+    assert ctypes.sizeof(stub) == ctypes.sizeof(nat.ScStepArgs)

@@ -14,6 +14,7 @@ import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libsc_b200.so")
+LIB_PATH = os.environ.get("SC_B200_LIB", LIB_PATH)  # A/B runs against another build of the same ABI
 CSRC = os.path.join(_HERE, "csrc")
 
 _lib = None

@@ -51,22 +51,24 @@ struct GemmShape {
 
 constexpr int kEpiWarps = 4 * 2;  // 4 row quarters x kEpiHalves
 
-template <int BN, int IO = 0>
+template <int BN, int IO = 0, int H = kEpiHalves>
 struct GemmCfg {
     static constexpr int kBTileBytes = BN * kBlockK * 4;
     static constexpr int kStageBytes = kATileBytes + kBTileBytes;
-    static constexpr int kIoBytes = kEpiWarps * IO * kIoTileBytes;  // epilogue staging tiles (epi_io.cuh)
+    static constexpr int kWarpsEpi = 4 * H;
+    static constexpr int kThreads = 128 + 32 * kWarpsEpi;
+    static constexpr int kIoBytes = kWarpsEpi * IO * kIoTileBytes;  // epilogue staging tiles (epi_io.cuh)
     static constexpr int kStagesRaw = (227 * 1024 - 2048 - kIoBytes) / kStageBytes;
     static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
     static constexpr int kTmemCols = (2 * BN <= 32) ? 32 : (2 * BN <= 64) ? 64 : (2 * BN <= 128) ? 128 : (2 * BN <= 256) ? 256 : 512;
-    static constexpr int kBarrierBytes = (2 * kStages + 4 + kIoBars * kEpiWarps) * 8 + 16;
+    static constexpr int kBarrierBytes = (2 * kStages + 4 + kIoBars * kWarpsEpi) * 8 + 16;
     static constexpr int kSmemBytes = kStages * kStageBytes + kIoBytes + kBarrierBytes + 1024;  // + alignment slack
     static_assert(BN % 32 == 0 && BN >= 32 && BN <= 256, "BN must be a multiple of 32 in [32,256]");
     static_assert(kStages >= 2, "not enough shared memory left for the operand pipeline");
 };
 
-// Epilogue warps per 32-row quarter of the tile: kEpiHalves unless the functor asks for more (Epi::kHalves; only
-// the CTA-pair kernel honours it).  More warps = more issue slots for instruction-bound epilogues, fewer chunks each.
+// Epilogue warps per 32-row quarter of the tile: kEpiHalves unless the functor sets Epi::kHalves (1: four epilogue
+// warps, each with twice the staging memory - room to double-buffer; 4: sixteen).
 template <class E, class = void>
 struct EpiHalvesOf { static constexpr int v = kEpiHalves; };
 template <class E>
@@ -89,6 +91,7 @@ struct RowCtx {
     int bn;         // tile width in columns
     int first;      // 1 on the warp's first tile (nothing was prefetched for it)
     int next_g;     // group of the next tile, -1 when this is the last one
+    int next_prob;  // its problem index
     int next_row0;  // first global row of this warp's 32-row slice in the next tile
     int next_col0;  // first global column of the next tile
 };
@@ -123,11 +126,11 @@ SC_DEVICE void epilogue_tile(const typename Epi::Params& ep, const RowCtx& ctx, 
 }
 
 template <int BN, bool A_MN, bool B_MN, class Epi>
-__global__ void __launch_bounds__(kGemmThreads, 1)
+__global__ void __launch_bounds__(128 + 128 * EpiHalvesOf<Epi>::v, 1)
 gemm_tf32_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
                  const __grid_constant__ typename Epi::Params ep) {
-    using Cfg = GemmCfg<BN, Epi::kIoBufs>;
-    static_assert(EpiHalvesOf<Epi>::v == kEpiHalves, "the single-CTA kernel runs kEpiHalves epilogue warps per quarter");
+    constexpr int kH = EpiHalvesOf<Epi>::v;
+    using Cfg = GemmCfg<BN, Epi::kIoBufs, kH>;
     constexpr int kStages = Cfg::kStages;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -137,7 +140,7 @@ gemm_tf32_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
     uint64_t* tmem_full = empty_bar + kStages;
     uint64_t* tmem_empty = tmem_full + 2;
     uint64_t* io_bar = tmem_empty + 2;
-    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(io_bar + kIoBars * kEpiWarps);
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(io_bar + kIoBars * Cfg::kWarpsEpi);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -156,9 +159,9 @@ gemm_tf32_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(&tmem_full[i], 1);
-            mbar_init(&tmem_empty[i], 128 * kEpiHalves);
+            mbar_init(&tmem_empty[i], 128 * kH);
         }
-        for (int i = 0; i < kIoBars * kEpiWarps; ++i) mbar_init(&io_bar[i], 1);
+        for (int i = 0; i < kIoBars * Cfg::kWarpsEpi; ++i) mbar_init(&io_bar[i], 1);
         fence_mbar_init();
     }
     if (warp == 2) {
@@ -281,15 +284,15 @@ gemm_tf32_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
             const uint32_t aph = (it >> 1) & 1;
             RowCtx ctx;
             ctx.g = g; ctx.row = tm * kBlockM + q * 32 + lane; ctx.col0 = tn * BN;
-            ctx.M = shape.M; ctx.N = shape.N; ctx.tile_m = tm; ctx.tile_n = tn; ctx.tiles_m = shape.tiles_m; ctx.tiles_n = shape.tiles_n; ctx.warp_q = q; ctx.prob = prob; ctx.half = half; ctx.halves = kEpiHalves; ctx.part = q + 4 * half;
+            ctx.M = shape.M; ctx.N = shape.N; ctx.tile_m = tm; ctx.tile_n = tn; ctx.tiles_m = shape.tiles_m; ctx.tiles_n = shape.tiles_n; ctx.warp_q = q; ctx.prob = prob; ctx.half = half; ctx.halves = kH; ctx.part = q + 4 * half;
             ctx.bn = BN; ctx.first = it == 0;
-            ctx.next_g = -1; ctx.next_row0 = 0; ctx.next_col0 = 0;
+            ctx.next_g = -1; ctx.next_prob = 0; ctx.next_row0 = 0; ctx.next_col0 = 0;
             if (tile + static_cast<int>(gridDim.x) < total_tiles) {
                 const int nt = tile + gridDim.x;
                 const int ngg = nt / tiles_per_group;
                 const int nrem = nt - ngg * tiles_per_group;
                 const int ntn = nrem / shape.tiles_m;
-                ctx.next_g = ngg % shape.G; ctx.next_row0 = (nrem - ntn * shape.tiles_m) * kBlockM + q * 32; ctx.next_col0 = ntn * BN;
+                ctx.next_g = ngg % shape.G; ctx.next_prob = ngg / shape.G; ctx.next_row0 = (nrem - ntn * shape.tiles_m) * kBlockM + q * 32; ctx.next_col0 = ntn * BN;
             }
             const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
             epilogue_tile<BN, Epi>(ep, ctx, io, &tmem_full[as], aph, taddr, [&] { mbar_arrive(&tmem_empty[as]); });
@@ -322,7 +325,7 @@ inline bool use_pdl_plain() { return (pdl_mask() & 1) != 0; }
 template <int BN, bool A_MN, bool B_MN, class Epi>
 cudaError_t launch_gemm(const GemmMaps& maps, GemmShape shape, const typename Epi::Params& ep, int num_sms,
                         cudaStream_t stream) {
-    using Cfg = GemmCfg<BN, Epi::kIoBufs>;
+    using Cfg = GemmCfg<BN, Epi::kIoBufs, EpiHalvesOf<Epi>::v>;
     auto kern = gemm_tf32_kernel<BN, A_MN, B_MN, Epi>;
     static bool attr_set[64] = {};  // per template instantiation, per device
     int dev = 0;
@@ -339,7 +342,7 @@ cudaError_t launch_gemm(const GemmMaps& maps, GemmShape shape, const typename Ep
     const int grid = static_cast<int>(total < num_sms ? total : num_sms);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(grid);
-    cfg.blockDim = dim3(kGemmThreads);
+    cfg.blockDim = dim3(Cfg::kThreads);
     cfg.dynamicSmemBytes = Cfg::kSmemBytes;
     cfg.stream = stream;
     cudaLaunchAttribute attr[1];

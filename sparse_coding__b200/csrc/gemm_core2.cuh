@@ -223,13 +223,14 @@ gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape sha
             ctx.tile_m = tm * 2 + rank; ctx.tile_n = tn; ctx.tiles_m = shape.tiles_m * 2; ctx.tiles_n = shape.tiles_n;
             ctx.warp_q = q; ctx.prob = prob; ctx.half = half; ctx.halves = kH; ctx.part = q + 4 * half;
             ctx.bn = BN; ctx.first = it == 0;
-            ctx.next_g = -1; ctx.next_row0 = 0; ctx.next_col0 = 0;
+            ctx.next_g = -1; ctx.next_prob = 0; ctx.next_row0 = 0; ctx.next_col0 = 0;
             if (tile + num_clusters < total_tiles) {
                 const int nt = tile + num_clusters;
                 const int ngg = nt / tiles_per_group;
                 const int nrem = nt - ngg * tiles_per_group;
                 const int ntn = nrem / shape.tiles_m;
                 ctx.next_g = ngg % shape.G;
+                ctx.next_prob = ngg / shape.G;
                 ctx.next_row0 = (nrem - ntn * shape.tiles_m) * (2 * kBlockM) + rank * kBlockM + q * 32;
                 ctx.next_col0 = ntn * BN;
             }

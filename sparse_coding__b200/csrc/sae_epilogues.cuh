@@ -250,7 +250,11 @@ SC_DEVICE void adam_update(float& p, float& mu, float& nu, float g, const AdamCo
 }
 
 struct EpiAdam {
-    static constexpr int kIoBufs = 3;  // p, mu, nu tiles staged per warp; loaded and stored by TMA
+    // HBM-bound epilogue: what matters is how many tile loads and stores are in flight.  Four epilogue warps
+    // (kHalves = 1), each with TWO sets of p / mu / nu staging tiles: while one set is computed on and stored, the
+    // other is already loading the warp's next chunk - across tile boundaries too (static tile schedule).
+    static constexpr int kHalves = 1;
+    static constexpr int kIoBufs = 6;  // 2 sets x (p, mu, nu) x 4 KB per warp
     struct alignas(64) Sub {
         CUtensorMap p_map, mu_map, nu_map;  // io maps of [G][N][d]
         CUtensorMap grad_map;               // io map of the gradient output (gradient-only mode)
@@ -285,30 +289,42 @@ struct EpiAdam {
             inv = fabsf(iv);
         }
     }
-    // tile loads for the chunk at tile column `co` (whole warp calls; lane 0 issues)
-    SC_DEVICE void prefetch(int co) {
-        io_wait_stores_read();  // staging tiles are free once the previous stores have read them
-        if ((threadIdx.x & 31) == 0) {
-            const int col = c.col0 + co, row0 = c.row;  // lane 0 owns the warp's first row
-            uint8_t* b = io.buf;
-            if (u.grad_only) {
-                io_expect(io, kIoTileBytes);
-                tma_load_3d(&u.p_map, io.bar, b, col, row0, c.g);
-            } else {
-                io_expect(io, 3 * kIoTileBytes);
-                tma_load_3d(&u.p_map, io.bar, b, col, row0, c.g);
-                tma_load_3d(&u.mu_map, io.bar, b + kIoTileBytes, col, row0, c.g);
-                tma_load_3d(&u.nu_map, io.bar, b + 2 * kIoTileBytes, col, row0, c.g);
-            }
+    // lane 0: tile loads of one chunk (problem `sub`, group g, rows row0.., columns col..) into staging set `set`
+    SC_DEVICE void request(int set, const Sub& sub, int g, int row0, int col) const {
+        uint8_t* b = io.buf + set * (3 * kIoTileBytes);
+        if (sub.grad_only) {
+            io_expect(io, kIoTileBytes, set);
+            tma_load_3d(&sub.p_map, io.bar + set, b, col, row0, g);
+        } else {
+            io_expect(io, 3 * kIoTileBytes, set);
+            tma_load_3d(&sub.p_map, io.bar + set, b, col, row0, g);
+            tma_load_3d(&sub.mu_map, io.bar + set, b + kIoTileBytes, col, row0, g);
+            tma_load_3d(&sub.nu_map, io.bar + set, b + 2 * kIoTileBytes, col, row0, g);
         }
+    }
+    // Called by the core before it waits for the accumulator.  Only the warp's very first tile needs it: every
+    // later first chunk was requested by the last chunk of the tile before.
+    SC_DEVICE void prefetch(int co) {
+        if (c.first && (threadIdx.x & 31) == 0) request((co >> 5) & 1, u, c.g, c.row, c.col0 + co);
     }
     SC_DEVICE void chunk(int co, float (&v)[32], int next_co) {
         const int lane = threadIdx.x & 31;
+        const int set = (co >> 5) & 1;  // kHalves == 1: consecutive chunks alternate between the two sets
         const int col = c.col0 + co, row0 = c.row - lane;
-        uint8_t* b = io.buf;
-        io_wait_loads(io);
-        float pv[32];
+        uint8_t* b = io.buf + set * (3 * kIoTileBytes);
+        io_wait_loads(io, set);
+        float pv[32], mv[32], nv[32];
         io_read_row(b, lane, pv);
+        if (!u.grad_only) {
+            io_read_row(b + kIoTileBytes, lane, mv);
+            io_read_row(b + 2 * kIoTileBytes, lane, nv);
+        }
+        // the other set was stored one chunk ago; once that store has read it, the next chunk loads into it
+        io_wait_stores_read();
+        if (lane == 0) {
+            if (next_co >= 0) request(set ^ 1, u, c.g, row0, c.col0 + next_co);
+            else if (c.next_g >= 0) request(set ^ 1, p.sub[c.next_prob], c.next_g, c.next_row0, c.next_col0);
+        }
         if (p.g_scale != 1.f) {
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] *= p.g_scale;
@@ -330,9 +346,6 @@ struct EpiAdam {
                 io_store_tile(&u.grad_map, b, col, row0, c.g);
             }
         } else {
-            float mv[32], nv[32];
-            io_read_row(b + kIoTileBytes, lane, mv);
-            io_read_row(b + 2 * kIoTileBytes, lane, nv);
 #pragma unroll
             for (int j = 0; j < 32; ++j) adam_update(pv[j], mv[j], nv[j], v[j], p.a);
             io_write_row(b, lane, pv);
@@ -347,7 +360,6 @@ struct EpiAdam {
             }
         }
         io_commit();
-        if (next_co >= 0) prefetch(next_co);
     }
     SC_DEVICE void finish() {}
 };

@@ -211,6 +211,30 @@ class FunctionalEnsemble:
             for v in group.values():
                 v.share_memory_()
 
+    def reinit_dead_features(self, member, c_totals, worst_vectors, encoder_norm_ratio=0.2):
+        """Dead-feature re-initialisation of experiments/huge_batch_size.py:224-254 for one ensemble member (that
+        script keeps its encoder as [d, N]; here dictionaries are [N, d], so columns there are rows here): features
+        whose summed activation `c_totals` [N] is zero get the worst-reconstructed data vectors `worst_vectors`
+        [n_dead, d] as encoder rows, scaled to `encoder_norm_ratio` / (mean encoder row norm), and the Adam moments
+        of every parameter of those features are reset.  Returns the indices that were replaced."""
+        dead = torch.where(c_totals.to(self.params["encoder"].device) == 0)[0]
+        n = int(dead.numel())
+        if n == 0:
+            return dead
+        wv = torch.as_tensor(worst_vectors, dtype=torch.float32, device=dead.device)
+        if wv.dim() == 1:  # huge_batch_size.py:234-235, n_replace == 1
+            wv = wv.unsqueeze(0)
+        if wv.shape[0] < n:
+            raise ValueError(f"{n} dead features but only {wv.shape[0]} replacement vectors")
+        enc = self.params["encoder"][member]
+        av_norm = torch.norm(enc, dim=1).mean()
+        enc[dead] = wv[:n] * encoder_norm_ratio / av_norm
+        st = self.optim_states[0]
+        for group in (st.mu, st.nu):
+            for v in group.values():
+                v[member][dead] = 0
+        return dead
+
     # ------------------------------------------------------------------ the hot path
     def _contig(self, store: dict, key: str, shape=None) -> torch.Tensor:
         t = store[key]

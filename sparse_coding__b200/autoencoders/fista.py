@@ -94,6 +94,30 @@ class FunctionalFista(DictSignature):
         return learned_dict / (learned_dict.norm(2, 0))
 
     @staticmethod
+    def quadratic_basis_update_rows(learned_dict, Res, ahat, lowestActivation, HessianDiag, stepSize=0.001, Noneg=False):
+        """What fista.py:131-138 is after, valid for any N and d: the same preconditioned gradient
+        step on the reconstruction error, dBasis[n] = stepSize * mean_b(a_bn Res_b) / (H_n + lowestActivation), with
+        every ATOM (row of the [N, d] dictionary) renormalised to unit length afterwards."""
+        dBasis = stepSize * torch.mm(ahat.t(), Res) / ahat.size(0)            # [N, d]
+        dBasis = dBasis / (HessianDiag + lowestActivation)[:, None]
+        learned_dict = learned_dict + dBasis
+        if Noneg:
+            learned_dict = learned_dict.clamp(min=0.)
+        return learned_dict / learned_dict.norm(2, 1, keepdim=True).clamp_min(1e-8)
+
+    @staticmethod
+    def dictionary_update_corrected(params, buffers, batch_centered, coeffs, learned_dict, num_iter=500):
+        """dictionary_update without the reference's defects: works for N != d (row-wise update and
+        normalisation) and the running Hessian diagonal PERSISTS (updated in place in buffers["hessian_diag"])."""
+        device = params["encoder"].device
+        coeffs_fista, res = FunctionalFista.fista(batch_centered, learned_dict, buffers["l1_alpha"], coeffs, num_iter, device)
+        ACT_HISTORY_LEN = 300
+        buffers["hessian_diag"].mul_((ACT_HISTORY_LEN - 1.0) / ACT_HISTORY_LEN).add_(
+            torch.pow(coeffs_fista, 2).mean(0) / ACT_HISTORY_LEN)
+        new_dict = FunctionalFista.quadratic_basis_update_rows(learned_dict, res, coeffs_fista, 0.001, buffers["hessian_diag"])
+        return new_dict, res
+
+    @staticmethod
     def dictionary_update(params, buffers, batch_centered, coeffs, learned_dict):
         """fista.py:88-96: 500 FISTA iterations from the SAE codes, running Hessian diagonal (kept in
         the dict the caller hands in), quadratic basis update."""

@@ -32,7 +32,10 @@ def ensemble_train_loop(ensemble, cfg, args, ensemble_name, sampler, dataset, pr
     dict_size == activation_size and the ensemble has more than one member (its normalisation
     broadcasts [M,N,d]/[M,1,N], and `squeeze(0)`), and raises otherwise.  `fista_dictionary_update`:
     None (default) = do what the reference does when it can run (N == d, M > 1) and raise the same
-    way when it cannot; False = plain SAE training loop without the FISTA block; True = force it.
+    way when it cannot; False = plain SAE training loop without the FISTA block; True = force it;
+    "corrected" = the same idea without the defects: every member's decoder is row-normalised,
+    updated by FunctionalFista.dictionary_update_corrected (valid for any N, d and M; the Hessian diagonal
+    persists in ensemble.buffers["hessian_diag"]) and written back.
     """
     torch.set_grad_enabled(False)
     torch.manual_seed(0)
@@ -56,7 +59,19 @@ def ensemble_train_loop(ensemble, cfg, args, ensemble_name, sampler, dataset, pr
 
         losses, aux_buffer = ensemble.step_batch(batch)
 
-        if fista_dictionary_update is not False and "decoder" in ensemble.params:
+        if fista_dictionary_update == "corrected" and "decoder" in ensemble.params:
+            from .autoencoders.learned_dict import _row_normalise_native
+            D = _row_normalise_native(ensemble.params["decoder"])
+            if "hessian_diag" not in ensemble.buffers:
+                ensemble.buffers["hessian_diag"] = torch.zeros_like(ensemble.params["encoder_bias"])
+            c_all = aux_buffer["c"]
+            for j in range(ensemble.n_models):
+                params_j = {k: v[j] for k, v in ensemble.params.items()}
+                buffers_j = {k: v[j] for k, v in ensemble.buffers.items()}   # views: in-place updates persist
+                xb = batch if batch.dim() == 2 else batch[j]
+                new_dict, _ = FunctionalFista.dictionary_update_corrected(params_j, buffers_j, xb, c_all[j], D[j])
+                ensemble.params["decoder"][j].copy_(new_dict)
+        elif fista_dictionary_update is not False and "decoder" in ensemble.params:
             params = ensemble.params
             buffers = ensemble.buffers
             c = aux_buffer["c"].squeeze(0).to(dtype)

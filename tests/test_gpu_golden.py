@@ -115,3 +115,65 @@ def test_train_loop_with_fista_dictionary_update_runs_only_when_square():
         sc.ensemble_train_loop(ens2, Cfg(), {"device": "cuda", "dict_size": 2 * d}, "e", sampler, data, Counter(), torch.float32)
     sc.ensemble_train_loop(ens2, Cfg(), {"device": "cuda", "dict_size": 2 * d}, "e", sampler, data, Counter(), torch.float32,
                            fista_dictionary_update=False)
+
+
+def test_corrected_dictionary_update_and_dead_feature_reinit():
+    """the row-normalised dictionary update works for N != d, keeps unit atoms, lowers the reconstruction
+    error of the FISTA codes and keeps its Hessian diagonal; dead features are re-seeded as in
+    experiments/huge_batch_size.py:224-254 with their Adam state cleared."""
+    import sparse_coding__b200 as sc
+    from sparse_coding__b200.autoencoders.fista import FunctionalFista
+
+    class Cfg:
+        use_wandb = False
+
+    class Counter:
+        value = 0
+
+    torch.manual_seed(0)
+    d, N, B, M = 64, 192, 512, 2
+    models = [FunctionalFista.init(d, N, l1, device="cuda") for l1 in (1e-2, 3e-2)]
+    ens = sc.FunctionalEnsemble(models, FunctionalFista, sc.torchopt_compat.adam, {"lr": 1e-3}, device="cuda")
+    g = torch.Generator().manual_seed(1)
+    feats = torch.randn(2 * N, d, generator=g)
+    feats /= feats.norm(dim=1, keepdim=True)
+    codes = torch.zeros(4 * B, 2 * N)
+    idx = torch.rand(4 * B, 2 * N, generator=g).argsort(1)[:, :5]
+    codes.scatter_(1, idx, torch.rand(4 * B, 5, generator=g))
+    data = (codes @ feats).cuda()
+    batches = [list(range(i * B, (i + 1) * B)) for i in range(4)]
+    sc.ensemble_train_loop(ens, Cfg(), {"device": "cuda"}, "e", batches, data, Counter(), torch.float32,
+                           fista_dictionary_update="corrected")
+    dec = ens.params["decoder"]
+    assert torch.allclose(dec.norm(dim=-1), torch.ones(M, N, device="cuda"), atol=1e-5)
+    assert float(ens.buffers["hessian_diag"].abs().sum()) > 0           # persisted, unlike the reference's
+    # one more update on a fixed batch lowers the FISTA reconstruction error for that batch
+    x = data[:B]
+    p0 = {k: v[0] for k, v in ens.params.items()}
+    b0 = {k: v[0] for k, v in ens.buffers.items()}
+    D0 = dec[0].clone()
+    a0 = torch.relu(x @ D0.T)
+    _, res0 = FunctionalFista.fista(x, D0, b0["l1_alpha"], a0, 200, "cuda")
+    D1, _ = FunctionalFista.dictionary_update_corrected(p0, b0, x, a0, D0, num_iter=200)
+    for _ in range(20):
+        D1, _ = FunctionalFista.dictionary_update_corrected(p0, b0, x, a0, D1, num_iter=200)
+    _, res1 = FunctionalFista.fista(x, D1, b0["l1_alpha"], a0, 200, "cuda")
+    assert float(res1.pow(2).mean()) < float(res0.pow(2).mean())
+    # dead-feature re-initialisation
+    c_totals = torch.ones(N, device="cuda")
+    c_totals[[3, 50, 191]] = 0
+    worst = torch.randn(3, d, device="cuda")
+    st = ens.optim_states[0]
+    enc_before = ens.params["encoder"].clone()
+    av = enc_before[1].norm(dim=1).mean()
+    dead = ens.reinit_dead_features(1, c_totals, worst)
+    assert dead.tolist() == [3, 50, 191]
+    assert torch.allclose(ens.params["encoder"][1, dead], worst * 0.2 / av)
+    keep = torch.ones(N, dtype=torch.bool, device="cuda")
+    keep[dead] = False
+    assert torch.equal(ens.params["encoder"][1, keep], enc_before[1, keep]) and torch.equal(ens.params["encoder"][0], enc_before[0])
+    for grp in (st.mu, st.nu):
+        for k, v in grp.items():
+            assert float(v[1][dead].abs().sum()) == 0 and float(v[1].abs().sum()) > 0, k
+    assert ens.reinit_dead_features(0, torch.ones(N), worst).numel() == 0
+    ens.step_batch(x)  # the engine keeps training on the edited state

@@ -74,6 +74,14 @@ struct EpiHalvesOf { static constexpr int v = kEpiHalves; };
 template <class E>
 struct EpiHalvesOf<E, decltype((void)E::kHalves)> { static constexpr int v = E::kHalves; };
 
+// Optional work for warp 3, which has no role in the GEMM: Epi::side_job(params, cta, nctas) when the functor has one.
+template <class E>
+SC_DEVICE auto run_side_job(const typename E::Params& p, int cta, int nctas, int) -> decltype(E::side_job(p, cta, nctas), void()) {
+    E::side_job(p, cta, nctas);
+}
+template <class E>
+SC_DEVICE void run_side_job(const typename E::Params&, int, int, long) {}
+
 // Context handed to an epilogue functor for one accumulator row of one tile.
 struct RowCtx {
     int g;       // group / ensemble member
@@ -266,6 +274,8 @@ gemm_tf32_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
                 umma_commit(&tmem_full[as]);  // accumulator ready for the epilogue
             }
         }
+    } else if (warp == 3) {
+        run_side_job<Epi>(ep, blockIdx.x, gridDim.x, 0);
     } else if (warp >= 4) {
         // ------------------------------------------------------------------ epilogue
         const int q = warp & 3;

@@ -200,6 +200,8 @@ gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape sha
                 umma_commit_2cta(&tmem_full[as]);
             }
         }
+    } else if (warp == 3) {
+        run_side_job<Epi>(ep, blockIdx.x, gridDim.x, 0);
     } else if (warp >= 4) {
         // ------------------------------------------------------------------ epilogue (both CTAs, own 128 rows)
         const int q = warp & 3;

@@ -249,6 +249,80 @@ SC_DEVICE void adam_update(float& p, float& mu, float& nu, float g, const AdamCo
     p = fmaf(upd, -a.lr, p);
 }
 
+// ---------------------------------------------------------------------------------------------
+// Finalize: loss scalars (sae_ensemble.py:62-71) from the per-warp partials of G1 / G2, bias gradient
+// db + beta b/||b|| (zero sub-gradient at b == 0) and its Adam step.  Small, latency-bound work that depends
+// on G1-G3 only: it runs on the otherwise idle fourth warp of every CTA of the weight-gradient kernel
+// (EpiAdam::side_job), concurrently with that kernel's first tile, instead of in a launch of its own.
+// ---------------------------------------------------------------------------------------------
+struct RsFinal {  // destinations of the fused reduce-scatter mode (ScStepArgs.rs_*): per owner, bias gradient and losses
+    int world, rows;
+    float* bias[8];
+    float* losses[8];
+};
+struct FinalizeArgs {
+    const float* l1_part; int n_l1;
+    const float* mse_part; int n_mse;
+    const float* db_part; int tiles_b;
+    float *bias, *bias_mu, *bias_nu;
+    const float *l1_alpha, *bias_decay;
+    float* out_losses;
+    int M, B, d, N;       // B: the normalising (global) batch size
+    AdamConst a;
+    float* grad_bias;     // gradient-only mode: write the bias gradient here instead of updating
+    const float* bnorm;   // [M] ||b||_2 of the pre-update bias (prologue)
+    float db_scale;
+    RsFinal rs;
+};
+// `warp` of `nwarps` cooperating warps (any number >= 1); deterministic for a given nwarps
+SC_DEVICE void finalize_work(const FinalizeArgs& f, int warp, int nwarps) {
+    const int lane = threadIdx.x & 31;
+    for (int m = warp; m < f.M; m += nwarps) {
+        float acc = 0.f;
+        for (int i = lane; i < f.n_l1; i += 32) acc += f.l1_part[(long long)m * f.n_l1 + i];
+        const float l1_sum = warp_sum(acc);
+        acc = 0.f;
+        for (int i = lane; i < f.n_mse; i += 32) acc += f.mse_part[(long long)m * f.n_mse + i];
+        const float sq_sum = warp_sum(acc);
+        if (lane == 0) {
+            const float l_rec = sq_sum / ((float)f.B * (float)f.d);
+            const float l_l1 = f.l1_alpha[m] * (l1_sum / (float)f.B);
+            const float l_bd = f.bias_decay[m] * f.bnorm[m];
+            f.out_losses[0 * f.M + m] = l_rec + l_l1 + l_bd;
+            f.out_losses[1 * f.M + m] = l_rec;
+            f.out_losses[2 * f.M + m] = l_l1;
+            f.out_losses[3 * f.M + m] = l_bd;
+            // fused data-parallel mode (M == 1): every rank adds its share of the loss terms to every rank's buffer
+            for (int r = 0; r < f.rs.world; ++r) {
+                atomicAdd(f.rs.losses[r] + 0, l_rec);
+                atomicAdd(f.rs.losses[r] + 1, l_l1);
+                atomicAdd(f.rs.losses[r] + 2, l_bd);
+            }
+        }
+    }
+    const long long total = (long long)f.M * f.N;
+    for (long long o = (long long)warp * 32 + lane; o < total; o += (long long)nwarps * 32) {
+        const int m = static_cast<int>(o / f.N), n = static_cast<int>(o - (long long)m * f.N);
+        const float bnorm = f.bnorm[m];
+        const float bscale = bnorm > 0.f ? f.bias_decay[m] / bnorm : 0.f;
+        float g = 0.f;
+        for (int t = 0; t < f.tiles_b; ++t) g += f.db_part[((long long)m * f.tiles_b + t) * f.N + n];
+        g *= f.db_scale;
+        float p = f.bias[o];
+        g += bscale * p;
+        if (f.rs.world > 0) {
+            const int owner = n / f.rs.rows;  // M == 1: o == n
+            atomicAdd(f.rs.bias[owner] + (n - owner * f.rs.rows), g);
+        } else if (f.grad_bias) {
+            f.grad_bias[o] = g;
+        } else {
+            float mu = f.bias_mu[o], nu = f.bias_nu[o];
+            adam_update(p, mu, nu, g, f.a);
+            f.bias[o] = p; f.bias_mu[o] = mu; f.bias_nu[o] = nu;
+        }
+    }
+}
+
 struct EpiAdam {
     // HBM-bound epilogue: what matters is how many tile loads and stores are in flight.  Four epilogue warps
     // (kHalves = 1), each with TWO sets of p / mu / nu staging tiles: while one set is computed on and stored, the
@@ -272,7 +346,13 @@ struct EpiAdam {
         int rs_world;                  // 0: off
         int rs_rows;                   // dictionary rows per owner (multiple of 32)
         CUtensorMap rs_map[2][8];      // [problem][owner]: io map of the owner's [1][rs_rows][d] accumulation buffer
+        int fin_on;                    // 1: the idle warps of this launch also do the step's finalize work
+        FinalizeArgs fin;
     };
+    // warp 3 of CTA `cta` of `nctas` (no role in the GEMM)
+    static SC_DEVICE void side_job(const Params& p, int cta, int nctas) {
+        if (p.fin_on) finalize_work(p.fin, cta, nctas);
+    }
     const Params& p;
     const Sub& u;
     const RowCtx c;

@@ -105,13 +105,6 @@ __global__ void adam_apply_kernel(float4* __restrict__ p, float4* __restrict__ m
     }
 }
 
-// destinations of the fused reduce-scatter mode (ScStepArgs.rs_*): per owner, its bias-gradient and loss buffers
-struct RsFinal {
-    int world, rows;
-    float* bias[8];
-    float* losses[8];
-};
-
 // Owner's Adam on its slice, new parameters stored to every rank's copy (peer-mapped), gradient buffer re-zeroed
 struct PeerDst {
     float4* p[8];
@@ -136,64 +129,11 @@ __global__ void dp_adam_broadcast_kernel(float4* __restrict__ g, float4* __restr
     }
 }
 
-__global__ void finalize_kernel(const float* __restrict__ l1_part, int n_l1, const float* __restrict__ mse_part, int n_mse,
-                                const float* __restrict__ db_part, int tiles_b, float* __restrict__ bias,
-                                float* __restrict__ bias_mu, float* __restrict__ bias_nu,
-                                const float* __restrict__ l1_alpha, const float* __restrict__ bias_decay,
-                                float* __restrict__ out_losses, int M, int B, int d, int N, int tied, AdamConst a,
-                                float* __restrict__ grad_bias, float* __restrict__ bnorm_ws, float db_scale, RsFinal rs) {
+// stand-alone form of the finalize work (sae_epilogues.cuh); the fused steps run it inside the weight-gradient launch
+__global__ void finalize_kernel(FinalizeArgs f) {
     pdl_launch_dependents();
     pdl_wait();
-    // grid (ceil(N/256), M).  Every block needs ||b|| of the PRE-update bias: block x == 0 of each member
-    // computed it into bnorm_ws in bias_norm_kernel (launched before), so no block reads a bias another
-    // block already updated.
-    __shared__ float sh[8];
-    const int m = blockIdx.y;
-    const float bnorm = bnorm_ws[m];
-    const float lam = l1_alpha[m], beta = bias_decay[m];
-    if (blockIdx.x == 0) {
-        float acc = 0.f;
-        for (int i = threadIdx.x; i < n_l1; i += blockDim.x) acc += l1_part[(long long)m * n_l1 + i];
-        const float l1_sum = block_sum(acc, sh);
-        acc = 0.f;
-        for (int i = threadIdx.x; i < n_mse; i += blockDim.x) acc += mse_part[(long long)m * n_mse + i];
-        const float sq_sum = block_sum(acc, sh);
-        if (threadIdx.x == 0) {
-            const float l_rec = sq_sum / ((float)B * (float)d);  // B here is the normalising (global) batch size
-            const float l_l1 = lam * (l1_sum / (float)B);
-            const float l_bd = beta * bnorm;
-            out_losses[0 * M + m] = l_rec + l_l1 + l_bd;
-            out_losses[1 * M + m] = l_rec;
-            out_losses[2 * M + m] = l_l1;
-            out_losses[3 * M + m] = l_bd;
-            // fused data-parallel mode (M == 1): every rank adds its share of the loss terms to every rank's buffer
-            for (int r = 0; r < rs.world; ++r) {
-                atomicAdd(rs.losses[r] + 0, l_rec);
-                atomicAdd(rs.losses[r] + 1, l_l1);
-                atomicAdd(rs.losses[r] + 2, l_bd);
-            }
-        }
-    }
-    const float bscale = bnorm > 0.f ? beta / bnorm : 0.f;
-    const int n = blockIdx.x * blockDim.x + threadIdx.x;
-    if (n < N) {
-        float g = 0.f;
-        for (int t = 0; t < tiles_b; ++t) g += db_part[((long long)m * tiles_b + t) * N + n];
-        g *= db_scale;
-        const long long o = (long long)m * N + n;
-        float p = bias[o];
-        g += bscale * p;
-        if (rs.world > 0) {
-            const int owner = n / rs.rows;  // M == 1: o == n
-            atomicAdd(rs.bias[owner] + (n - owner * rs.rows), g);
-        } else if (grad_bias) {
-            grad_bias[o] = g;
-        } else {
-            float mu = bias_mu[o], nu = bias_nu[o];
-            adam_update(p, mu, nu, g, a);
-            bias[o] = p; bias_mu[o] = mu; bias_nu[o] = nu;
-        }
-    }
+    finalize_work(f, blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), gridDim.x * (blockDim.x >> 5));
 }
 
 // ||b||_2 per member (sae_ensemble.py:64), one block per member
@@ -301,6 +241,16 @@ RsFinal make_rs_final(const ScStepArgs& a) {
     for (int r = 0; r < a.rs_world; ++r) { f.bias[r] = a.rs_grad_bias[r]; f.losses[r] = a.rs_losses[r]; }
     return f;
 }
+FinalizeArgs make_finalize(const ScStepArgs& a, const float* l1_part, int n_l1, const float* mse_part, int n_mse,
+                           const float* db_part, int tiles_b, const float* bnorm, int Bn, const AdamConst& ad, float db_scale) {
+    FinalizeArgs f{};
+    f.l1_part = l1_part; f.n_l1 = n_l1; f.mse_part = mse_part; f.n_mse = n_mse; f.db_part = db_part; f.tiles_b = tiles_b;
+    f.bias = a.bias; f.bias_mu = a.bias_mu; f.bias_nu = a.bias_nu; f.l1_alpha = a.l1_alpha; f.bias_decay = a.bias_decay;
+    f.out_losses = a.out_losses; f.M = a.M; f.B = Bn; f.d = a.d; f.N = a.N; f.a = ad;
+    f.grad_bias = (a.grad_enc != nullptr && a.rs_world == 0) ? a.grad_bias : nullptr;
+    f.bnorm = bnorm; f.db_scale = db_scale; f.rs = make_rs_final(a);
+    return f;
+}
 
 int sae_step_f16_impl(const ScStepArgs& a);
 
@@ -348,6 +298,8 @@ static int sae_step_impl(const ScStepArgs& a) {
         else launch_k(prep_params_kernel, dim3(grid), dim3(256), 0, st, a.enc, w.enc_r, a.dec, w.D_r, w.inv_norm, N, d, 1);
         SC_CUDA(cudaGetLastError(), "prep launch");
     }
+    launch_k(bias_norm_kernel, dim3(M), dim3(256), 0, st, a.bias, N, w.bnorm);  // ||b|| of the pre-update bias
+    SC_CUDA(cudaGetLastError(), "bias_norm launch");
     prof_mark(st, "prep_params");
     // 3. G1: c = relu(x W_e^T + b)                                  [B x N], K = d
     {
@@ -389,6 +341,8 @@ static int sae_step_impl(const ScStepArgs& a) {
             return 0;
         };
         SC_TRY(fill_rs(e, a));
+        e.fin = make_finalize(a, w.l1_part, w.n_l1, w.mse_part, w.n_mse, w.db_part, w.tiles_b, w.bnorm, Bn, ad, 1.0f);
+        e.fin_on = 1;
         if (!a.tied) {
             // one launch, two independent problems: dW_e = dz^T x (plain) and dW_d = c^T R (projected)
             Seg s45[2] = {{mnmajor(w.dz, N, B, M, BN_), mnmajor(w.x_r, d, B, xg, Bd)},
@@ -404,15 +358,7 @@ static int sae_step_impl(const ScStepArgs& a) {
             SC_TRY((run_gemm<true, true, EpiAdam>(N, d, M, s, 2, e, st)));
         }
     }
-    prof_mark(st, "G45_dW_adam");
-    // 8. loss scalars + bias Adam
-    launch_k(bias_norm_kernel, dim3(M), dim3(256), 0, st, a.bias, N, w.bnorm);
-    launch_k(finalize_kernel, dim3(dim3(ceil_div(N, 256), M)), dim3(256), 0, st, w.l1_part, w.n_l1, w.mse_part, w.n_mse, w.db_part, w.tiles_b,
-                                                             a.bias, a.bias_mu, a.bias_nu, a.l1_alpha, a.bias_decay,
-                                                             a.out_losses, M, Bn, d, N, a.tied, ad,
-                                                             grad_mode ? a.grad_bias : nullptr, w.bnorm, 1.0f, make_rs_final(a));
-    SC_CUDA(cudaGetLastError(), "finalize launch");
-    prof_mark(st, "finalize");
+    prof_mark(st, "G45_dW_adam");  // includes the finalize work (loss scalars + bias Adam) on the idle warps
     return 0;
 }
 

@@ -1,5 +1,5 @@
-// fp16-operand mode of sc_sae_step (ScStepArgs.operand_format == 1): six launches (prologue, G1, G2, G3, G4+G5,
-// finalize), GEMM operands
+// fp16-operand mode of sc_sae_step (ScStepArgs.operand_format == 1): five launches (prologue, G1, G2, G3,
+// G4+G5 with the finalize work on its idle warps), GEMM operands
 // and the intermediate tensors c / r / dz in fp16 (see sae_epilogues_h.cuh for the scaling), master
 // weights, Adam state, accumulators and all loss arithmetic in fp32.  Needs the CTA-pair kernel, d and N
 // multiples of 64 and >= 128, B > 64 (sc_sae_step_f16_supported); other shapes use the TF32 mode.
@@ -253,6 +253,8 @@ int sae_step_f16_impl(const ScStepArgs& a) {
             return 0;
         };
         SC_TRY(fill_rs(e, a));
+        e.fin = make_finalize(a, w.l1_part, w.n_l1, w.mse_part, w.n_mse, w.db_part, w.tiles_b, w.bnorm, Bn, ad, sc_);
+        e.fin_on = 1;
         if (!a.tied) {
             Seg s45[2] = {{mnmajor_h(w.dz_h, N, B, M, BN_), mnmajor_h(w.x_h, d, B, xg, Bd)},
                           {mnmajor_h(c_h, N, B, M, BN_), mnmajor_h(w.r_h, d, B, M, Bd)}};
@@ -267,13 +269,7 @@ int sae_step_f16_impl(const ScStepArgs& a) {
             SC_TRY((run_gemm<true, true, EpiAdam, true>(N, d, M, s, 2, e, st)));
         }
     }
-    prof_mark(st, "G45_dW_adam");
-    launch_k(finalize_kernel, dim3(dim3(ceil_div(N, 256), M)), dim3(256), 0, st, w.l1_part, w.n_l1, w.mse_part, w.n_mse, w.db_part, w.tiles_b,
-                                                             a.bias, a.bias_mu, a.bias_nu, a.l1_alpha, a.bias_decay,
-                                                             a.out_losses, M, Bn, d, N, a.tied, ad,
-                                                             grad_mode ? a.grad_bias : nullptr, w.bnorm, sc_, make_rs_final(a));
-    SC_CUDA(cudaGetLastError(), "finalize launch");
-    prof_mark(st, "finalize");
+    prof_mark(st, "G45_dW_adam");  // includes the finalize work (loss scalars + bias Adam) on the idle warps
     if (a.out_c) {  // caller wants the fp32 aux tensor as well
         launch_k(half_to_float_kernel, dim3(grid1d(M * BN_ / 4)), dim3(256), 0, st, reinterpret_cast<const uint2*>(c_h),
                                                                reinterpret_cast<float4*>(a.out_c), M * BN_ / 4);

@@ -337,6 +337,30 @@ def run_ours(args):
         "kernels": per_kernel, "kernel_ms": kernel_ms,
     }
 
+    # the same step at larger batches (the Adam traffic of the weight-gradient kernel is per step, not per row, so
+    # tensor-core utilisation rises with the batch): short CUDA-event runs, reported beside the headline batch
+    by_batch = {str(B): {"ms_per_step": ms_step, "member_act_per_s": value, "step_tflops": roofline["step_tflops"],
+                         "frac_of_tensor_peak": roofline["step_frac_of_tensor_peak"]}}
+    if world == 1:
+        for b2 in (4096, 8192):
+            if b2 <= B or b2 * 4 > chunk.shape[0]:
+                continue
+            n2 = chunk.shape[0] // b2
+            for i in range(10):
+                ens.step_batch(chunk[(i % n2) * b2:(i % n2 + 1) * b2])
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for i in range(100):
+                ens.step_batch(chunk[(i % n2) * b2:(i % n2 + 1) * b2])
+            e1.record()
+            torch.cuda.synchronize()
+            ms2 = e0.elapsed_time(e1) / 100
+            tf2 = 10.0 * b2 * N_FEATS * D_ACT * M / (ms2 * 1e-3) / 1e12
+            by_batch[str(b2)] = {"ms_per_step": ms2, "member_act_per_s": b2 * M / (ms2 * 1e-3), "step_tflops": tf2,
+                                 "frac_of_tensor_peak": tf2 / tensor_peak}
+    roofline["by_batch"] = by_batch
+
     threads = os.cpu_count() or 1
     cpu_b = min(B, 512)
     cpu_val, cpu_sec = cpu_port_steps(cpu_b, 3, 1, threads)

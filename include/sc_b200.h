@@ -121,6 +121,8 @@ typedef struct {
     void* stream;
     int32_t operand_format; /* 0: TF32 operands; 1: fp16 operands (same 11-bit significand, twice the MMA rate);
                                needs sc_infer_f16_supported(B, d, N, transposed = statistics requested) */
+    void* out_c_half;       /* [G,B,N] fp16 codes or NULL (operand_format 1, no statistics): the form sc_decode's c_half
+                               takes, so that predict / FVU never materialise fp32 codes (learned_dict.py:42-47) */
 } ScEncodeArgs;
 size_t sc_encode_workspace_bytes(int32_t G, int32_t B, int32_t d, int32_t N, int32_t x_per_group);
 int sc_encode(const ScEncodeArgs* args);
@@ -141,6 +143,7 @@ typedef struct {
     size_t workspace_bytes;
     void* stream;
     int32_t operand_format; /* as in ScEncodeArgs; the codes are converted to fp16 (|c| <= 65504) */
+    const void* c_half;     /* [G,B,N] fp16 codes from sc_encode's out_c_half, used instead of c (operand_format 1) */
 } ScDecodeArgs;
 size_t sc_decode_workspace_bytes(int32_t G, int32_t B, int32_t d, int32_t N);
 /* 1 when sc_encode / sc_decode can run with fp16 operands for this shape (d, N multiples of 64 and >= 128;

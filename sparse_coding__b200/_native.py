@@ -63,7 +63,7 @@ class ScEncodeArgs(C.Structure):
         ("x", C.c_void_p), ("W", C.c_void_p), ("bias", C.c_void_p),
         ("out_c", C.c_void_p), ("out_nonzero", C.c_void_p), ("out_moments", C.c_void_p),
         ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t), ("stream", C.c_void_p),
-        ("operand_format", C.c_int32),
+        ("operand_format", C.c_int32), ("out_c_half", C.c_void_p),
     ]
 
 
@@ -74,7 +74,7 @@ class ScDecodeArgs(C.Structure):
         ("c", C.c_void_p), ("Wd", C.c_void_p), ("target", C.c_void_p),
         ("out_x_hat", C.c_void_p), ("out_sq_err", C.c_void_p),
         ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t), ("stream", C.c_void_p),
-        ("operand_format", C.c_int32),
+        ("operand_format", C.c_int32), ("c_half", C.c_void_p),
     ]
 
 

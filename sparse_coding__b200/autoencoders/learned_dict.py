@@ -33,9 +33,11 @@ def _operand_format():
     return os.environ.get("SC_B200_OPERANDS", "auto")
 
 
-def _encode_native(batch, encoder, bias, want_counts=False, want_moments=False, want_c=True):
+def _encode_native(batch, encoder, bias, want_counts=False, want_moments=False, want_c=True, want_half=False):
     """c = relu(batch @ encoder^T + bias) (learned_dict.py:127-131).  encoder may be [N,d] or a
-    stack [G,N,d]; optional per-feature statistics come from the same GEMM's epilogue."""
+    stack [G,N,d]; optional per-feature statistics come from the same GEMM's epilogue.
+    want_half: return the codes as fp16 [G,B,N] (None when the shape cannot run with fp16 operands) - the form
+    _decode_native(code_half=...) takes, so predict / FVU never write fp32 codes."""
     L = nat.lib()
     x = _prep(batch, "batch")
     W = _prep(encoder, "encoder")
@@ -54,12 +56,19 @@ def _encode_native(batch, encoder, bias, want_counts=False, want_moments=False, 
     need = L.sc_encode_workspace_bytes(G, B, d, N, int(per_group))
     ws_ptr, ws_bytes = _ws.aligned(need, dev)
     f16 = _operand_format() != "tf32" and bool(L.sc_infer_f16_supported(B, d, N, int(nz is not None)))
+    c_half = None
+    if want_half:
+        if not f16 or nz is not None:
+            return None, {}
+        c_half = torch.empty((G, B, N), dtype=torch.float16, device=dev)
     args = nat.ScEncodeArgs(G=G, B=B, d=d, N=N, x_per_group=int(per_group), x=nat.ptr(x), W=nat.ptr(W), bias=nat.ptr(b),
                             out_c=nat.ptr(c), out_nonzero=nat.ptr(nz), out_moments=nat.ptr(mom),
                             workspace=ws_ptr, workspace_bytes=ws_bytes, stream=nat.stream_ptr(dev),
-                            operand_format=int(f16))
+                            operand_format=int(f16), out_c_half=nat.ptr(c_half))
     with torch.cuda.device(dev):
         nat.check(L.sc_encode(C.byref(args)), "sc_encode")
+    if want_half:
+        return c_half, {}
     stats = {}
     if nz is not None:
         stats["nonzero"] = nz if stacked else nz[0]
@@ -71,11 +80,12 @@ def _encode_native(batch, encoder, bias, want_counts=False, want_moments=False, 
     return c, stats
 
 
-def _decode_native(code, decoder, normalise=True, target=None, want_x_hat=True):
+def _decode_native(code, decoder, normalise=True, target=None, want_x_hat=True, code_half=None):
     """x_hat = code @ rownorm(decoder) (learned_dict.py:29-32); with `target` also
-    sum((x_hat - target)^2).  Returns (x_hat or None, sq_err tensor or None)."""
+    sum((x_hat - target)^2).  Returns (x_hat or None, sq_err tensor or None).  code_half: fp16 codes [G,B,N] from
+    _encode_native(want_half=True), used instead of `code`."""
     L = nat.lib()
-    c = _prep(code, "code")
+    c = code_half if code_half is not None else _prep(code, "code")
     W = _prep(decoder, "decoder")
     stacked = W.dim() == 3
     G = W.shape[0] if stacked else 1
@@ -89,12 +99,13 @@ def _decode_native(code, decoder, normalise=True, target=None, want_x_hat=True):
     sq = torch.empty((G,), dtype=torch.float32, device=dev) if tgt is not None else None
     need = L.sc_decode_workspace_bytes(G, B, d, N)
     ws_ptr, ws_bytes = _ws.aligned(need, dev)
-    f16 = _operand_format() != "tf32" and bool(L.sc_infer_f16_supported(B, d, N, 0))
+    f16 = code_half is not None or (_operand_format() != "tf32" and bool(L.sc_infer_f16_supported(B, d, N, 0)))
     args = nat.ScDecodeArgs(G=G, B=B, d=d, N=N, normalise=int(normalise),
                             target_per_group=int(tgt is not None and tgt.dim() == 3),
-                            c=nat.ptr(c), Wd=nat.ptr(W), target=nat.ptr(tgt), out_x_hat=nat.ptr(x_hat),
-                            out_sq_err=nat.ptr(sq), workspace=ws_ptr, workspace_bytes=ws_bytes,
-                            stream=nat.stream_ptr(dev), operand_format=int(f16))
+                            c=None if code_half is not None else nat.ptr(c), Wd=nat.ptr(W), target=nat.ptr(tgt),
+                            out_x_hat=nat.ptr(x_hat), out_sq_err=nat.ptr(sq), workspace=ws_ptr, workspace_bytes=ws_bytes,
+                            stream=nat.stream_ptr(dev), operand_format=int(f16),
+                            c_half=nat.ptr(code_half) if code_half is not None else None)
     with torch.cuda.device(dev):
         nat.check(L.sc_decode(C.byref(args)), "sc_decode")
     if not stacked:
@@ -145,9 +156,20 @@ class LearnedDict(ABC):
     def uncenter(self, batch):
         return batch
 
+    def _encode_operands(self):
+        """(encoder matrix as encode() uses it, bias) for dictionaries whose encode is relu(x W^T + b), else None."""
+        return None
+
     def predict(self, batch):
-        """learned_dict.py:42-47."""
+        """learned_dict.py:42-47.  When encode is the plain affine + ReLU form the codes go from the encode kernel to
+        the decode kernel as fp16 (the decode GEMM's operand format anyway) and are never written in fp32."""
         batch_centered = self.center(batch)
+        eb = self._encode_operands()
+        if eb is not None:
+            c_half, _ = _encode_native(batch_centered, eb[0], eb[1], want_c=False, want_half=True)
+            if c_half is not None:
+                x_hat = _decode_native(None, self._dictionary_source(), normalise=True, code_half=c_half)[0]
+                return self.uncenter(x_hat)
         c = self.encode(batch_centered)
         x_hat_centered = self.decode(c)
         return self.uncenter(x_hat_centered)
@@ -170,6 +192,9 @@ class UntiedSAE(LearnedDict):
 
     def _dictionary_source(self):
         return self.decoder
+
+    def _encode_operands(self):
+        return self.encoder, self.encoder_bias
 
     def to_device(self, device):
         self.encoder = self.encoder.to(device)
@@ -242,10 +267,14 @@ class TiedSAE(LearnedDict):
         self.center_rot = self.center_rot.to(device)
         self.center_scale = self.center_scale.to(device)
 
+    def _encode_operands(self):
+        enc = _row_normalise_native(self.encoder) if self.norm_encoder else self.encoder
+        return enc, self.encoder_bias
+
     def encode(self, batch):
         """learned_dict.py:186-196."""
-        enc = _row_normalise_native(self.encoder) if self.norm_encoder else self.encoder
-        return _encode_native(batch, enc, self.encoder_bias)[0]
+        enc, bias = self._encode_operands()
+        return _encode_native(batch, enc, bias)[0]
 
 
 # pickles must resolve under the reference's module path (big_sweep.py:424 torch.save of these objects)

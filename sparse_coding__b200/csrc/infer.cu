@@ -3,7 +3,7 @@
 // into their epilogues, plus the raw GEMM hook used by the tests.
 #include "../../include/sc_b200.h"
 #include "host_common.cuh"
-#include "sae_epilogues.cuh"
+#include "sae_epilogues_h.cuh"
 
 namespace sc {
 
@@ -170,7 +170,9 @@ static int encode_impl(const ScEncodeArgs& a) {
     if (G <= 0 || B <= 0 || d <= 0 || N <= 0) return fail(-1, "G, B, d, N must be positive");
     if ((d & 3) || (N & 3)) return fail(-1, "d and N must be multiples of 4 (got d=%d N=%d)", d, N);
     if (!a.x || !a.W || !a.workspace) return fail(-1, "x / W / workspace is NULL");
-    if (!a.out_c && !a.out_nonzero && !a.out_moments) return fail(-1, "no output requested");
+    if (!a.out_c && !a.out_nonzero && !a.out_moments && !a.out_c_half) return fail(-1, "no output requested");
+    if (a.out_c_half && (a.operand_format != 1 || a.out_nonzero || a.out_moments))
+        return fail(-1, "out_c_half needs operand_format 1 and no statistics outputs");
     const size_t need = sc_encode_workspace_bytes(G, B, d, N, a.x_per_group);
     if (a.workspace_bytes < need) return fail(-1, "workspace too small: %zu given, %zu needed", a.workspace_bytes, need);
     cudaStream_t st = static_cast<cudaStream_t>(a.stream);
@@ -192,6 +194,16 @@ static int encode_impl(const ScEncodeArgs& a) {
             return run_gemm<false, false, EpiEncodeT, true>(N, B, G, &s, 1, ep, st);
         }
         Seg s{kmajor_h(x_h, B, d, xg, Bd), kmajor_h(W_h, N, d, G, Nd)};
+        if (a.out_c_half) {  // fp16 codes for sc_decode (predict / FVU): the train step's encode epilogue
+            if (reinterpret_cast<uintptr_t>(a.out_c_half) & 15) return fail(-1, "out_c_half is not 16-byte aligned");
+            EpiEncodeH::Params eh{};
+            const char* err = nullptr;
+            const int rc = make_io_map_h(&eh.c_map, a.out_c_half, B, N, G, BN_, &err);
+            if (rc != 0) return fail(rc, "%s", err ? err : "io tensor map creation failed");
+            eh.bias = a.bias; eh.l1_part = nullptr; eh.dict_size = nullptr;
+            SC_TRY((run_gemm<false, false, EpiEncodeH, true>(B, N, G, &s, 1, eh, st)));
+            if (!a.out_c) return 0;
+        }
         EpiEncode::Params ep{};
         const char* err = nullptr;
         const int rc = make_io_map(&ep.c_map, a.out_c, B, N, G, BN_, &err);
@@ -225,7 +237,8 @@ static int decode_impl(const ScDecodeArgs& a) {
     const int G = a.G, B = a.B, d = a.d, N = a.N;
     if (G <= 0 || B <= 0 || d <= 0 || N <= 0) return fail(-1, "G, B, d, N must be positive");
     if ((d & 3) || (N & 3)) return fail(-1, "d and N must be multiples of 4 (got d=%d N=%d)", d, N);
-    if (!a.c || !a.Wd || !a.workspace) return fail(-1, "c / Wd / workspace is NULL");
+    if ((!a.c && !a.c_half) || !a.Wd || !a.workspace) return fail(-1, "c / Wd / workspace is NULL");
+    if (a.c_half && a.operand_format != 1) return fail(-1, "c_half needs operand_format 1");
     if (a.out_sq_err && !a.target) return fail(-1, "out_sq_err needs a target");
     const size_t need = sc_decode_workspace_bytes(G, B, d, N);
     if (a.workspace_bytes < need) return fail(-1, "workspace too small: %zu given, %zu needed", a.workspace_bytes, need);
@@ -239,7 +252,8 @@ static int decode_impl(const ScDecodeArgs& a) {
         __half* c_h = reinterpret_cast<__half*>(cv.floats(((size_t)G * BN_ + 1) / 2));
         __half* D_h = reinterpret_cast<__half*>(cv.floats(((size_t)G * Nd + 1) / 2));
         float* part = cv.floats((size_t)G * n_part);
-        SC_TRY(to_half(a.c, c_h, G * BN_, st));
+        if (a.c_half) c_h = const_cast<__half*>(static_cast<const __half*>(a.c_half));
+        else SC_TRY(to_half(a.c, c_h, G * BN_, st));
         if (a.normalise) {
             launch_k(prep_params_h_kernel, dim3(ceil_div(N, 8), G), dim3(256), 0, st, nullptr, nullptr, a.Wd, D_h, nullptr, N, d);
             SC_CUDA(cudaGetLastError(), "prep launch");

@@ -32,7 +32,7 @@ struct EpiEncodeH {
     SC_DEVICE void prefetch(int co) {
         const int col = c.col0 + co;
         const int ncols = c.N - col;
-        if (ncols > 0) {
+        if (ncols > 0 && p.bias) {
             load_row32(p.bias + (long long)c.g * c.N + col, nxt, ncols);
         } else {
 #pragma unroll
@@ -72,6 +72,7 @@ struct EpiEncodeH {
         io_commit();
     }
     SC_DEVICE void finish() {
+        if (!p.l1_part) return;  // inference use: codes only
         const float s = warp_sum((sum + sum1) + (sum2 + sum3));
         if ((threadIdx.x & 31) == 0) {
             const int tiles = c.tiles_m * c.tiles_n;

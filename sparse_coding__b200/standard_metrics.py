@@ -62,8 +62,13 @@ def fraction_variance_unexplained(model: LearnedDict, batch):
     eb = _encoder_and_bias(model)
     identity = not isinstance(model, TiedSAE) or model._identity_centering()
     if eb is not None and identity:
-        c, _ = _encode_native(batch, eb[0], eb[1])
-        _, sq = _decode_native(c, model._dictionary_source(), normalise=True, target=batch, want_x_hat=False)
+        c_half, _ = _encode_native(batch, eb[0], eb[1], want_c=False, want_half=True)  # fp16 codes, never in fp32
+        if c_half is not None:
+            _, sq = _decode_native(None, model._dictionary_source(), normalise=True, target=batch, want_x_hat=False,
+                                   code_half=c_half)
+        else:
+            c, _ = _encode_native(batch, eb[0], eb[1])
+            _, sq = _decode_native(c, model._dictionary_source(), normalise=True, target=batch, want_x_hat=False)
         return sq / total_variance_sum(batch)
     x_hat = model.predict(batch)
     residuals = (batch - x_hat).pow(2).mean()

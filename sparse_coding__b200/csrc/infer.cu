@@ -48,6 +48,11 @@ struct EpiEncodeT {
         const int col = c.col0 + co;
         const int nb = c.N - col;
         float* cp = p.c ? p.c + c.g * p.c_gstride + (long long)col * p.feats + c.row : nullptr;
+        if (!cp && !p.moments && nb >= 32) {  // counts only (mean L0, dead features): the common metric call
+#pragma unroll
+            for (int j = 0; j < 32; ++j) cnt += (v[j] + bn > 0.f) ? 1.f : 0.f;
+            return;
+        }
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
             if (j < nb) {

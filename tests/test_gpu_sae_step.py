@@ -423,3 +423,58 @@ def test_fused_reduce_scatter_data_parallel_equals_full_batch_step(kind, fmt, wo
             assert err < 1e-4, (step, k, err)
         for dp in ranks:
             assert float(dp.acc.abs().max()) == 0.0   # accumulation buffers are left zeroed for the next step
+
+
+@pytest.mark.parametrize("fmt,shape", [(0, (3, 130, 100, 36)), (0, (2, 515, 256, 512)), (1, (3, 200, 128, 192)), (1, (2, 515, 256, 576))])
+def test_step_writes_nothing_outside_its_buffers(fmt, shape):
+    """Ragged shapes through the C ABI with guard regions: every tensor the library writes (parameters, moments,
+    codes, losses, workspace) sits inside a larger allocation filled with a sentinel; after three steps every guard
+    byte must still be the sentinel (the tile stores clip, the row-wise stores are bounds-checked)."""
+    import ctypes as C
+    from sparse_coding__b200 import _native as nat
+    L = nat.lib()
+    M, B, d, N = shape
+    G = 4096  # guard elements on both sides
+    dev = "cuda"
+    torch.manual_seed(5)
+    bufs = {}
+
+    def guarded(name, n, dtype=torch.float32, init=None):
+        t = torch.full((n + 2 * G,), 7.25, dtype=dtype, device=dev)
+        inner = t[G:G + n]
+        if init is not None:
+            inner.copy_(init.reshape(-1))
+        else:
+            inner.zero_()
+        bufs[name] = t
+        return inner
+
+    enc = guarded("enc", M * N * d, init=0.05 * torch.randn(M, N, d))
+    dec = guarded("dec", M * N * d, init=0.05 * torch.randn(M, N, d))
+    bias = guarded("bias", M * N, init=0.01 * torch.randn(M, N))
+    st = {k: guarded(k, M * N * d) for k in ("enc_mu", "enc_nu", "dec_mu", "dec_nu")}
+    sb = {k: guarded(k, M * N) for k in ("bias_mu", "bias_nu")}
+    losses = guarded("losses", 4 * M)
+    c32 = guarded("c32", M * B * N)
+    c16 = guarded("c16", M * B * N, dtype=torch.float16)
+    need = L.sc_sae_step_workspace_bytes(M, B, d, N, 0, 0)
+    ws = torch.full((need + 2 * 1024 * 64,), 0x5A, dtype=torch.uint8, device=dev)
+    off = (-(ws.data_ptr() + 1024 * 32)) % 1024 + 1024 * 32
+    x = torch.randn(B, d, device=dev)
+    l1 = torch.full((M,), 1e-3, device=dev)
+    bd = torch.zeros(M, device=dev)
+    adam = nat.ScAdam(1e-3, 0.9, 0.999, 1e-8, 0.0, 0.1, 0.001)
+    p = nat.ptr
+    for _ in range(3):
+        a = nat.ScStepArgs(M=M, B=B, d=d, N=N, tied=0, x_per_member=0, x=p(x), enc=p(enc), enc_mu=p(st["enc_mu"]),
+                           enc_nu=p(st["enc_nu"]), bias=p(bias), bias_mu=p(sb["bias_mu"]), bias_nu=p(sb["bias_nu"]),
+                           dec=p(dec), dec_mu=p(st["dec_mu"]), dec_nu=p(st["dec_nu"]), l1_alpha=p(l1), bias_decay=p(bd),
+                           adam=adam, out_losses=p(losses), out_c=p(c32) if fmt == 0 else None,
+                           workspace=C.c_void_p(ws.data_ptr() + off), workspace_bytes=need,
+                           stream=nat.stream_ptr(torch.device(dev)), operand_format=fmt, out_c_half=p(c16) if fmt == 1 else None)
+        nat.check(L.sc_sae_step(C.byref(a)), "sc_sae_step")
+    torch.cuda.synchronize()
+    assert torch.isfinite(losses).all() and float(losses[:M].min()) > 0
+    for name, t in bufs.items():
+        assert bool((t[:G] == 7.25).all()) and bool((t[-G:] == 7.25).all()), f"guard of {name} overwritten"
+    assert bool((ws[:off] == 0x5A).all()) and bool((ws[off + need:] == 0x5A).all()), "workspace guard overwritten"

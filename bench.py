@@ -379,8 +379,8 @@ def run_ours(args):
                                 "working set per step > 1 GB"},
         "activations_per_sec": value / (M * world) ,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": B * D_ACT * 4, "d2h_bytes_per_step": M * 4},
-        # our kernels per step: one launch mark each in the library (fp16 mode: prologue, G1, G2, G3, G4+G5,
-        # finalize = 6); the TF32 mode's last mark covers two launches (bias norm + finalize)
+        # our kernels per step: one launch mark each in the library (fp16 mode: prologue, G1, G2, G3, G4+G5 = 5);
+        # in TF32 mode one mark covers two launches (operand preparation + bias norm)
         "gpu_launches": (len(marks) // prof_steps + (0 if fmt == "f16" else 1)) * args.steps,
         "roofline": roofline, "cpu_baseline": cpu_baseline, "clocks": clocks.summary(),
     }

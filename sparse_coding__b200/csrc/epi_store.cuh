@@ -31,20 +31,6 @@ SC_DEVICE void load_row32(const float* src, float (&v)[32], int ncols) {
     }
 }
 
-// same, bypassing L1 (ld.global.cg)
-SC_DEVICE void load_row32_cg(const float* src, float (&v)[32], int ncols) {
-    if (ncols >= 32 && (reinterpret_cast<uintptr_t>(src) & 15) == 0) {
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            const float4 t = __ldcg(reinterpret_cast<const float4*>(src) + j);
-            v[4 * j] = t.x; v[4 * j + 1] = t.y; v[4 * j + 2] = t.z; v[4 * j + 3] = t.w;
-        }
-    } else {
-#pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] = (j < ncols) ? __ldcg(src + j) : 0.f;
-    }
-}
-
 struct EpiStore {
     struct Params {
         float* C;

@@ -1,7 +1,8 @@
 // sc_sae_step: one FunctionalEnsemble.step_batch (reference autoencoders/ensemble.py:175-193) for
-// the SAE / Fista / TiedSAE signatures, as eight launches on the caller's stream:
-//   round x -> prep params -> G1 encode -> G2 decode+MSE -> G3 dL/dz -> G4/G5 dW with fused Adam
-//   -> finalize (loss scalars + bias Adam).
+// the SAE / Fista / TiedSAE signatures, TF32-operand mode: seven launches on the caller's stream:
+//   round x -> prep params -> ||b|| -> G1 encode -> G2 decode+MSE -> G3 dL/dz -> G4/G5 dW with fused Adam
+//   (the finalize work - loss scalars + bias Adam - runs on that launch's idle warps).
+// The default fp16-operand mode is sae_step_h.cu (five launches).
 // Five tcgen05 TF32 GEMMs per member carry 10 B N d flops; everything else is fused epilogue work.
 #include "../../include/sc_b200.h"
 #include "host_common.cuh"

@@ -75,7 +75,10 @@ struct EpiFistaRes {
 // the update itself); the three [32 x 32] tiles y_hi, y_lo, a come in and go out through the warp's
 // staging tiles by TMA, in place, so the global traffic is fully coalesced.
 struct EpiFistaStep {
-    static constexpr int kIoBufs = 3;
+    // HBM-heavy epilogue (six 4 KB tiles per chunk): four epilogue warps with two staging sets each, the next
+    // chunk's y_hi / y_lo / a_prev tiles load while the current chunk is processed and stored (as in EpiAdam).
+    static constexpr int kHalves = 1;
+    static constexpr int kIoBufs = 6;
     struct alignas(64) Params {
         CUtensorMap yhi_map, ylo_map, a_map;  // io maps of [B][N]
         const float* eta;                      // device scalar
@@ -89,25 +92,31 @@ struct EpiFistaStep {
         eta = *p.eta;
         thr = eta * p.l1;
     }
-    SC_DEVICE void prefetch(int co) {
-        io_wait_stores_read();
-        if ((threadIdx.x & 31) == 0) {
-            const int col = c.col0 + co, row0 = c.row;
-            io_expect(io, 3 * kIoTileBytes);
-            tma_load_3d(&p.yhi_map, io.bar, io.buf, col, row0, 0);
-            tma_load_3d(&p.ylo_map, io.bar, io.buf + kIoTileBytes, col, row0, 0);
-            tma_load_3d(&p.a_map, io.bar, io.buf + 2 * kIoTileBytes, col, row0, 0);
-        }
+    SC_DEVICE void request(int set, int row0, int col) const {  // lane 0
+        uint8_t* b = io.buf + set * (3 * kIoTileBytes);
+        io_expect(io, 3 * kIoTileBytes, set);
+        tma_load_3d(&p.yhi_map, io.bar + set, b, col, row0, 0);
+        tma_load_3d(&p.ylo_map, io.bar + set, b + kIoTileBytes, col, row0, 0);
+        tma_load_3d(&p.a_map, io.bar + set, b + 2 * kIoTileBytes, col, row0, 0);
+    }
+    SC_DEVICE void prefetch(int co) {  // only the warp's very first chunk; later ones are requested one chunk ahead
+        if (c.first && (threadIdx.x & 31) == 0) request((co >> 5) & 1, c.row, c.col0 + co);
     }
     SC_DEVICE void chunk(int co, float (&v)[32], int next_co) {
         const int lane = threadIdx.x & 31;
+        const int set = (co >> 5) & 1;
         const int col = c.col0 + co, row0 = c.row - lane;
-        uint8_t* b = io.buf;
-        io_wait_loads(io);
+        uint8_t* b = io.buf + set * (3 * kIoTileBytes);
+        io_wait_loads(io, set);
         float yh[32], yl[32], av[32];
         io_read_row(b, lane, yh);
         io_read_row(b + kIoTileBytes, lane, yl);
         io_read_row(b + 2 * kIoTileBytes, lane, av);
+        io_wait_stores_read();  // the other set's store (one chunk ago) has read it
+        if (lane == 0) {
+            if (next_co >= 0) request(set ^ 1, row0, c.col0 + next_co);
+            else if (c.next_g >= 0) request(set ^ 1, c.next_row0, c.next_col0);
+        }
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
             const float yn = (yh[j] + yl[j]) + eta * v[j];   // ahat_y.add(eta * Res D^T)
@@ -128,7 +137,6 @@ struct EpiFistaStep {
             tma_store_3d(&p.a_map, b + 2 * kIoTileBytes, col, row0, 0);
         }
         io_commit();
-        if (next_co >= 0) prefetch(next_co);
     }
     SC_DEVICE void finish() {}
 };

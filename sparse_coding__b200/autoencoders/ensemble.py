@@ -285,12 +285,15 @@ class FunctionalEnsemble:
         """ensemble.py:175-193.  Returns (loss_dict of [M] tensors, {"c": [M,B,N]})."""
         return self._run(minibatches, expand_dims, grad_only=False)
 
-    def compute_grads(self, minibatches, expand_dims=True, batch_total=0, bias_decay=None):
+    def compute_grads(self, minibatches, expand_dims=True, batch_total=0, bias_decay=None, out=None):
         """Gradient-only twin of step_batch: what vmap(grad(sig.loss)) returns at ensemble.py:180,
         without the Adam update.  `batch_total` (> 0) replaces the local batch size in the loss
         normalisation (data-parallel shards); `bias_decay` overrides buffers["bias_decay"].
+        `out`: optional dict of preallocated contiguous tensors shaped like .params to receive the gradients (e.g.
+        views into one flat buffer that is all-reduced in place).
         Returns (grads dict like .params, loss_dict, {"c": ...})."""
-        return self._run(minibatches, expand_dims, grad_only=True, batch_total=batch_total, bias_decay=bias_decay)
+        return self._run(minibatches, expand_dims, grad_only=True, batch_total=batch_total, bias_decay=bias_decay,
+                         grad_out=out)
 
     def adam_constants(self, advance=True):
         """(ScAdam for this step)."""
@@ -328,7 +331,7 @@ class FunctionalEnsemble:
                                    reduce_scatter=reduce_scatter)
         return losses, aux
 
-    def _run(self, minibatches, expand_dims, grad_only, batch_total=0, bias_decay=None, reduce_scatter=None):
+    def _run(self, minibatches, expand_dims, grad_only, batch_total=0, bias_decay=None, reduce_scatter=None, grad_out=None):
         L = nat.lib()
         M = self.n_models
         x = minibatches
@@ -373,9 +376,15 @@ class FunctionalEnsemble:
         adam = self.adam_constants(advance=not grad_only)
         grads = None
         if grad_only and reduce_scatter is None:
-            grads = {"encoder": torch.empty_like(enc), "encoder_bias": torch.empty_like(bias)}
-            if not tied:
-                grads["decoder"] = torch.empty_like(dec)
+            if grad_out is not None:
+                grads = {k: grad_out[k] for k in (("encoder", "encoder_bias") if tied else ("encoder", "encoder_bias", "decoder"))}
+                for k, g in grads.items():
+                    if not (g.is_contiguous() and g.shape == self.params[k].shape and g.dtype == torch.float32 and g.is_cuda):
+                        raise ValueError(f"out[{k!r}] must be a contiguous float32 CUDA tensor of shape {tuple(self.params[k].shape)}")
+            else:
+                grads = {"encoder": torch.empty_like(enc), "encoder_bias": torch.empty_like(bias)}
+                if not tied:
+                    grads["decoder"] = torch.empty_like(dec)
 
         fmt = self.operand_format
         if fmt not in ("auto", "tf32", "f16"):

@@ -54,36 +54,56 @@ class DataParallelEnsemble:
         for t in self.engine.params.values():
             dist.broadcast(t, src=src, group=self.group)
 
-    def _flatten(self, grads: Dict[str, torch.Tensor], extra: torch.Tensor) -> torch.Tensor:
-        n = sum(g.numel() for g in grads.values()) + extra.numel()
-        ref = next(iter(grads.values()))
+    def _grad_views(self, n_extra: int):
+        """One flat buffer holding every gradient (+ n_extra loss scalars): the fused step writes into views of it,
+        so a single in-place all-reduce covers everything and nothing is copied."""
+        params = self.engine.params
+        n = sum(p.numel() for p in params.values()) + n_extra
+        ref = next(iter(params.values()))
         if self._flat is None or self._flat.numel() != n or self._flat.device != ref.device:
-            self._flat = torch.empty(n, dtype=ref.dtype, device=ref.device)
-        off = 0
-        for g in grads.values():
-            self._flat[off:off + g.numel()].copy_(g.reshape(-1))
-            off += g.numel()
-        self._flat[off:].copy_(extra.reshape(-1))
-        return self._flat
+            self._flat = torch.empty(n, dtype=torch.float32, device=ref.device)
+            self._views, off = {}, 0
+            for k, p in params.items():
+                self._views[k] = self._flat[off:off + p.numel()].view(p.shape)
+                off += p.numel()
+            self._extra = self._flat[off:]
+        return self._views, self._extra
 
     def step_batch(self, local_rows: torch.Tensor, expand_dims=True):
         eng, world = self.engine, self.world
-        b_local = torch.tensor([local_rows.shape[-2]], device=local_rows.device, dtype=torch.int64)
-        if world > 1:
-            dist.all_reduce(b_local, group=self.group)
-        b_total = int(b_local.item())
+        # global batch size: one small all-reduce + host read, repeated only when this rank's row count changes
+        # (ranks are expected to change their row counts together, as a sharded sampler does)
+        n_local = int(local_rows.shape[-2])
+        if getattr(self, "_b_cache", (None, None))[0] != n_local:
+            b_local = torch.tensor([n_local], device=local_rows.device, dtype=torch.int64)
+            if world > 1:
+                dist.all_reduce(b_local, group=self.group)
+            self._b_cache = (n_local, int(b_local.item()))
+        b_total = self._b_cache[1]
         # the bias-decay term does not depend on the batch: give each rank 1/world of it so the sum is right
         bd = eng.buffers["bias_decay"].to(torch.float32) / world
-        grads, losses, aux = eng.compute_grads(local_rows, expand_dims=expand_dims, batch_total=b_total, bias_decay=bd)
-        parts = torch.stack([losses["l_reconstruction"], losses["l_l1"], losses["l_bias_decay"]]).to(torch.float32)
-        if world > 1:
-            flat = self._flatten(grads, parts)
-            dist.all_reduce(flat, group=self.group)
-            off = 0
-            for k, g in grads.items():
-                g.copy_(flat[off:off + g.numel()].view_as(g))
-                off += g.numel()
-            parts = flat[off:].view_as(parts).clone()
+        M = eng.params["encoder"].shape[0]
+        can_view = all(hasattr(p, "is_cuda") and p.is_cuda and p.is_contiguous() for p in eng.params.values())
+        if can_view:
+            views, extra = self._grad_views(3 * M)
+            grads, losses, aux = eng.compute_grads(local_rows, expand_dims=expand_dims, batch_total=b_total, bias_decay=bd,
+                                                   out=views)
+            parts = extra.view(3, M)
+            parts.copy_(torch.stack([losses["l_reconstruction"], losses["l_l1"], losses["l_bias_decay"]]))
+            if world > 1:
+                dist.all_reduce(self._flat, group=self.group)
+            parts = parts.clone()
+        else:  # engines without preallocated-output support (the CPU stand-ins of the gloo tests)
+            grads, losses, aux = eng.compute_grads(local_rows, expand_dims=expand_dims, batch_total=b_total, bias_decay=bd)
+            parts = torch.stack([losses["l_reconstruction"], losses["l_l1"], losses["l_bias_decay"]]).to(torch.float32)
+            if world > 1:
+                flat = torch.cat([g.reshape(-1) for g in grads.values()] + [parts.reshape(-1)])
+                dist.all_reduce(flat, group=self.group)
+                off = 0
+                for k, g in grads.items():
+                    g.copy_(flat[off:off + g.numel()].view_as(g))
+                    off += g.numel()
+                parts = flat[off:].view_as(parts).clone()
         eng.apply_grads(grads)
         out = {"loss": parts.sum(0), "l_reconstruction": parts[0], "l_l1": parts[1]}
         if "l_bias_decay" in losses and not getattr(eng, "_kind", "") == "tied":

@@ -66,6 +66,8 @@ def main():
             out["max_rel_loss_diff_vs_single_gpu_full_batch"] = worst
             out["mean_abs_param_diff"] = {k: float((ens.params[k] - ref.params[k]).abs().mean()) for k in ens.params}
             del ref
+    for s in range(3):  # warm-up (allocator, lazy module loading, NCCL channels)
+        dp.step_batch(full[lo:hi])
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()

@@ -160,3 +160,51 @@ def calc_moments_streaming(learned_dict, activations, batch_size=1000):
     skew = m3 / torch.clamp(var ** 1.5, min=1e-8)
     kurtosis = m4 / torch.clamp(var ** 2, min=1e-8)
     return times_active, mean, var, skew, kurtosis, m4
+
+
+# ---------------------------------------------------------------------------------------------
+# Max-cosine-similarity family (standard_metrics.py:268-300).  The [m, g] similarity matrix is one GEMM of
+# two row-normalised dictionaries; it runs through the encode kernel (operands rounded to nearest, fp32
+# accumulate) with a constant bias of 2 so that its ReLU never clips (|cos| <= 1), removed after the row max.
+# ---------------------------------------------------------------------------------------------
+def _max_cosine_sim(rows: torch.Tensor, against: torch.Tensor) -> torch.Tensor:
+    """max_g <rows[m], against[g]> for every m; both [*, d], used as given (callers pass unit-norm rows)."""
+    bias = torch.full((against.shape[0],), 2.0, dtype=torch.float32, device=rows.device)
+    sim, _ = _encode_native(rows, against, bias)
+    return sim.max(dim=-1).values - 2.0
+
+
+def mcs_duplicates(ground: LearnedDict, model: LearnedDict):
+    """standard_metrics.py:268-272: max cosine similarity of each model atom with all ground atoms."""
+    return _max_cosine_sim(model.get_learned_dict(), ground.get_learned_dict())
+
+
+def mmcs(model: LearnedDict, model2: LearnedDict):
+    """standard_metrics.py:274-275."""
+    return mcs_duplicates(model, model2).mean()
+
+
+def mcs_to_fixed(model: LearnedDict, truth):
+    """standard_metrics.py:277-280."""
+    return _max_cosine_sim(model.get_learned_dict(), truth)
+
+
+def mmcs_to_fixed(model: LearnedDict, truth):
+    """standard_metrics.py:282-283."""
+    return mcs_to_fixed(model, truth).mean()
+
+
+def mmcs_from_list(ld_list):
+    """standard_metrics.py:285-295: symmetric matrix of mmcs between all pairs (lower triangle computed)."""
+    n_dicts = len(ld_list)
+    mmcs_t = torch.eye(n_dicts)
+    for i in range(n_dicts):
+        for j in range(i):
+            mmcs_t[i, j] = mmcs(ld_list[i], ld_list[j])
+            mmcs_t[j, i] = mmcs_t[i, j]
+    return mmcs_t
+
+
+def representedness(features, model: LearnedDict):
+    """standard_metrics.py:297-301: mmcs the other way around."""
+    return _max_cosine_sim(features, model.get_learned_dict())

@@ -165,3 +165,37 @@ def test_fista_300_iterations_at_pythia_width():
     assert float((res.cpu().double() - res_ref).abs().max()) < 1e-4
     # size-independent property: residual is consistent with the codes
     assert float((x.cuda() - a @ D.cuda() - res).abs().max()) < 1e-4
+
+
+def test_max_cosine_similarity_family():
+    """standard_metrics.py:268-300 against plain fp32 torch, including a row whose similarities are all negative
+    (the ReLU of the encode kernel must not clip it)."""
+    import sparse_coding__b200 as sc
+    from sparse_coding__b200 import standard_metrics as sm
+    torch.manual_seed(3)
+    d, n1, n2 = 128, 384, 512
+    W1, W2 = torch.randn(n1, d, device="cuda"), torch.randn(n2, d, device="cuda")
+    W2[:, 0] = W2[:, 0].abs() + 3.0          # every atom of the second dictionary leans towards +e0 ...
+    W1[5] = 0.0
+    W1[5, 0] = -1.0                           # ... and this atom of the first one is -e0: all its cosines are negative
+    ld1 = sc.UntiedSAE(torch.randn(n1, d, device="cuda"), W1, torch.zeros(n1, device="cuda"))
+    ld2 = sc.TiedSAE(W2, torch.zeros(n2, device="cuda"), norm_encoder=True)
+    D1 = W1 / W1.norm(dim=1, keepdim=True)
+    D2 = W2 / W2.norm(dim=1, keepdim=True)
+    old = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        want = (D1 @ D2.T).max(dim=-1).values
+        want_r = (D2 @ D1.T).max(dim=-1).values
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = old
+    got = sm.mcs_duplicates(ld2, ld1)
+    assert got.shape == (n1,) and float(want[5]) < 0
+    assert float((got - want).abs().max()) < 5e-4
+    assert abs(float(sm.mmcs(ld2, ld1)) - float(want.mean())) < 1e-4      # mmcs(a, b) = mcs_duplicates(ground=a, model=b).mean()
+    assert abs(float(sm.mmcs(ld1, ld2)) - float(want_r.mean())) < 1e-4
+    assert float((sm.mcs_to_fixed(ld1, D2) - want).abs().max()) < 5e-4
+    assert abs(float(sm.mmcs_to_fixed(ld1, D2)) - float(want.mean())) < 1e-4
+    assert float((sm.representedness(D2, ld1) - want_r).abs().max()) < 5e-4
+    m = sm.mmcs_from_list([ld1, ld2])
+    assert m.shape == (2, 2) and float(m[0, 0]) == 1.0 and abs(float(m[1, 0]) - float(want.mean())) < 1e-4 and m[0, 1] == m[1, 0]

@@ -34,7 +34,10 @@ def ensemble_case(ns, kind, seed):
     torch.manual_seed(seed)
     d, N, B, steps = 32, 64, 48, 6
     l1s, bds = [1e-3, 1e-2, 3e-2], [0.0, 0.01, 0.0]
-    if kind == "tied":
+    if kind in ("masked_untied", "masked_tied"):  # mixed dictionary sizes stacked to N (sae_ensemble.py:307-442)
+        sig = ns.sae_ensemble.FunctionalMaskedTiedSAE if kind == "masked_tied" else ns.sae_ensemble.FunctionalMaskedSAE
+        models = [sig.init(d, n, N, l1) for n, l1 in zip((24, 64, 40), l1s)]
+    elif kind == "tied":
         def mk(l1, bd, i):
             if i == 0:
                 return ns.FunctionalTiedSAE.init(d, N, l1, bias_decay=bd)
@@ -116,6 +119,8 @@ def main():
     os.makedirs(OUT, exist_ok=True)
     torch.save(ensemble_case(ns, "untied", 100), os.path.join(OUT, "ensemble_untied.pt"))
     torch.save(ensemble_case(ns, "tied", 200), os.path.join(OUT, "ensemble_tied.pt"))
+    torch.save(ensemble_case(ns, "masked_untied", 500), os.path.join(OUT, "ensemble_masked_untied.pt"))
+    torch.save(ensemble_case(ns, "masked_tied", 600), os.path.join(OUT, "ensemble_masked_tied.pt"))
     torch.save(inference_case(ns, 300), os.path.join(OUT, "inference.pt"))
     torch.save(fista_case(ns, 400), os.path.join(OUT, "fista.pt"))
     for f in sorted(os.listdir(OUT)):

@@ -16,17 +16,19 @@ def load(name):
     return torch.load(os.path.join(GOLD, name), weights_only=False)
 
 
-@pytest.mark.parametrize("name", ["ensemble_untied.pt", "ensemble_tied.pt"])
+@pytest.mark.parametrize("name", ["ensemble_untied.pt", "ensemble_tied.pt", "ensemble_masked_untied.pt",
+                                  "ensemble_masked_tied.pt"])
 def test_step_batch_against_reference_fixture(name):
     import sparse_coding__b200 as sc
     g = load(name)
-    tied = g["kind"] == "tied"
+    tied = g["kind"] in ("tied", "masked_tied")
     M = g["init_params"]["encoder"].shape[0]
     models = []
     for m in range(M):
         models.append(({k: v[m].clone() for k, v in g["init_params"].items()},
                        {k: v[m].clone() for k, v in g["buffers"].items()}))
-    sig = sc.FunctionalTiedSAE if tied else sc.FunctionalSAE
+    sig = {"tied": sc.FunctionalTiedSAE, "untied": sc.FunctionalSAE, "masked_tied": sc.FunctionalMaskedTiedSAE,
+           "masked_untied": sc.FunctionalMaskedSAE}[g["kind"]]
     ens = sc.FunctionalEnsemble(models, sig, sc.torchopt_compat.adam, {"lr": g["lr"]}, device="cuda")
     B = g["batch"]
     for s, want in enumerate(g["losses"]):

@@ -17,7 +17,8 @@ constexpr int kIoBars = 4;  // tile-load mbarriers per epilogue warp
 struct EpiIo {
     uint8_t* buf;     // this warp's staging tiles (Epi::kIoBufs x 4 KB, 1024-byte aligned)
     uint64_t* bar;    // this warp's kIoBars mbarriers for tile loads (one per load slot)
-    uint32_t* phase;  // bit s = parity of the next completion on bar[s] (one word per warp, lives across tiles)
+    uint32_t* phase;  // bit s (< kIoBars) = parity of the next completion on bar[s]; bits >= 8 are free for the functor
+                      // (one word per warp, lives across tiles)
 };
 
 // element (r, c) of a staging tile sits at r*128 + ((c/4) ^ (r & 7))*16 + (c % 4)*4

@@ -207,8 +207,12 @@ struct EpiBackCodeHT {
         const int i = (co >> 5) / c.halves;  // slot of this chunk
         const int bcol = c.col0 + co;
         const bool live = bcol < c.N;          // else the whole chunk lies beyond the batch: nothing was requested
-        uint8_t* dt = io.buf + kSlots * 2048 + (i & 1) * 2048;
+        // the two dz staging tiles alternate per STORED chunk (bit 8 of the warp's persistent phase word), not per
+        // chunk index: a ragged tile can have an odd number of live chunks, and the tile used now must be the one
+        // whose last store is two bulk groups back
+        uint8_t* dt = io.buf + kSlots * 2048 + ((*io.phase >> 8) & 1u) * 2048;
         if (live) {
+            *io.phase ^= 1u << 8;
             const uint8_t* ct = io.buf + i * 2048;
             io_wait_loads(io, i);
             io_wait_stores_read_n<1>();  // the dz tile stored two chunks ago has been read

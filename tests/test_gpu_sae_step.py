@@ -272,14 +272,15 @@ def test_zero_preactivation_passes_gradient(kind):
         assert float((fw["z"][[5, 77]] == 0).float().mean()) == 1.0
 
 
+@pytest.mark.parametrize("B", [1024, 300])
 @pytest.mark.parametrize("kind,fmt", [("tied", "auto"), ("untied", "auto"), ("untied", "tf32")])
-def test_back_to_back_steps_equal_synchronised_steps(kind, fmt):
+def test_back_to_back_steps_equal_synchronised_steps(kind, fmt, B):
     """Steps enqueued back to back with no host synchronisation, every aux kept alive (so each step's code
     buffer is a fresh allocation, whose first touch is slow) must give bit-identical losses to the same steps run
     one at a time.  Guards the asynchronous staging-tile / TMA-store hand-offs inside the epilogues: a staging
     tile reused before its store had read it only shows up when stores are slow and nothing waits in between."""
     import sparse_coding__b200 as sc
-    M, B, d, N = 4, 1024, 256, 512
+    M, d, N = 4, 256, 512   # B = 300: ragged tiles, an odd number of live chunks per epilogue warp in the last tile
     data = make_sparse_data(8 * B, d, 2 * d, 8, seed=9).cuda()
     g = torch.Generator().manual_seed(11)
     idxs = [torch.randint(0, data.shape[0], (B,), generator=g).cuda() for _ in range(12)]

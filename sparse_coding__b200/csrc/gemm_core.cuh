@@ -47,6 +47,9 @@ struct GemmShape {
     int tiles_m, tiles_n;
     int nprob;  // > 1: segment p is an independent problem p (own operands, own epilogue parameters) sharing
                 // the launch; groups are then laid out as [problem][member]
+    int ksplit; // > 1 (CTA-pair kernel, one segment): every output tile is computed as ksplit partial tiles over
+                // disjoint ranges of the K loop, each by its own CTA pair; the epilogue sees RowCtx::split and must
+                // combine the partials itself (reduce-add).  For outputs with fewer tiles than CTA pairs.
 };
 
 constexpr int kEpiWarps = 4 * 2;  // 4 row quarters x kEpiHalves
@@ -96,6 +99,7 @@ struct RowCtx {
     int halves;  // epilogue warps per quarter in this launch (EpiHalvesOf<Epi>)
     int part;    // warp_q + 4*half: slot for per-warp partial results (0..4*halves-1)
     // the tile this warp processes next (static schedule), for functors that prefetch across tiles:
+    int split;      // which K range this partial tile covers (0 when GemmShape::ksplit <= 1)
     int bn;         // tile width in columns
     int first;      // 1 on the warp's first tile (nothing was prefetched for it)
     int next_g;     // group of the next tile, -1 when this is the last one
@@ -295,7 +299,7 @@ gemm_tf32_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
             RowCtx ctx;
             ctx.g = g; ctx.row = tm * kBlockM + q * 32 + lane; ctx.col0 = tn * BN;
             ctx.M = shape.M; ctx.N = shape.N; ctx.tile_m = tm; ctx.tile_n = tn; ctx.tiles_m = shape.tiles_m; ctx.tiles_n = shape.tiles_n; ctx.warp_q = q; ctx.prob = prob; ctx.half = half; ctx.halves = kH; ctx.part = q + 4 * half;
-            ctx.bn = BN; ctx.first = it == 0;
+            ctx.split = 0; ctx.bn = BN; ctx.first = it == 0;
             ctx.next_g = -1; ctx.next_prob = 0; ctx.next_row0 = 0; ctx.next_col0 = 0;
             if (tile + static_cast<int>(gridDim.x) < total_tiles) {
                 const int nt = tile + gridDim.x;

@@ -98,7 +98,8 @@ gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape sha
 
     const int nprob = shape.nprob > 1 ? shape.nprob : 1;
     const int tiles_per_group = shape.tiles_m * shape.tiles_n;  // tiles_m counts 256-row tiles here
-    const int total_tiles = tiles_per_group * shape.G * nprob;
+    const int ksplit = shape.ksplit > 1 ? shape.ksplit : 1;  // partial tiles per output tile (split fastest)
+    const int total_tiles = tiles_per_group * shape.G * nprob * ksplit;
     const int cluster_id = blockIdx.x >> 1;
     const int num_clusters = gridDim.x >> 1;
 
@@ -107,7 +108,8 @@ gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape sha
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
-            for (int tile = cluster_id; tile < total_tiles; tile += num_clusters) {
+            for (int ptile = cluster_id; ptile < total_tiles; ptile += num_clusters) {
+                const int tile = ptile / ksplit, split = ptile - tile * ksplit;
                 const int gg = tile / tiles_per_group;
                 const int prob = gg / shape.G;
                 const int g = gg - prob * shape.G;
@@ -119,8 +121,10 @@ gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape sha
                 const int seg_lo = nprob > 1 ? prob : 0, seg_hi = nprob > 1 ? prob + 1 : shape.nseg;
                 for (int seg = seg_lo; seg < seg_hi; ++seg) {
                     const int kblocks = (shape.K[seg] + kKElems - 1) / kKElems;
+                    const int kper = (kblocks + ksplit - 1) / ksplit;
+                    const int kb_lo = split * kper, kb_hi = kb_lo + kper < kblocks ? kb_lo + kper : kblocks;
                     const int ga = g * shape.a_gmul[seg], gb = g * shape.b_gmul[seg];
-                    for (int kb = 0; kb < kblocks; ++kb) {
+                    for (int kb = kb_lo; kb < kb_hi; ++kb) {
                         mbar_wait(&empty_bar[stage], phase ^ 1);
                         uint8_t* sa = smem + stage * Cfg::kStageBytes;
                         uint8_t* sb = sa + kATileBytes;
@@ -157,7 +161,8 @@ gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape sha
             int stage = 0;
             uint32_t phase = 0;
             int it = 0;
-            for (int tile = cluster_id; tile < total_tiles; tile += num_clusters, ++it) {
+            for (int ptile = cluster_id; ptile < total_tiles; ptile += num_clusters, ++it) {
+                const int tile = ptile / ksplit, split = ptile - tile * ksplit;
                 const int as = it & 1;
                 const uint32_t aph = (it >> 1) & 1;
                 mbar_wait(&tmem_empty[as], aph ^ 1);
@@ -168,7 +173,9 @@ gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape sha
                 const int seg_lo = nprob > 1 ? prob : 0, seg_hi = nprob > 1 ? prob + 1 : shape.nseg;
                 for (int seg = seg_lo; seg < seg_hi; ++seg) {
                     const int kblocks = (shape.K[seg] + kKElems - 1) / kKElems;
-                    for (int kb = 0; kb < kblocks; ++kb) {
+                    const int kper = (kblocks + ksplit - 1) / ksplit;
+                    const int kb_lo = split * kper, kb_hi = kb_lo + kper < kblocks ? kb_lo + kper : kblocks;
+                    for (int kb = kb_lo; kb < kb_hi; ++kb) {
                         mbar_wait(&full_bar[stage], phase);
                         tc_fence_after();
                         const uint32_t a_base = smem_u32(smem + stage * Cfg::kStageBytes);
@@ -209,7 +216,8 @@ gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape sha
         uint32_t io_phase = 0;
         EpiIo io{io_smem + (warp - 4) * (Epi::kIoBufs * kIoTileBytes), &io_bar[kIoBars * (warp - 4)], &io_phase};
         int it = 0;
-        for (int tile = cluster_id; tile < total_tiles; tile += num_clusters, ++it) {
+        for (int ptile = cluster_id; ptile < total_tiles; ptile += num_clusters, ++it) {
+            const int tile = ptile / ksplit, split = ptile - tile * ksplit;
             const int gg = tile / tiles_per_group;
             const int prob = gg / shape.G;
             const int g = gg - prob * shape.G;
@@ -224,10 +232,10 @@ gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape sha
             // partial-sum slots are indexed by 128-row tile: report this CTA's half as its own row tile
             ctx.tile_m = tm * 2 + rank; ctx.tile_n = tn; ctx.tiles_m = shape.tiles_m * 2; ctx.tiles_n = shape.tiles_n;
             ctx.warp_q = q; ctx.prob = prob; ctx.half = half; ctx.halves = kH; ctx.part = q + 4 * half;
-            ctx.bn = BN; ctx.first = it == 0;
+            ctx.split = split; ctx.bn = BN; ctx.first = it == 0;
             ctx.next_g = -1; ctx.next_prob = 0; ctx.next_row0 = 0; ctx.next_col0 = 0;
-            if (tile + num_clusters < total_tiles) {
-                const int nt = tile + num_clusters;
+            if (ptile + num_clusters < total_tiles) {
+                const int nt = (ptile + num_clusters) / ksplit;
                 const int ngg = nt / tiles_per_group;
                 const int nrem = nt - ngg * tiles_per_group;
                 const int ntn = nrem / shape.tiles_m;
@@ -269,7 +277,8 @@ cudaError_t launch_gemm_2cta(const GemmMaps& maps, GemmShape shape, const typena
     }
     shape.tiles_m = (shape.M + 2 * kBlockM - 1) / (2 * kBlockM);
     shape.tiles_n = (shape.N + BN - 1) / BN;
-    const long long total = 1LL * shape.tiles_m * shape.tiles_n * shape.G * (shape.nprob > 1 ? shape.nprob : 1);
+    const long long total = 1LL * shape.tiles_m * shape.tiles_n * shape.G * (shape.nprob > 1 ? shape.nprob : 1) *
+                            (shape.ksplit > 1 ? shape.ksplit : 1);
     if (total <= 0) return cudaSuccess;
     const int pairs = num_sms / 2;
     const int clusters = static_cast<int>(total < pairs ? total : pairs);

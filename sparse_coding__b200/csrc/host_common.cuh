@@ -155,10 +155,12 @@ struct GemmPlan {
 };
 
 inline int plan_gemm(GemmPlan* pl, int M, int N, int G, const Seg* segs, int nseg, bool a_mn, bool b_mn,
-                     bool segs_are_problems = false, int bn = 0) {
+                     bool segs_are_problems = false, int bn = 0, int ksplit = 0) {
     memset(pl, 0, sizeof *pl);
     SC_TRY(device_sm_count(&pl->sms));
     pl->bn = bn > 0 ? bn : pick_bn(N);
+    if (ksplit > 1 && (nseg != 1 || segs[0].a.elem_bytes != 2)) return fail(-3, "split-K needs one fp16 segment");
+    pl->sh.ksplit = ksplit > 1 ? ksplit : 1;
     pl->eb = segs[0].a.elem_bytes == 2 ? 2 : 4;
     pl->cta2 = use_cta_pairs() || pl->eb == 2;
     GemmShape& sh = pl->sh;
@@ -212,10 +214,10 @@ int launch_plan(const GemmPlan& pl, const typename Epi::Params& ep, cudaStream_t
 // ACC[g] = sum_seg A_seg[g] B_seg[g]^T over G groups, epilogue Epi.  Operand majors are compile-time.
 template <bool A_MN, bool B_MN, class Epi, bool F16 = false>
 int run_gemm(int M, int N, int G, const Seg* segs, int nseg, const typename Epi::Params& ep, cudaStream_t stream,
-             bool segs_are_problems = false, int bn = 0) {
+             bool segs_are_problems = false, int bn = 0, int ksplit = 0) {
     if (M <= 0 || N <= 0 || G <= 0) return 0;
     GemmPlan pl;
-    SC_TRY(plan_gemm(&pl, M, N, G, segs, nseg, A_MN, B_MN, segs_are_problems, bn));
+    SC_TRY(plan_gemm(&pl, M, N, G, segs, nseg, A_MN, B_MN, segs_are_problems, bn, ksplit));
     return launch_plan<A_MN, B_MN, Epi, F16>(pl, ep, stream);
 }
 

@@ -135,6 +135,30 @@ struct EpiDecodeH {
     }
 };
 
+// G2 with split K (few output tiles: small ensembles): every partial accumulator tile is ADDED into a zeroed fp32
+// x_hat buffer by TMA reduce-add; residual_h_kernel then forms r = x_hat - x and the MSE partial sums.
+struct EpiReduceTile {
+    static constexpr int kIoBufs = 1;
+    struct alignas(64) Params {
+        CUtensorMap out_map;  // fp32 io map of the accumulation buffer [G][rows][cols]
+    };
+    const Params& p;
+    const RowCtx c;
+    const EpiIo io;
+    SC_DEVICE EpiReduceTile(const Params& p_, const RowCtx& c_, const EpiIo& io_) : p(p_), c(c_), io(io_) {}
+    SC_DEVICE void prefetch(int) {}
+    SC_DEVICE void chunk(int co, float (&v)[32], int /*next_co*/) {
+        const int lane = threadIdx.x & 31;
+        io_wait_stores_read();
+        io_write_row(io.buf, lane, v);
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) tma_reduce_add_3d(&p.out_map, io.buf, c.col0 + co, c.row, c.g);  // clipped at the tensor's edge
+        io_commit();
+    }
+    SC_DEVICE void finish() {}
+};
+
 // G3 (transposed: rows = feature n, cols = batch b): dz' from q' = r D^T and the fp16 codes.
 // The thread of an accumulator row owns ONE feature and walks along the batch, so c and dz ([B][N] in memory)
 // are touched column-wise: both go through 32 x 32 fp16 staging tiles moved by TMA (box = 32 features x 32 batch

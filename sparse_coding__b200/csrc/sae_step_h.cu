@@ -78,7 +78,7 @@ __global__ void __launch_bounds__(256) step_prologue_h_kernel(const float* __res
                                                               long long x_n4, int x_blocks, const float* __restrict__ enc,
                                                               __half* __restrict__ enc_h, const float* __restrict__ W,
                                                               __half* __restrict__ D_h, float* __restrict__ inv_norm, int N,
-                                                              int d) {
+                                                              int d, float4* __restrict__ zero, long long zero_n4) {
     pdl_launch_dependents();
     pdl_wait();
     __shared__ float sh[8];
@@ -100,6 +100,9 @@ __global__ void __launch_bounds__(256) step_prologue_h_kernel(const float* __res
             __half2 h[2] = {__floats2half2_rn(v.x, v.y), __floats2half2_rn(v.z, v.w)};
             x_h[i] = *reinterpret_cast<uint2*>(h);
         }
+        // split-K decode accumulates into this buffer (EpiReduceTile): clear it here instead of in a memset node
+        for (long long i = blk * (long long)blockDim.x + threadIdx.x; i < zero_n4; i += (long long)x_blocks * blockDim.x)
+            zero[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         return;
     }
     blk -= x_blocks;
@@ -137,9 +140,32 @@ __global__ void __launch_bounds__(256) step_prologue_h_kernel(const float* __res
     }
 }
 
+// r = half(x_hat - x), mse_part[m][j] = sum of r^2 over slab j (n_mse slabs per member; block (j, m))
+__global__ void __launch_bounds__(256) residual_h_kernel(const float4* __restrict__ x_hat, const float4* __restrict__ x,
+                                                         uint2* __restrict__ r_h, float* __restrict__ mse_part, long long n4,
+                                                         int n_mse, long long x_mstride4) {
+    pdl_launch_dependents();
+    pdl_wait();
+    __shared__ float sh[8];
+    const int m = blockIdx.y;
+    const long long per = (n4 + n_mse - 1) / n_mse;
+    const long long lo = blockIdx.x * per, hi = lo + per < n4 ? lo + per : n4;
+    float acc = 0.f;
+    for (long long i = lo + threadIdx.x; i < hi; i += blockDim.x) {
+        const float4 a = x_hat[m * n4 + i], b = x[m * x_mstride4 + i];
+        const float r0 = a.x - b.x, r1 = a.y - b.y, r2 = a.z - b.z, r3 = a.w - b.w;
+        acc += (r0 * r0 + r1 * r1) + (r2 * r2 + r3 * r3);
+        __half2 h[2] = {__floats2half2_rn(r0, r1), __floats2half2_rn(r2, r3)};
+        r_h[m * n4 + i] = *reinterpret_cast<uint2*>(h);
+    }
+    const float t = block_sum(acc, sh);
+    if (threadIdx.x == 0) mse_part[(long long)m * n_mse + blockIdx.x] = t;
+}
+
 struct StepWsH {
     __half *x_h, *enc_h, *D_h, *r_h, *dz_h;
-    float *inv_norm, *l1_part, *mse_part, *db_part, *s_part, *bnorm;
+    float *inv_norm, *l1_part, *mse_part, *db_part, *s_part, *bnorm, *x_hat;
+    int g2_split;  // > 1: G2 runs split-K into x_hat
     int n_l1, n_mse, tiles_b;
     size_t bytes;
 };
@@ -163,6 +189,24 @@ static StepWsH carve_step_h(void* base, int M, int B, int d, int N, int tied, in
     w.db_part = c.floats(Mz * w.tiles_b * Nz);
     w.s_part = c.floats(Mz * w.tiles_b * Nz);
     w.bnorm = c.floats(Mz);
+    // G2's output has M ceil(B/256) ceil(d/bn) tiles; with fewer than half as many as CTA pairs most of the machine
+    // would idle through its long K = N loop: split K so that the partial tiles fill it (>= 8 k-blocks each)
+    w.g2_split = 1;
+    w.x_hat = nullptr;
+    {
+        const long long tiles = (long long)M * ceil_div(B, 256) * ceil_div(d, pick_bn(d));
+        const int pairs = 74, kblocks = ceil_div(N, 64);
+        int sp = static_cast<int>(pairs / (tiles > 0 ? tiles : 1));
+        if (sp > kblocks / 8) sp = kblocks / 8;
+        if (sp > 8) sp = 8;
+        if (sp >= 2 && (d & 3) == 0) {
+            while (sp > 1 && (long long)(sp - 1) * ceil_div(kblocks, sp) >= kblocks) --sp;  // no empty K range
+            if (sp >= 2) {
+                w.g2_split = sp;
+                w.x_hat = c.floats(Mz * Bz * dz_);
+            }
+        }
+    }
     w.bytes = c.off;
     return w;
 }
@@ -205,12 +249,14 @@ int sae_step_f16_impl(const ScStepArgs& a) {
         const long long x_n4 = xg * Bd / 4;
         const int x_blocks = static_cast<int>(x_n4 / 1024 + 1 < 1024 ? x_n4 / 1024 + 1 : 1024);
         const int blocks = M + x_blocks + ceil_div(N, 8) * M;
+        float4* zero = w.g2_split > 1 ? reinterpret_cast<float4*>(w.x_hat) : nullptr;
+        const long long zero_n4 = w.g2_split > 1 ? (long long)M * Bd / 4 : 0;
         if (a.tied)
             launch_k(step_prologue_h_kernel, dim3(blocks), dim3(256), 0, st, a.bias, w.bnorm, M, reinterpret_cast<const float4*>(a.x),
-                     reinterpret_cast<uint2*>(w.x_h), x_n4, x_blocks, nullptr, nullptr, a.enc, w.D_h, w.inv_norm, N, d);
+                     reinterpret_cast<uint2*>(w.x_h), x_n4, x_blocks, nullptr, nullptr, a.enc, w.D_h, w.inv_norm, N, d, zero, zero_n4);
         else
             launch_k(step_prologue_h_kernel, dim3(blocks), dim3(256), 0, st, a.bias, w.bnorm, M, reinterpret_cast<const float4*>(a.x),
-                     reinterpret_cast<uint2*>(w.x_h), x_n4, x_blocks, a.enc, w.enc_h, a.dec, w.D_h, w.inv_norm, N, d);
+                     reinterpret_cast<uint2*>(w.x_h), x_n4, x_blocks, a.enc, w.enc_h, a.dec, w.D_h, w.inv_norm, N, d, zero, zero_n4);
         SC_CUDA(cudaGetLastError(), "prologue launch");
     }
     prof_mark(st, "prologue");
@@ -222,7 +268,20 @@ int sae_step_f16_impl(const ScStepArgs& a) {
         SC_TRY((run_gemm<false, false, EpiEncodeH, true>(B, N, M, &s, 1, ep, st)));
     }
     prof_mark(st, "G1_encode");
-    {   // G2
+    if (w.g2_split > 1) {  // G2, split K: partial tiles reduce-added into x_hat, then the residual pass
+        Seg s{kmajor_h(c_h, B, N, M, BN_), mnmajor_h(w.D_h, d, N, M, Nd)};
+        EpiReduceTile::Params ep{};
+        {
+            const char* err = nullptr;
+            const int rc = make_io_map(&ep.out_map, w.x_hat, B, d, M, Bd, &err);
+            if (rc != 0) return fail(rc, "%s", err ? err : "io tensor map creation failed");
+        }
+        SC_TRY((run_gemm<false, true, EpiReduceTile, true>(B, d, M, &s, 1, ep, st, false, 0, w.g2_split)));
+        launch_k(residual_h_kernel, dim3(w.n_mse, M), dim3(256), 0, st, reinterpret_cast<const float4*>(w.x_hat),
+                 reinterpret_cast<const float4*>(a.x), reinterpret_cast<uint2*>(w.r_h), w.mse_part, Bd / 4, w.n_mse,
+                 a.x_per_member ? Bd / 4 : 0LL);
+        SC_CUDA(cudaGetLastError(), "residual launch");
+    } else {   // G2
         Seg s{kmajor_h(c_h, B, N, M, BN_), mnmajor_h(w.D_h, d, N, M, Nd)};
         EpiDecodeH::Params ep{a.x, w.r_h, w.mse_part, a.x_per_member ? Bd : 0, Bd};
         SC_TRY((run_gemm<false, true, EpiDecodeH, true>(B, d, M, &s, 1, ep, st)));

@@ -12,6 +12,10 @@ half the PCIe and HBM bytes) and stays resident; `chunk[idxs]` gathers, converts
 device (`sc_gather_rows`), and the sampler draws its permutation on the device, so a training step has no
 host->device traffic at all.  `ResidentChunk` quacks like the fp32 tensor the reference loop expects
 (`dataset[batch_idxs].to(device)`, `.shape`), so `ensemble_train_loop` keeps its signature.
+
+The loop does NOT upload a host tensor behind the caller's back: for one pass over an fp32 host chunk the upload moves
+the same bytes over PCIe as the per-step copies and is serial (measured: no gain).  Residency pays when the chunk is
+uploaded in fp16 (half the bytes) and shared by every ensemble trained on it - which is what `train_on_chunks` does.
 """
 import ctypes as C
 import os

@@ -69,8 +69,10 @@ typedef struct {
     /* operand_format 0: GEMM operands and c / R / dz in fp32 storage rounded to TF32 (kind::tf32).
      * operand_format 1: the same tensors in fp16 (kind::f16, same 11-bit significand, twice the MMA rate, half
      * the bytes; residual and dz kept unscaled so nothing underflows); needs sc_sae_step_f16_supported(B,d,N).
-     * In format 1 the codes are written to out_c_half ([M,B,N] fp16, required) and out_c may be NULL
-     * (when given it is filled from the fp16 codes).  Inputs with |x| > 65504 overflow fp16: use format 0. */
+     * In format 1 the engine keeps the codes TRANSPOSED: out_c_half (required) is c^T = [M][N][ldb] fp16 with
+     * ldb = B rounded up to a multiple of 8 (columns >= B are never written or read); out_c may be NULL (when
+     * given it is filled from the fp16 codes, as [M,B,N] fp32; sc_codes_to_float does the same later).
+     * Inputs with |x| > 65504 overflow fp16: use format 0. */
     int32_t operand_format;
     void* out_c_half;
     /* Masked ensembles (FunctionalMaskedSAE / FunctionalMaskedTiedSAE, sae_ensemble.py:307-442): member m only
@@ -92,11 +94,26 @@ typedef struct {
     float* rs_grad_dec[8];
     float* rs_grad_bias[8];
     float* rs_losses[8];
+    /* operand_format 1, untied, full update (no grad_* / rs_*): the Adam epilogue leaves fp16 copies of the UPDATED
+     * encoder / decoder and the decoder's row norms in the workspace, so the next step does not have to re-read the
+     * fp32 weights.  operands_valid = 1 tells the step that this hand-over is intact: same workspace, same M, d, N, and
+     * nothing but sc_sae_step has written the parameters since the previous full step; 0 (always safe) rebuilds the
+     * copies.
+     * In this mode the stored codes are c / ||W_d|| per feature; out_code_scale ([M,N] floats; operand_format 1 only;
+     * required with out_c, otherwise optional) receives the factor that sc_codes_to_float applies to the stored codes:
+     * ||W_d|| here, 1 in every other mode. */
+    int32_t operands_valid;
+    float* out_code_scale;
 } ScStepArgs;
 
 size_t sc_sae_step_workspace_bytes(int32_t M, int32_t B, int32_t d, int32_t N, int32_t tied, int32_t x_per_member);
 int sc_sae_step(const ScStepArgs* args);
 int sc_sae_step_f16_supported(int32_t B, int32_t d, int32_t N);
+/* aux "c" of step_batch (sae_ensemble.py:73-75) from the fp16-mode codes: out [M,B,N] fp32 from codes_t =
+ * ScStepArgs.out_c_half ([M][N][ldb] fp16, ldb = B rounded up to 8) times code_scale (ScStepArgs.out_code_scale, [M,N],
+ * or NULL for 1); entries with a negative pre-activation are -0. */
+int sc_codes_to_float(const void* codes_t, const float* code_scale, float* out, int32_t M, int32_t B, int32_t N,
+                      void* stream);
 
 /* Elementwise Adam exactly as the fused epilogues apply it (torchopt 0.7.1 semantics, see ScAdam):
  * p, mu, nu updated in place from gradient g, n elements (multiple of 4). */

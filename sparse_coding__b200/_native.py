@@ -24,7 +24,7 @@ EXPORTS = [
     "sc_version", "sc_last_error", "sc_sae_step_workspace_bytes", "sc_sae_step",
     "sc_encode_workspace_bytes", "sc_encode", "sc_decode_workspace_bytes", "sc_decode",
     "sc_fista_workspace_bytes", "sc_fista", "sc_gemm_tf32", "sc_adam_apply", "sc_row_normalise", "sc_column_variance",
-    "sc_profile_begin", "sc_profile_end", "sc_encode_noalloc", "sc_sae_step_f16_supported",
+    "sc_profile_begin", "sc_profile_end", "sc_encode_noalloc", "sc_sae_step_f16_supported", "sc_codes_to_float",
     "sc_gather_rows", "sc_column_mean_workspace_bytes", "sc_column_mean", "sc_infer_f16_supported", "sc_dp_adam_broadcast",
 ]
 
@@ -53,6 +53,7 @@ class ScStepArgs(C.Structure):
         ("rs_world", C.c_int32), ("rs_rows", C.c_int32),
         ("rs_grad_enc", C.c_void_p * 8), ("rs_grad_dec", C.c_void_p * 8),
         ("rs_grad_bias", C.c_void_p * 8), ("rs_losses", C.c_void_p * 8),
+        ("operands_valid", C.c_int32), ("out_code_scale", C.c_void_p),
     ]
 
 
@@ -139,6 +140,8 @@ def lib() -> C.CDLL:
         L.sc_column_variance.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]
         L.sc_sae_step_f16_supported.argtypes = [C.c_int32] * 3
         L.sc_sae_step_f16_supported.restype = C.c_int
+        L.sc_codes_to_float.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]
+        L.sc_codes_to_float.restype = C.c_int
         L.sc_adam_apply.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(ScAdam), C.c_void_p]
         L.sc_adam_apply.restype = C.c_int
         L.sc_gather_rows.argtypes = [C.POINTER(ScGatherArgs)]

@@ -6,6 +6,7 @@ autoencoders/ensemble.py:15-193 (same constructor, attributes, state_dict keys a
 from __future__ import annotations
 
 import ctypes as C
+from collections.abc import Mapping
 from typing import Dict, List, Optional
 
 import numpy as np
@@ -64,38 +65,51 @@ def _sig_kind(sig) -> str:
     return kind
 
 
-class LazyCodes(dict):
-    """aux dict of step_batch in fp16-operand mode: {"c": codes}.  The engine keeps the codes as an fp16
-    [M,B,N] tensor (that is what its GEMMs read); the float32 tensor the reference returns
-    (sae_ensemble.py:73-75) is produced on first access, so callers that ignore `aux` - most do - never
-    pay for the 4*M*B*N-byte write."""
+class LazyCodes(Mapping):
+    """aux of step_batch in fp16-operand mode: behaves like the reference's {"c": codes} (sae_ensemble.py:73-75).
+    The engine keeps the codes as an fp16 TRANSPOSED tensor c^T [M, N, ldb] (that is what its GEMMs read,
+    `codes_t`); the float32 [M, B, N] tensor the reference returns is produced by `sc_codes_to_float` on first
+    access, so callers that ignore `aux` - most do - never pay for the 4*M*B*N-byte write.  Every access path
+    (indexing, iteration, dict(aux), {**aux}, copy, pickle) goes through __getitem__ and sees the real tensor."""
 
-    def __init__(self, c_half):
-        super().__init__(c=None)
-        self.c_half = c_half
+    def __init__(self, codes_t, batch_rows, code_scale=None):
+        self.codes_t = codes_t
+        self.code_scale = code_scale  # [M, N] factor per feature (the untied step stores c / ||W_d||), or None
+        self.batch_rows = int(batch_rows)
         self._c = None
 
     def _materialise(self):
         if self._c is None:
-            self._c = self.c_half.float()
-            dict.__setitem__(self, "c", self._c)
+            M, N, _ = self.codes_t.shape
+            out = torch.empty((M, self.batch_rows, N), dtype=torch.float32, device=self.codes_t.device)
+            with torch.cuda.device(out.device):
+                nat.check(nat.lib().sc_codes_to_float(nat.ptr(self.codes_t), nat.ptr(self.code_scale), nat.ptr(out), M,
+                                                      self.batch_rows, N, nat.stream_ptr(out.device)), "sc_codes_to_float")
+            self._c = out
         return self._c
 
     def __getitem__(self, key):
         if key == "c":
             return self._materialise()
-        return dict.__getitem__(self, key)
+        raise KeyError(key)
 
-    def get(self, key, default=None):
-        return self[key] if key in self else default
+    def __iter__(self):
+        return iter(("c",))
 
-    def values(self):
-        self._materialise()
-        return dict.values(self)
+    def __len__(self):
+        return 1
 
-    def items(self):
-        self._materialise()
-        return dict.items(self)
+    def __reduce__(self):
+        return (dict, ({"c": self._materialise()},))
+
+    def __copy__(self):
+        return {"c": self._materialise()}
+
+    def copy(self):
+        return self.__copy__()
+
+    def __repr__(self):
+        return f"LazyCodes(M={self.codes_t.shape[0]}, B={self.batch_rows}, N={self.codes_t.shape[1]})"
 
 
 class FunctionalEnsemble:
@@ -313,6 +327,7 @@ class FunctionalEnsemble:
         """vmap(optimizer.update) + apply_updates (ensemble.py:182-191) from explicit gradients."""
         L = nat.lib()
         adam = self.adam_constants(advance=True)
+        self._ops_key = None  # the parameters change outside the fused step: its operand hand-over is void
         st = self.optim_states[0]
         for k, g in grads.items():
             p = self._contig(self.params, k)
@@ -395,9 +410,19 @@ class FunctionalEnsemble:
         self.last_operand_format = "f16" if f16 else "tf32"
         losses = torch.empty((4, M), dtype=torch.float32, device=x.device)
         c = None if f16 else torch.empty((M, B, N), dtype=torch.float32, device=x.device)
-        c_half = torch.empty((M, B, N), dtype=torch.float16, device=x.device) if f16 else None
+        # fp16 mode keeps the codes transposed, c^T [M][N][ldb], ldb = B rounded up to 8 (include/sc_b200.h)
+        c_half = torch.empty((M, N, (B + 7) & ~7), dtype=torch.float16, device=x.device) if f16 else None
+        code_scale = torch.empty((M, N), dtype=torch.float32, device=x.device) if f16 else None
         need = L.sc_sae_step_workspace_bytes(M, B, d, N, int(tied), int(per_member))
         ws_ptr, ws_bytes = self._ws.aligned(need, x.device)
+        # Hand-over of the fp16 operand copies from the previous step's Adam epilogue (ScStepArgs.operands_valid): intact
+        # while the workspace, the shapes and the parameter tensors (identity and torch version counter - the engine's own
+        # writes do not bump it) are what the previous full step left.
+        ops_key = None
+        if f16 and not tied and not grad_only:
+            ops_key = (ws_ptr.value, M, d, N, enc.data_ptr(), enc._version, dec.data_ptr(), dec._version)
+        ops_valid = ops_key is not None and getattr(self, "_ops_key", None) == ops_key
+        self._ops_key = None  # re-armed below once the step has been enqueued
         args = nat.ScStepArgs(
             M=M, B=B, d=d, N=N, tied=int(tied), x_per_member=int(per_member),
             x=nat.ptr(x), enc=nat.ptr(enc), enc_mu=nat.ptr(enc_mu), enc_nu=nat.ptr(enc_nu),
@@ -411,6 +436,7 @@ class FunctionalEnsemble:
             grad_dec=nat.ptr(grads.get("decoder")) if grads else None,
             B_total=int(batch_total),
             operand_format=int(f16), out_c_half=nat.ptr(c_half), dict_size=nat.ptr(dict_size),
+            operands_valid=int(ops_valid), out_code_scale=nat.ptr(code_scale),
         )
         if reduce_scatter is not None:
             rs = reduce_scatter
@@ -423,6 +449,8 @@ class FunctionalEnsemble:
                     args.rs_grad_dec[r] = rs["grad_dec"][r]
         with torch.cuda.device(x.device):
             nat.check(L.sc_sae_step(C.byref(args)), "sc_sae_step")
+        if ops_key is not None:
+            self._ops_key = ops_key
         loss_dict = {"loss": losses[0], "l_reconstruction": losses[1], "l_l1": losses[2]}
         if masked:
             pass  # loss, l_reconstruction, l_l1 only
@@ -430,7 +458,7 @@ class FunctionalEnsemble:
             loss_dict["l_bias_decay"] = losses[3]
         elif grad_only:
             loss_dict["l_bias_decay"] = losses[3]
-        aux = LazyCodes(c_half) if f16 else {"c": c}
+        aux = LazyCodes(c_half, B, code_scale) if f16 else {"c": c}
         if grad_only:
             return grads, loss_dict, aux
         return loss_dict, aux

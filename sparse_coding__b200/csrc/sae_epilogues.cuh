@@ -8,6 +8,7 @@
 #pragma once
 #include "epi_io.cuh"
 #include "epi_store.cuh"
+#include <cuda_fp16.h>
 
 namespace sc {
 
@@ -15,6 +16,31 @@ SC_DEVICE float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
     return v;
+}
+
+// "Fold" mode of the untied fp16 step: the decoder operand copy is half(W_d), NOT row-normalised (the Adam epilogue
+// of the previous step wrote it together with per-column-tile partial sums of w^2, so no kernel re-reads the fp32
+// weights), and the normalisation D = W_d / max(||W_d||, 1e-8) lives in per-feature scalars of the epilogues:
+//   codes stored as   c' = c  * inv        (x_hat = c D = c' W_d;   s = sum_b c q = sum_b c' (r W_d^T))
+//   dz    stored as   dz'' = dz * nrm      (dz = inv (r W_d^T) + l1 ... ;  dW_e = inv dz''^T x,  db = inv sum_b dz'')
+//   dD = nrm c'^T r, and the projected gradient (dD - s D) inv = c'^T r - s inv^2 W_d.
+// Rows under the clamp (||W_d|| < 1e-8) use scale 1 everywhere; their gradient is dD / 1e-8 as in the reference.
+struct RowNorm {
+    float nrm, inv;   // max(||W_n||, 1e-8) and its reciprocal
+    float ns, is;     // scales applied to stored tensors: nrm / inv, or 1 / 1 for a clamped row (and outside fold mode)
+    bool clamped;
+};
+// inv_norm[g][row] = 1 / max(||W_d row||, 1e-8), negative when the clamp is active (written by the step's prologue);
+// nullptr outside fold mode: every scale is 1
+SC_DEVICE RowNorm row_norm_of(const float* inv_norm, int g, int feats, int row) {
+    RowNorm r{1.f, 1.f, 1.f, 1.f, false};
+    if (!inv_norm || row >= feats) return r;
+    const float iv = inv_norm[(long long)g * feats + row];
+    r.clamped = iv < 0.f;
+    r.inv = fabsf(iv);
+    r.nrm = 1.f / r.inv;
+    if (!r.clamped) { r.ns = r.nrm; r.is = r.inv; }
+    return r;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -224,6 +250,7 @@ struct EpiBackCode {
 // ---------------------------------------------------------------------------------------------
 struct AdamConst {
     float lr, b1, b2, omb1, omb2, eps, eps_root, rbc1, rbc2;  // omb = 1 - beta, rbc = 1 / (1 - beta^t)
+    float nlr_rbc1;  // -lr * rbc1
 };
 
 SC_DEVICE float sqrt_approx(float x) {
@@ -237,16 +264,15 @@ SC_DEVICE float rcp_approx(float x) {
     return r;
 }
 
-// ~10 instructions per element (MUFU sqrt / rcp, 1-2 ulp): the update is lr * O(1), so the
+// 11 instructions per element (MUFU sqrt / rcp, 1-2 ulp): the update is lr * O(1), so the
 // approximation is far below fp32 resolution of the parameter and keeps the epilogue small enough
-// for the instruction cache.
+// for the instruction cache.  The two bias corrections ride on an FFMA each: nu_hat + eps_root = fma(nu, rbc2, eps_root)
+// and p -= lr * mu_hat / den = fma(mu / den, -lr * rbc1, p).
 SC_DEVICE void adam_update(float& p, float& mu, float& nu, float g, const AdamConst& a) {
     mu = fmaf(mu, a.b1, g * a.omb1);
     nu = fmaf(nu, a.b2, (g * g) * a.omb2);
-    const float mh = mu * a.rbc1;
-    const float nh = nu * a.rbc2;
-    const float upd = mh * rcp_approx(sqrt_approx(nh + a.eps_root) + a.eps);
-    p = fmaf(upd, -a.lr, p);
+    const float den = sqrt_approx(fmaf(nu, a.rbc2, a.eps_root)) + a.eps;
+    p = fmaf(mu * rcp_approx(den), a.nlr_rbc1, p);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -328,7 +354,7 @@ struct EpiAdam {
     // (kHalves = 1), each with TWO sets of p / mu / nu staging tiles: while one set is computed on and stored, the
     // other is already loading the warp's next chunk - across tile boundaries too (static tile schedule).
     static constexpr int kHalves = 1;
-    static constexpr int kIoBufs = 6;  // 2 sets x (p, mu, nu) x 4 KB per warp
+    static constexpr int kIoBufs = 7;  // 2 sets x (p, mu, nu) x 4 KB per warp + one fp16 tile [32][64] (fold mode)
     struct alignas(64) Sub {
         CUtensorMap p_map, mu_map, nu_map;  // io maps of [G][N][d]
         CUtensorMap grad_map;               // io map of the gradient output (gradient-only mode)
@@ -336,6 +362,12 @@ struct EpiAdam {
         const float* inv_norm;              // [G][N]  1/max(||W_n||,1e-8), negative when the clamp is active
         int projected;
         int grad_only;
+        // fold mode (untied fp16 step, see RowNorm): the accumulators carry the decoder normalisation as per-row scales,
+        // and the epilogue leaves behind what the next step's GEMMs need, so that no kernel re-reads the fp32 weights
+        const float* fold_inv;              // [G][N] 1/max(||W_d row||,1e-8) of the DECODER before this step (sign: clamp)
+        float* wsq_out;                     // [G][wsq_parts][N] partial sums of w^2 of the updated decoder (decoder problem only)
+        CUtensorMap half_map;               // fp16 io map (box 64 x 32) of the [G][N][d] copy of the updated parameter
+        int half_on;
     };
     struct alignas(64) Params {
         Sub sub[2];   // one per batched problem (untied: [0] encoder, [1] decoder)
@@ -347,6 +379,8 @@ struct EpiAdam {
         int rs_rows;                   // dictionary rows per owner (multiple of 32)
         CUtensorMap rs_map[2][8];      // [problem][owner]: io map of the owner's [1][rs_rows][d] accumulation buffer
         int fin_on;                    // 1: the idle warps of this launch also do the step's finalize work
+        int fold;                      // 1: fold mode
+        int wsq_parts;
         FinalizeArgs fin;
     };
     // warp 3 of CTA `cta` of `nctas` (no role in the GEMM)
@@ -357,13 +391,23 @@ struct EpiAdam {
     const Sub& u;
     const RowCtx c;
     const EpiIo io;
-    float s, inv;
-    bool clamped;
+    float s, inv, gsc, wsq;
+    bool clamped, half_store;
+    int half_store_col;
     SC_DEVICE EpiAdam(const Params& p_, const RowCtx& c_, const EpiIo& io_)
-        : p(p_), u(p_.sub[c_.prob]), c(c_), io(io_), s(0.f), inv(1.f), clamped(false) {
+        : p(p_), u(p_.sub[c_.prob]), c(c_), io(io_), s(0.f), inv(1.f), gsc(p_.g_scale), wsq(0.f), clamped(false),
+          half_store(false), half_store_col(0) {
         if (u.projected && c.row < c.M) {
             for (int t = 0; t < p.tiles_b; ++t) s += u.s_part[((long long)c.g * p.tiles_b + t) * c.M + c.row];
             s *= p.g_scale;
+        }
+        if (p.fold) {
+            const RowNorm rn = row_norm_of(u.fold_inv, c.g, c.M, c.row);
+            clamped = rn.clamped;
+            inv = rn.inv;
+            if (u.projected) s *= inv * inv;   // g = acc - (s inv^2) W   (clamped rows: g = acc inv, s unused)
+            else gsc *= rn.is;                 // dW_e = inv dz''^T x
+        } else if (u.projected && c.row < c.M) {
             const float iv = u.inv_norm[(long long)c.g * c.M + c.row];
             clamped = iv < 0.f;
             inv = fabsf(iv);
@@ -405,13 +449,18 @@ struct EpiAdam {
             if (next_co >= 0) request(set ^ 1, u, c.g, row0, c.col0 + next_co);
             else if (c.next_g >= 0) request(set ^ 1, p.sub[c.next_prob], c.next_g, c.next_row0, c.next_col0);
         }
-        if (p.g_scale != 1.f) {
+        if (p.g_scale != 1.f || p.fold) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] *= p.g_scale;
+            for (int j = 0; j < 32; ++j) v[j] *= gsc;
         }
         if (u.projected) {
+            if (p.fold) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = clamped ? v[j] * inv : (v[j] - s * (pv[j] * inv)) * inv;
+                for (int j = 0; j < 32; ++j) v[j] = clamped ? v[j] * inv : fmaf(-s, pv[j], v[j]);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] = clamped ? v[j] * inv : (v[j] - s * (pv[j] * inv)) * inv;
+            }
         }
         if (u.grad_only) {
             io_write_row(b, lane, v);
@@ -428,6 +477,7 @@ struct EpiAdam {
         } else {
 #pragma unroll
             for (int j = 0; j < 32; ++j) adam_update(pv[j], mv[j], nv[j], v[j], p.a);
+            if (p.fold) leave_operands(pv, co, next_co < 0);
             io_write_row(b, lane, pv);
             io_write_row(b + kIoTileBytes, lane, mv);
             io_write_row(b + 2 * kIoTileBytes, lane, nv);
@@ -437,11 +487,44 @@ struct EpiAdam {
                 tma_store_3d(&u.p_map, b, col, row0, c.g);
                 tma_store_3d(&u.mu_map, b + kIoTileBytes, col, row0, c.g);
                 tma_store_3d(&u.nu_map, b + 2 * kIoTileBytes, col, row0, c.g);
+                if (half_store) tma_store_3d(&u.half_map, io.buf + 6 * kIoTileBytes, half_store_col, row0, c.g);
             }
+            half_store = false;
         }
         io_commit();
     }
-    SC_DEVICE void finish() {}
+    // fold mode: fp16 copy of the updated parameters - two 32-column chunks share one [32][64] staging tile (128-byte
+    // rows: one L2 request per row and chunk pair) - and, for the decoder, this thread's share of the row's sum of squares
+    SC_DEVICE void leave_operands(const float (&pv)[32], int co, bool last) {
+        const int lane = threadIdx.x & 31;
+        if (u.wsq_out) {
+            const int ncols = c.N - (c.col0 + co);
+#pragma unroll
+            for (int j = 0; j < 32; ++j) wsq = (j < ncols) ? fmaf(pv[j], pv[j], wsq) : wsq;
+        }
+        if (!u.half_on) return;
+        uint8_t* tile = io.buf + 6 * kIoTileBytes;
+        const int hsel = (co >> 5) & 1;
+        const uint32_t row = smem_u32(tile) + lane * 128;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            uint32_t h[4];
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+                const __half2 x = __floats2half2_rn(pv[8 * j + 2 * t], pv[8 * j + 2 * t + 1]);
+                h[t] = *reinterpret_cast<const uint32_t*>(&x);
+            }
+            sts_128u(row + (((4 * hsel + j) ^ (lane & 7)) << 4), h[0], h[1], h[2], h[3]);
+        }
+        if (hsel == 1 || last) {  // the caller's fence + __syncwarp precede the store it issues for us
+            half_store_col = c.col0 + (co & ~63);
+            half_store = true;
+        }
+    }
+    SC_DEVICE void finish() {
+        if (p.fold && u.wsq_out && c.row < c.M)
+            u.wsq_out[((long long)c.g * p.wsq_parts + c.tile_n) * c.M + c.row] = wsq;
+    }
 };
 
 }  // namespace sc

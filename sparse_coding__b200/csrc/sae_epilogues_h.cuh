@@ -159,12 +159,85 @@ struct EpiReduceTile {
     SC_DEVICE void finish() {}
 };
 
+// G1 of the TRAIN step, computed transposed (rows = feature n, cols = batch b): the codes are kept as
+// c^T [G][N][ldb] fp16 (z < 0 stored as -0), which makes them row accesses for every later consumer - the dL/dz
+// epilogue (thread = feature) reads its own row, the weight-gradient GEMMs read c^T / dz^T K-major.  The bias is one
+// scalar per thread.  Batch columns >= B (zero-filled x rows on a ragged tile) are written as -0 and clipped by the store.
+template <int H>
+struct EpiEncodeTHT {
+    static constexpr int kHalves = H;  // epilogue warps per row quarter
+    static constexpr int kIoBufs = 1;  // one 4 KB buffer = two 2 KB fp16 staging tiles, used alternately
+    struct alignas(64) Params {
+        CUtensorMap c_map;     // fp16 io map of c^T [G][N][B] (row stride ldb)
+        const float* bias;     // [G][N]
+        float* l1_part;
+        const int* dict_size;  // [G] or nullptr: features >= dict_size[g] are masked out
+        const float* fold_inv; // fold mode: [G][N] 1/max(||W_d row||,1e-8) (sign: clamp), else nullptr
+        float* code_scale;     // fold mode, optional: [G][N] factor that turns the stored codes back into c (ScStepArgs.out_code_scale)
+    };
+    const Params& p;
+    const RowCtx c;
+    const EpiIo io;
+    float sum, sum1, sum2, sum3;
+    float bcs, cs, ns;  // bias * cs; scale of the stored code (fold mode: 1/||W_d||, else 1) and its reciprocal
+    bool live_row;
+    SC_DEVICE EpiEncodeTHT(const Params& p_, const RowCtx& c_, const EpiIo& io_)
+        : p(p_), c(c_), io(io_), sum(0.f), sum1(0.f), sum2(0.f), sum3(0.f) {
+        const int live_end = p.dict_size ? min(p.dict_size[c.g], c.M) : c.M;
+        live_row = c.row < live_end;
+        const RowNorm rn = row_norm_of(p.fold_inv, c.g, c.M, c.row);
+        cs = rn.is; ns = rn.ns;
+        bcs = live_row ? p.bias[(long long)c.g * c.M + c.row] * cs : 0.f;
+    }
+    SC_DEVICE void prefetch(int) {}
+    SC_DEVICE void chunk(int co, float (&v)[32], int /*next_co*/) {
+        const int col = c.col0 + co;  // batch index of v[0]
+        const int lane = threadIdx.x & 31;
+        const int nb = c.N - col;     // c.N = B here
+        // stored code c' = max(z, -0) * cs = max(z * cs, -0): -0.0 marks z < 0 (adding it to the L1 sum is a no-op);
+        // outside fold mode cs = 1 and fma(acc, 1, b) is acc + b exactly
+        if (live_row && nb >= 32) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+                v[j] = fmaxf(fmaf(v[j], cs, bcs), -0.0f);
+                v[j + 1] = fmaxf(fmaf(v[j + 1], cs, bcs), -0.0f);
+                v[j + 2] = fmaxf(fmaf(v[j + 2], cs, bcs), -0.0f);
+                v[j + 3] = fmaxf(fmaf(v[j + 3], cs, bcs), -0.0f);
+                sum += v[j]; sum1 += v[j + 1]; sum2 += v[j + 2]; sum3 += v[j + 3];
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                v[j] = (live_row && j < nb) ? fmaxf(fmaf(v[j], cs, bcs), -0.0f) : -0.0f;  // masked features behave like z < 0
+                sum += v[j];
+            }
+        }
+        // the two staging tiles alternate per stored chunk (bit 8 of the warp's persistent phase word: a tile can have an
+        // odd number of chunks per warp), so the one used now is the one whose store is two bulk groups back
+        uint8_t* tile = io.buf + ((*io.phase >> 8) & 1u) * 2048;
+        *io.phase ^= 1u << 8;
+        io_wait_stores_read_n<1>();
+        io_write_row_h(tile, lane, v);
+        io_store_tile(&p.c_map, tile, col, c.row - lane, c.g);
+        io_commit();
+    }
+    SC_DEVICE void finish() {
+        if (p.code_scale && c.tile_n == 0 && c.half == 0 && c.row < c.M) p.code_scale[(long long)c.g * c.M + c.row] = ns;
+        const float s = warp_sum(((sum + sum1) + (sum2 + sum3)) * ns);  // L1 term counts the unscaled codes
+        if ((threadIdx.x & 31) == 0) {
+            const int tiles = c.tiles_m * c.tiles_n;
+            p.l1_part[((long long)c.g * tiles + c.tile_n * c.tiles_m + c.tile_m) * (4 * H) + c.part] = s;
+        }
+    }
+};
+using EpiEncodeTH = EpiEncodeTHT<2>;
+
 // G3 (transposed: rows = feature n, cols = batch b): dz' from q' = r D^T and the fp16 codes.
-// The thread of an accumulator row owns ONE feature and walks along the batch, so c and dz ([B][N] in memory)
-// are touched column-wise: both go through 32 x 32 fp16 staging tiles moved by TMA (box = 32 features x 32 batch
-// rows).  The four c tiles a warp needs for a 256-column accumulator tile sit in four slots; as soon as a slot
-// has been read, the same chunk of the warp's NEXT tile is requested into it, so the loads fly during the rest
-// of this tile and the wait for the next accumulator - no register prefetch, no exposed load latency.
+// c^T and dz^T are [N][ldb] in memory, so the thread of an accumulator row (one feature, walking along the batch)
+// touches them ROW-wise: 32 x 32 fp16 staging tiles moved by TMA (box = 32 batch columns x 32 features), each lane
+// reading / writing its own 64-byte row with four 16-byte shared accesses.  The four c tiles a warp needs for a
+// 256-column accumulator tile sit in four slots; as soon as a slot has been read, the same chunk of the warp's NEXT
+// tile is requested into it, so the loads fly during the rest of this tile and the wait for the next accumulator.
 template <int H>
 struct EpiBackCodeHT {
     // H warps per row quarter (4 H epilogue warps): 8 / H chunks of 32 columns per warp and 256-wide tile.
@@ -173,8 +246,8 @@ struct EpiBackCodeHT {
     static constexpr int kIoBufs = (kSlots + 2 + 1) / 2;  // per warp: kSlots c slots + 2 dz staging tiles of 2 KB
     static_assert(kSlots <= kIoBars, "one load barrier per c slot");
     struct alignas(64) Params {
-        CUtensorMap c_map;    // fp16 io map of c  [G][B][N]
-        CUtensorMap dz_map;   // fp16 io map of dz [G][B][N]  (scaled by B d / 2)
+        CUtensorMap c_map;    // fp16 io map of c^T  [G][N][B]
+        CUtensorMap dz_map;   // fp16 io map of dz^T [G][N][B]  (scaled by B d / 2)
         const float* l1;      // [G]
         const float* bias;    // [G][N] (tied only)
         float* db_part;       // [G][parts][N]  (scaled)
@@ -182,23 +255,25 @@ struct EpiBackCodeHT {
         float l1_scale;       // d / 2:  lam/B * (B d / 2)
         int tied;
         int feats;
+        const float* fold_inv; // fold mode (untied): [G][N] 1/max(||W_d row||,1e-8) (sign: clamp), else nullptr
     };
     const Params& p;
     const RowCtx c;
     const EpiIo io;
-    float db, s, l1_term, bn;
-    uint32_t off[4];  // byte offset of this lane's element in rows j with ((j >> 1) & 3) == k (SWIZZLE_64B)
+    float db, db1, s, s1, l1_term, bn, db_scale;
     // chunk i of a tile covers accumulator columns (half + i * halves) * 32 ...
     SC_DEVICE void request(int slot, int g, int row0, int bcol) const {
         io_expect(io, 2048, slot);
-        tma_load_3d(&p.c_map, io.bar + slot, io.buf + slot * 2048, row0, bcol, g);
+        tma_load_3d(&p.c_map, io.bar + slot, io.buf + slot * 2048, bcol, row0, g);
     }
-    SC_DEVICE EpiBackCodeHT(const Params& p_, const RowCtx& c_, const EpiIo& io_) : p(p_), c(c_), io(io_), db(0.f), s(0.f) {
+    SC_DEVICE EpiBackCodeHT(const Params& p_, const RowCtx& c_, const EpiIo& io_)
+        : p(p_), c(c_), io(io_), db(0.f), db1(0.f), s(0.f), s1(0.f) {
         const int lane = threadIdx.x & 31;
-        l1_term = p.l1[c.g] * p.l1_scale;
+        // fold mode: the accumulator is r W_d^T (not normalised); dz is stored multiplied by ||W_d|| (see RowNorm)
+        const RowNorm rn = row_norm_of(p.fold_inv, c.g, p.feats, c.row);
+        l1_term = p.l1[c.g] * p.l1_scale * rn.ns;
+        db_scale = rn.is;
         bn = (p.tied && c.row < c.M) ? p.bias[(long long)c.g * p.feats + c.row] : 0.f;
-#pragma unroll
-        for (int k = 0; k < 4; ++k) off[k] = (((lane >> 3) ^ k) << 4) + ((lane & 7) << 1);
         if (c.first && lane == 0) {
             for (int i = 0; i < kSlots; ++i) {
                 const int bc = c.col0 + (c.half + i * c.halves) * 32;
@@ -209,21 +284,32 @@ struct EpiBackCodeHT {
     SC_DEVICE void prefetch(int) {}
     template <bool TIED>
     SC_DEVICE void body(const uint8_t* ct, uint8_t* dt, const float (&v)[32]) {
-        const uint32_t cs = smem_u32(ct), ds = smem_u32(dt);
-        int32_t h[32];
+        const int lane = threadIdx.x & 31;
+        const uint32_t cs = smem_u32(ct) + lane * 64, ds = smem_u32(dt) + lane * 64;
+        const int sw = (lane >> 1) & 3;  // SWIZZLE_64B: 16-byte chunk j of row r sits at chunk j ^ ((r >> 1) & 3)
+        uint4 hc[4];
 #pragma unroll
-        for (int j = 0; j < 32; ++j) h[j] = lds_s16(cs + j * 64 + off[(j >> 1) & 3]);  // all loads in flight first
+        for (int j = 0; j < 4; ++j) hc[j] = lds_128u(cs + ((j ^ sw) << 4));  // all loads in flight first
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-            // fp16 bit pattern, sign-extended: < 0 <=> sign bit set <=> z < 0;  > 0 <=> c > 0
-            const float cv = __half2float(__ushort_as_half(static_cast<unsigned short>(h[j] & 0xffff)));
-            const float q = v[j];
-            const float t = h[j] > 0 ? q + l1_term : q;
-            const float dzv = h[j] < 0 ? 0.f : t;
-            sts_u16(ds + j * 64 + off[(j >> 1) & 3], __half_as_ushort(__float2half_rn(dzv)));
-            db += dzv;
-            s = fmaf(cv, q, s);
-            if (TIED) s = fmaf(dzv, cv - bn, s);
+        for (int j = 0; j < 4; ++j) {
+            const uint32_t w[4] = {hc[j].x, hc[j].y, hc[j].z, hc[j].w};
+            uint32_t o[4];
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+                const float2 cf = __half22float2(*reinterpret_cast<const __half2*>(&w[t]));
+                const float q0 = v[8 * j + 2 * t], q1 = v[8 * j + 2 * t + 1];
+                // sign bit set <=> z < 0 (code -0);  > 0 <=> c > 0
+                const float t0 = cf.x > 0.f ? q0 + l1_term : q0;
+                const float t1 = cf.y > 0.f ? q1 + l1_term : q1;
+                const float d0 = __float_as_int(cf.x) < 0 ? 0.f : t0;
+                const float d1 = __float_as_int(cf.y) < 0 ? 0.f : t1;
+                const __half2 dh = __floats2half2_rn(d0, d1);
+                o[t] = *reinterpret_cast<const uint32_t*>(&dh);
+                db += d0; db1 += d1;
+                s = fmaf(cf.x, q0, s); s1 = fmaf(cf.y, q1, s1);
+                if (TIED) { s = fmaf(d0, cf.x - bn, s); s1 = fmaf(d1, cf.y - bn, s1); }
+            }
+            sts_128u(ds + ((j ^ sw) << 4), o[0], o[1], o[2], o[3]);
         }
     }
     SC_DEVICE void chunk(int co, float (&v)[32], int /*next_co*/) {
@@ -244,11 +330,11 @@ struct EpiBackCodeHT {
             else body<false>(ct, dt, v);
             fence_proxy_async_smem();
         }
-        // every lane has read slot i (and written its dz column): store, and hand the slot to the next tile's chunk i
+        // every lane has read slot i (and written its dz row): store, and hand the slot to the next tile's chunk i
         __syncwarp();
         if (lane == 0) {
             if (live) {
-                tma_store_3d(&p.dz_map, dt, c.row, bcol, c.g);
+                tma_store_3d(&p.dz_map, dt, bcol, c.row - lane, c.g);
                 tma_store_commit();
             }
             if (c.next_g >= 0 && c.next_col0 + co < c.N) request(i, c.next_g, c.next_row0, c.next_col0 + co);
@@ -257,8 +343,8 @@ struct EpiBackCodeHT {
     SC_DEVICE void finish() {
         if (c.row >= c.M) return;
         const long long o = ((long long)c.g * c.tiles_n * c.halves + c.tile_n * c.halves + c.half) * p.feats + c.row;
-        p.db_part[o] = db;
-        p.s_part[o] = s;
+        p.db_part[o] = (db + db1) * db_scale;
+        p.s_part[o] = s + s1;
     }
 };
 // Measured on the headline shape: H = 4 (16 epilogue warps, 640 threads, 96-register cap, 3 pipeline stages) is

@@ -194,6 +194,7 @@ static AdamConst make_adam(const ScAdam& a) {
     k.omb1 = static_cast<float>(1.0 - static_cast<double>(a.b1));
     k.omb2 = static_cast<float>(1.0 - static_cast<double>(a.b2));
     k.eps = a.eps; k.eps_root = a.eps_root; k.rbc1 = 1.0f / a.bc1; k.rbc2 = 1.0f / a.bc2;
+    k.nlr_rbc1 = -a.lr * k.rbc1;
     return k;
 }
 

@@ -37,8 +37,13 @@ int make_rowmajor_map(CUtensorMap* out, const float* base, int64_t rows, int64_t
 // Row-major fp32 [G][rows][cols] map for the epilogue staging tiles: box {32 cols, 32 rows}, 128-byte swizzle.
 int make_io_map(CUtensorMap* out, const float* base, int64_t rows, int64_t cols, int64_t g, int64_t gstride,
                 const char** err);
-// Same for fp16 tensors: box {32 cols, 32 rows} = 64-byte rows, 64-byte swizzle.
+// Same for fp16 tensors: box {32 cols, 32 rows} = 64-byte rows, 64-byte swizzle.  ld: row stride in elements
+// (multiple of 8; 0 = cols).
 int make_io_map_h(CUtensorMap* out, const void* base, int64_t rows, int64_t cols, int64_t g, int64_t gstride,
-                  const char** err);
+                  const char** err, int64_t ld = 0);
+
+// fp16 [G][rows][cols] map with box {64 cols, 32 rows} = 128-byte rows, 128-byte swizzle (two 32-column chunks per store)
+int make_io_map_h64(CUtensorMap* out, const void* base, int64_t rows, int64_t cols, int64_t g, int64_t gstride,
+                    const char** err);
 
 }  // namespace sc

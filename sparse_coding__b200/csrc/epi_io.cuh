@@ -36,6 +36,24 @@ SC_DEVICE void io_write_row(uint8_t* tile, int r, const float (&v)[32]) {
     for (int j = 0; j < 8; ++j) sts_128(row + ((j ^ (r & 7)) << 4), v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
 }
 
+// W consecutive columns (W = 32: the whole row, 16: columns [16 h, 16 h + 16)) of row r
+template <int W>
+SC_DEVICE void io_read_cols(const uint8_t* tile, int r, int h, float (&v)[W]) {
+    const uint32_t row = smem_u32(tile) + r * 128;
+#pragma unroll
+    for (int j = 0; j < W / 4; ++j) {
+        const float4 t = lds_128(row + (((j + h * (W / 4)) ^ (r & 7)) << 4));
+        v[4 * j] = t.x; v[4 * j + 1] = t.y; v[4 * j + 2] = t.z; v[4 * j + 3] = t.w;
+    }
+}
+template <int W>
+SC_DEVICE void io_write_cols(uint8_t* tile, int r, int h, const float (&v)[W]) {
+    const uint32_t row = smem_u32(tile) + r * 128;
+#pragma unroll
+    for (int j = 0; j < W / 4; ++j)
+        sts_128(row + (((j + h * (W / 4)) ^ (r & 7)) << 4), v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+}
+
 // Whole warp.  Make the rows just written visible to the async proxy, then lane 0 stores the tile.
 // The caller commits the group (io_commit) once all tiles of the step are issued.
 SC_DEVICE void io_store_tile(const CUtensorMap* map, const uint8_t* tile, int col, int row, int g) {

@@ -54,13 +54,13 @@ struct GemmShape {
 
 constexpr int kEpiWarps = 4 * 2;  // 4 row quarters x kEpiHalves
 
-template <int BN, int IO = 0, int H = kEpiHalves>
+template <int BN, int IO = 0, int H = kEpiHalves, int OWNERS = 4 * H>
 struct GemmCfg {
     static constexpr int kBTileBytes = BN * kBlockK * 4;
     static constexpr int kStageBytes = kATileBytes + kBTileBytes;
     static constexpr int kWarpsEpi = 4 * H;
     static constexpr int kThreads = 128 + 32 * kWarpsEpi;
-    static constexpr int kIoBytes = kWarpsEpi * IO * kIoTileBytes;  // epilogue staging tiles (epi_io.cuh)
+    static constexpr int kIoBytes = OWNERS * IO * kIoTileBytes;  // epilogue staging tiles (epi_io.cuh)
     static constexpr int kStagesRaw = (227 * 1024 - 2048 - kIoBytes) / kStageBytes;
     static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
     static constexpr int kTmemCols = (2 * BN <= 32) ? 32 : (2 * BN <= 64) ? 64 : (2 * BN <= 128) ? 128 : (2 * BN <= 256) ? 256 : 512;
@@ -76,6 +76,18 @@ template <class E, class = void>
 struct EpiHalvesOf { static constexpr int v = kEpiHalves; };
 template <class E>
 struct EpiHalvesOf<E, decltype((void)E::kHalves)> { static constexpr int v = E::kHalves; };
+
+// Column split (Epi::kColSplit == 2, with kHalves == 2): the two warps of a row quarter do not alternate chunks but
+// SHARE every chunk - warp `half` takes columns [16 half, 16 half + 16) of each 32-column chunk - and share one set of
+// staging tiles and load barriers per quarter.  For epilogues whose arithmetic per element, not their memory
+// traffic, is what a single warp per scheduler cannot get through (the Adam update).
+template <class E, class = void>
+struct EpiColSplitOf { static constexpr int v = 1; };
+template <class E>
+struct EpiColSplitOf<E, decltype((void)E::kColSplit)> { static constexpr int v = E::kColSplit; };
+// number of owners of staging memory: one per epilogue warp, or one per row quarter when the columns are split
+template <class E>
+struct EpiIoOwnersOf { static constexpr int v = EpiColSplitOf<E>::v == 2 ? 4 : 4 * EpiHalvesOf<E>::v; };
 
 // Optional work for warp 3, which has no role in the GEMM: Epi::side_job(params, cta, nctas) when the functor has one.
 template <class E>
@@ -116,20 +128,34 @@ SC_DEVICE void epilogue_tile(const typename Epi::Params& ep, const RowCtx& ctx, 
                              uint32_t parity, uint32_t taddr, Release release) {
     Epi epi(ep, ctx, io);
     constexpr int kH = EpiHalvesOf<Epi>::v;
-    constexpr int kChunks = (BN / 32 + kH - 1) / kH;
-    // global loads the functor needs for its first chunk do not depend on the accumulator: issue them
-    // before waiting for the MMAs, and the next chunk's while the current one is processed
-    if (ctx.half < BN / 32) epi.prefetch(ctx.half * 32);
-    mbar_wait(full_bar, parity);
-    tc_fence_after();
-#pragma unroll 1  // keep the (large) functor body in the instruction cache
-    for (int i = 0; i < kChunks; ++i) {
-        const int c = ctx.half + i * kH;
-        if (c < BN / 32) {
-            float v[32];
-            tmem_ld32(taddr + c * 32, v);
+    if constexpr (EpiColSplitOf<Epi>::v == 2) {
+        static_assert(kH == 2, "column split pairs the two warps of a row quarter");
+        epi.prefetch(0);
+        mbar_wait(full_bar, parity);
+        tc_fence_after();
+#pragma unroll 1
+        for (int c = 0; c < BN / 32; ++c) {
+            float v[16];
+            tmem_ld16(taddr + c * 32 + ctx.half * 16, v);
             tmem_ld_wait();
-            epi.chunk(c * 32, v, (c + kH < BN / 32) ? (c + kH) * 32 : -1);
+            epi.chunk(c * 32, v, (c + 1 < BN / 32) ? (c + 1) * 32 : -1);
+        }
+    } else {
+        constexpr int kChunks = (BN / 32 + kH - 1) / kH;
+        // global loads the functor needs for its first chunk do not depend on the accumulator: issue them
+        // before waiting for the MMAs, and the next chunk's while the current one is processed
+        if (ctx.half < BN / 32) epi.prefetch(ctx.half * 32);
+        mbar_wait(full_bar, parity);
+        tc_fence_after();
+#pragma unroll 1  // keep the (large) functor body in the instruction cache
+        for (int i = 0; i < kChunks; ++i) {
+            const int c = ctx.half + i * kH;
+            if (c < BN / 32) {
+                float v[32];
+                tmem_ld32(taddr + c * 32, v);
+                tmem_ld_wait();
+                epi.chunk(c * 32, v, (c + kH < BN / 32) ? (c + kH) * 32 : -1);
+            }
         }
     }
     tc_fence_before();
@@ -142,7 +168,7 @@ __global__ void __launch_bounds__(128 + 128 * EpiHalvesOf<Epi>::v, 1)
 gemm_tf32_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
                  const __grid_constant__ typename Epi::Params ep) {
     constexpr int kH = EpiHalvesOf<Epi>::v;
-    using Cfg = GemmCfg<BN, Epi::kIoBufs, kH>;
+    using Cfg = GemmCfg<BN, Epi::kIoBufs, kH, EpiIoOwnersOf<Epi>::v>;
     constexpr int kStages = Cfg::kStages;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -285,7 +311,8 @@ gemm_tf32_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
         const int q = warp & 3;
         const int half = (warp - 4) >> 2;
         uint32_t io_phase = 0;
-        EpiIo io{io_smem + (warp - 4) * (Epi::kIoBufs * kIoTileBytes), &io_bar[kIoBars * (warp - 4)], &io_phase};
+        const int io_owner = EpiColSplitOf<Epi>::v == 2 ? q : warp - 4;
+        EpiIo io{io_smem + io_owner * (Epi::kIoBufs * kIoTileBytes), &io_bar[kIoBars * io_owner], &io_phase};
         int it = 0;
         for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
             const int gg = tile / tiles_per_group;
@@ -339,7 +366,7 @@ inline bool use_pdl_plain() { return (pdl_mask() & 1) != 0; }
 template <int BN, bool A_MN, bool B_MN, class Epi>
 cudaError_t launch_gemm(const GemmMaps& maps, GemmShape shape, const typename Epi::Params& ep, int num_sms,
                         cudaStream_t stream) {
-    using Cfg = GemmCfg<BN, Epi::kIoBufs, EpiHalvesOf<Epi>::v>;
+    using Cfg = GemmCfg<BN, Epi::kIoBufs, EpiHalvesOf<Epi>::v, EpiIoOwnersOf<Epi>::v>;
     auto kern = gemm_tf32_kernel<BN, A_MN, B_MN, Epi>;
     static bool attr_set[64] = {};  // per template instantiation, per device
     int dev = 0;

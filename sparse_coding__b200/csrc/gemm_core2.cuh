@@ -19,14 +19,14 @@
 
 namespace sc {
 
-template <int BN, int IO = 0, int H = kEpiHalves>
+template <int BN, int IO = 0, int H = kEpiHalves, int OWNERS = 4 * H>
 struct GemmCfg2 {
     static constexpr int kWarpsEpi = 4 * H;
     static constexpr int kThreads = 128 + 32 * kWarpsEpi;
     static constexpr int kBHalf = BN / 2;
     static constexpr int kBTileBytes = kBHalf * kBlockK * 4;
     static constexpr int kStageBytes = kATileBytes + kBTileBytes;
-    static constexpr int kIoBytes = kWarpsEpi * IO * kIoTileBytes;
+    static constexpr int kIoBytes = OWNERS * IO * kIoTileBytes;
     static constexpr int kStagesRaw = (227 * 1024 - 2048 - kIoBytes) / kStageBytes;
     static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
     static constexpr int kTmemCols = GemmCfg<BN>::kTmemCols;
@@ -44,7 +44,7 @@ __global__ void __launch_bounds__(128 + 128 * EpiHalvesOf<Epi>::v, 1)
 gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
                       const __grid_constant__ typename Epi::Params ep) {
     constexpr int kH = EpiHalvesOf<Epi>::v;
-    using Cfg = GemmCfg2<BN, Epi::kIoBufs, kH>;
+    using Cfg = GemmCfg2<BN, Epi::kIoBufs, kH, EpiIoOwnersOf<Epi>::v>;
     constexpr int kStages = Cfg::kStages;
     constexpr int kBHalf = Cfg::kBHalf;
     constexpr int kKElems = 128 / EB;            // operand elements per k-block
@@ -214,7 +214,8 @@ gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape sha
         const int q = warp & 3;
         const int half = (warp - 4) >> 2;
         uint32_t io_phase = 0;
-        EpiIo io{io_smem + (warp - 4) * (Epi::kIoBufs * kIoTileBytes), &io_bar[kIoBars * (warp - 4)], &io_phase};
+        const int io_owner = EpiColSplitOf<Epi>::v == 2 ? q : warp - 4;
+        EpiIo io{io_smem + io_owner * (Epi::kIoBufs * kIoTileBytes), &io_bar[kIoBars * io_owner], &io_phase};
         int it = 0;
         for (int ptile = cluster_id; ptile < total_tiles; ptile += num_clusters, ++it) {
             const int tile = ptile / ksplit, split = ptile - tile * ksplit;
@@ -265,7 +266,7 @@ gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape sha
 template <int BN, bool A_MN, bool B_MN, class Epi, int EB = 4>
 cudaError_t launch_gemm_2cta(const GemmMaps& maps, GemmShape shape, const typename Epi::Params& ep, int num_sms,
                              cudaStream_t stream) {
-    using Cfg = GemmCfg2<BN, Epi::kIoBufs, EpiHalvesOf<Epi>::v>;
+    using Cfg = GemmCfg2<BN, Epi::kIoBufs, EpiHalvesOf<Epi>::v, EpiIoOwnersOf<Epi>::v>;
     auto kern = gemm_tf32_2cta_kernel<BN, A_MN, B_MN, Epi, EB>;
     static bool attr_set[64] = {};
     int dev = 0;

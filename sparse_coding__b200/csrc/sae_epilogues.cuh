@@ -349,40 +349,53 @@ SC_DEVICE void finalize_work(const FinalizeArgs& f, int warp, int nwarps) {
     }
 }
 
-struct EpiAdam {
-    // HBM-bound epilogue: what matters is how many tile loads and stores are in flight.  Four epilogue warps
-    // (kHalves = 1), each with TWO sets of p / mu / nu staging tiles: while one set is computed on and stored, the
-    // other is already loading the warp's next chunk - across tile boundaries too (static tile schedule).
-    static constexpr int kHalves = 1;
-    static constexpr int kIoBufs = 7;  // 2 sets x (p, mu, nu) x 4 KB per warp + one fp16 tile [32][64] (fold mode)
-    struct alignas(64) Sub {
-        CUtensorMap p_map, mu_map, nu_map;  // io maps of [G][N][d]
-        CUtensorMap grad_map;               // io map of the gradient output (gradient-only mode)
-        const float* s_part;                // [G][parts][N] (projected only)
-        const float* inv_norm;              // [G][N]  1/max(||W_n||,1e-8), negative when the clamp is active
-        int projected;
-        int grad_only;
-        // fold mode (untied fp16 step, see RowNorm): the accumulators carry the decoder normalisation as per-row scales,
-        // and the epilogue leaves behind what the next step's GEMMs need, so that no kernel re-reads the fp32 weights
-        const float* fold_inv;              // [G][N] 1/max(||W_d row||,1e-8) of the DECODER before this step (sign: clamp)
-        float* wsq_out;                     // [G][wsq_parts][N] partial sums of w^2 of the updated decoder (decoder problem only)
-        CUtensorMap half_map;               // fp16 io map (box 64 x 32) of the [G][N][d] copy of the updated parameter
-        int half_on;
-    };
-    struct alignas(64) Params {
-        Sub sub[2];   // one per batched problem (untied: [0] encoder, [1] decoder)
-        int tiles_b;  // partial slots per feature in s_part
-        float g_scale;  // applied to the accumulator and to s (fp16 mode keeps them scaled by B d / 2; else 1)
-        AdamConst a;
-        // fused reduce-scatter (ScStepArgs.rs_world > 0): gradient tiles are ADDED into their owner's buffer
-        int rs_world;                  // 0: off
-        int rs_rows;                   // dictionary rows per owner (multiple of 32)
-        CUtensorMap rs_map[2][8];      // [problem][owner]: io map of the owner's [1][rs_rows][d] accumulation buffer
-        int fin_on;                    // 1: the idle warps of this launch also do the step's finalize work
-        int fold;                      // 1: fold mode
-        int wsq_parts;
-        FinalizeArgs fin;
-    };
+// Parameters of the weight-gradient + Adam epilogue (EpiAdamT below)
+struct alignas(64) AdamSub {
+    CUtensorMap p_map, mu_map, nu_map;  // io maps of [G][N][d]
+    CUtensorMap grad_map;               // io map of the gradient output (gradient-only mode)
+    const float* s_part;                // [G][parts][N] (projected only)
+    const float* inv_norm;              // [G][N]  1/max(||W_n||,1e-8), negative when the clamp is active
+    int projected;
+    int grad_only;
+    // fold mode (untied fp16 step, see RowNorm): the accumulators carry the decoder normalisation as per-row scales,
+    // and the epilogue leaves behind what the next step's GEMMs need, so that no kernel re-reads the fp32 weights
+    const float* fold_inv;              // [G][N] 1/max(||W_d row||,1e-8) of the DECODER before this step (sign: clamp)
+    float* wsq_out;                     // [G][wsq_parts][N] partial sums of w^2 of the updated decoder (decoder problem only)
+    CUtensorMap half_map;               // fp16 io map (box 64 x 32) of the [G][N][d] copy of the updated parameter
+    int half_on;
+};
+struct alignas(64) AdamParams {
+AdamSub sub[2];   // one per batched problem (untied: [0] encoder, [1] decoder)
+    int tiles_b;  // partial slots per feature in s_part
+    float g_scale;  // applied to the accumulator and to s (fp16 mode keeps them scaled by B d / 2; else 1)
+    AdamConst a;
+    // fused reduce-scatter (ScStepArgs.rs_world > 0): gradient tiles are ADDED into their owner's buffer
+    int rs_world;                  // 0: off
+    int rs_rows;                   // dictionary rows per owner (multiple of 32)
+    CUtensorMap rs_map[2][8];      // [problem][owner]: io map of the owner's [1][rs_rows][d] accumulation buffer
+    int fin_on;                    // 1: the idle warps of this launch also do the step's finalize work
+    int fold;                      // 1: fold mode
+    int wsq_parts;                 // partial slots per feature in wsq_out: column tiles x SPLIT
+    FinalizeArgs fin;
+};
+
+// SPLIT = 1: four epilogue warps, each with its own staging tiles.  SPLIT = 2 (gemm_core.cuh "column split"): eight
+// warps, the two of a row quarter share the quarter's staging tiles and each handles 16 of a chunk's 32 columns - the
+// Adam arithmetic (11 ops + 6 shared-memory vector accesses per element, two MUFU among them) is more than one warp
+// per scheduler issues in the time the tile's HBM traffic takes, two warps per scheduler overlap each other's
+// latencies.  Warp half 0 of the quarter owns the TMA traffic; one 64-thread named barrier per chunk orders the
+// other warp's row writes before the tile stores.
+template <int SPLIT>
+struct EpiAdamT {
+    // HBM-bound epilogue: what matters is how many tile loads and stores are in flight.  Per quarter TWO sets of
+    // p / mu / nu staging tiles: while one set is computed on and stored, the other is already loading the next chunk -
+    // across tile boundaries too (static tile schedule).
+    static constexpr int kHalves = SPLIT;
+    static constexpr int kColSplit = SPLIT;
+    static constexpr int W = 32 / SPLIT;  // columns per thread and chunk
+    static constexpr int kIoBufs = 7;  // 2 sets x (p, mu, nu) x 4 KB + one fp16 tile [32][64] (fold mode)
+    using Sub = AdamSub;
+    using Params = AdamParams;
     // warp 3 of CTA `cta` of `nctas` (no role in the GEMM)
     static SC_DEVICE void side_job(const Params& p, int cta, int nctas) {
         if (p.fin_on) finalize_work(p.fin, cta, nctas);
@@ -392,11 +405,11 @@ struct EpiAdam {
     const RowCtx c;
     const EpiIo io;
     float s, inv, gsc, wsq;
-    bool clamped, half_store;
+    bool clamped, half_store, owner;  // owner: this warp issues the quarter's TMA loads and stores
     int half_store_col;
-    SC_DEVICE EpiAdam(const Params& p_, const RowCtx& c_, const EpiIo& io_)
+    SC_DEVICE EpiAdamT(const Params& p_, const RowCtx& c_, const EpiIo& io_)
         : p(p_), u(p_.sub[c_.prob]), c(c_), io(io_), s(0.f), inv(1.f), gsc(p_.g_scale), wsq(0.f), clamped(false),
-          half_store(false), half_store_col(0) {
+          half_store(false), owner(SPLIT == 1 || c_.half == 0), half_store_col(0) {
         if (u.projected && c.row < c.M) {
             for (int t = 0; t < p.tiles_b; ++t) s += u.s_part[((long long)c.g * p.tiles_b + t) * c.M + c.row];
             s *= p.g_scale;
@@ -413,7 +426,7 @@ struct EpiAdam {
             inv = fabsf(iv);
         }
     }
-    // lane 0: tile loads of one chunk (problem `sub`, group g, rows row0.., columns col..) into staging set `set`
+    // lane 0 of the owner warp: tile loads of one chunk (problem `sub`, group g, rows row0.., columns col..) into set `set`
     SC_DEVICE void request(int set, const Sub& sub, int g, int row0, int col) const {
         uint8_t* b = io.buf + set * (3 * kIoTileBytes);
         if (sub.grad_only) {
@@ -429,61 +442,75 @@ struct EpiAdam {
     // Called by the core before it waits for the accumulator.  Only the warp's very first tile needs it: every
     // later first chunk was requested by the last chunk of the tile before.
     SC_DEVICE void prefetch(int co) {
-        if (c.first && (threadIdx.x & 31) == 0) request((co >> 5) & 1, u, c.g, c.row, c.col0 + co);
+        if (c.first && owner && (threadIdx.x & 31) == 0) request((co >> 5) & 1, u, c.g, c.row, c.col0 + co);
     }
-    SC_DEVICE void chunk(int co, float (&v)[32], int next_co) {
+    // every thread of the quarter has written its part of the staging rows: make them visible to the async proxy
+    // and let the owner's lane 0 go on to the tile stores
+    SC_DEVICE void rows_written() const {
+        fence_proxy_async_smem();
+        if (SPLIT == 1) __syncwarp();
+        else bar_sync_named(1 + c.warp_q, 64);
+    }
+    SC_DEVICE void chunk(int co, float (&v)[W], int next_co) {
         const int lane = threadIdx.x & 31;
-        const int set = (co >> 5) & 1;  // kHalves == 1: consecutive chunks alternate between the two sets
+        const int h = SPLIT == 1 ? 0 : c.half;
+        const int set = (co >> 5) & 1;  // consecutive chunks alternate between the two sets
         const int col = c.col0 + co, row0 = c.row - lane;
         uint8_t* b = io.buf + set * (3 * kIoTileBytes);
         io_wait_loads(io, set);
-        float pv[32], mv[32], nv[32];
-        io_read_row(b, lane, pv);
+        float pv[W], mv[W], nv[W];
+        io_read_cols<W>(b, lane, h, pv);
         if (!u.grad_only) {
-            io_read_row(b + kIoTileBytes, lane, mv);
-            io_read_row(b + 2 * kIoTileBytes, lane, nv);
+            io_read_cols<W>(b + kIoTileBytes, lane, h, mv);
+            io_read_cols<W>(b + 2 * kIoTileBytes, lane, h, nv);
         }
-        // the other set was stored one chunk ago; once that store has read it, the next chunk loads into it
-        io_wait_stores_read();
-        if (lane == 0) {
-            if (next_co >= 0) request(set ^ 1, u, c.g, row0, c.col0 + next_co);
-            else if (c.next_g >= 0) request(set ^ 1, p.sub[c.next_prob], c.next_g, c.next_row0, c.next_col0);
+        // the other set was stored one chunk ago (both warps of the quarter had written their rows before that
+        // store was issued); once the store has read it, the next chunk loads into it
+        if (owner) {
+            io_wait_stores_read();
+            if (lane == 0) {
+                if (next_co >= 0) request(set ^ 1, u, c.g, row0, c.col0 + next_co);
+                else if (c.next_g >= 0) request(set ^ 1, p.sub[c.next_prob], c.next_g, c.next_row0, c.next_col0);
+            }
         }
+        // the owner has seen the previous chunk's stores read their tiles: only now may the other warp of the quarter
+        // overwrite the fp16 tile those stores included
+        if (SPLIT == 2 && p.fold) bar_sync_named(5 + c.warp_q, 64);
         if (p.g_scale != 1.f || p.fold) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] *= gsc;
+            for (int j = 0; j < W; ++j) v[j] *= gsc;
         }
         if (u.projected) {
             if (p.fold) {
 #pragma unroll
-                for (int j = 0; j < 32; ++j) v[j] = clamped ? v[j] * inv : fmaf(-s, pv[j], v[j]);
+                for (int j = 0; j < W; ++j) v[j] = clamped ? v[j] * inv : fmaf(-s, pv[j], v[j]);
             } else {
 #pragma unroll
-                for (int j = 0; j < 32; ++j) v[j] = clamped ? v[j] * inv : (v[j] - s * (pv[j] * inv)) * inv;
+                for (int j = 0; j < W; ++j) v[j] = clamped ? v[j] * inv : (v[j] - s * (pv[j] * inv)) * inv;
             }
         }
         if (u.grad_only) {
-            io_write_row(b, lane, v);
-            if (p.rs_world > 0) {
-                // the warp's 32 rows belong to one owner (rs_rows is a multiple of 32); rows past M are clipped by
-                // the map of the last owner
-                const int owner = min(row0 / p.rs_rows, p.rs_world - 1);
-                fence_proxy_async_smem();
-                __syncwarp();
-                if (lane == 0) tma_reduce_add_3d(&p.rs_map[c.prob][owner], b, col, row0 - owner * p.rs_rows, 0);
-            } else {
-                io_store_tile(&u.grad_map, b, col, row0, c.g);
+            io_write_cols<W>(b, lane, h, v);
+            rows_written();
+            if (owner && lane == 0) {
+                if (p.rs_world > 0) {
+                    // the quarter's 32 rows belong to one owner rank (rs_rows is a multiple of 32); rows past M are
+                    // clipped by the map of the last owner
+                    const int rk = min(row0 / p.rs_rows, p.rs_world - 1);
+                    tma_reduce_add_3d(&p.rs_map[c.prob][rk], b, col, row0 - rk * p.rs_rows, 0);
+                } else {
+                    tma_store_3d(&u.grad_map, b, col, row0, c.g);
+                }
             }
         } else {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) adam_update(pv[j], mv[j], nv[j], v[j], p.a);
-            if (p.fold) leave_operands(pv, co, next_co < 0);
-            io_write_row(b, lane, pv);
-            io_write_row(b + kIoTileBytes, lane, mv);
-            io_write_row(b + 2 * kIoTileBytes, lane, nv);
-            fence_proxy_async_smem();
-            __syncwarp();
-            if (lane == 0) {
+            for (int j = 0; j < W; ++j) adam_update(pv[j], mv[j], nv[j], v[j], p.a);
+            if (p.fold) leave_operands(pv, co, h, next_co < 0);
+            io_write_cols<W>(b, lane, h, pv);
+            io_write_cols<W>(b + kIoTileBytes, lane, h, mv);
+            io_write_cols<W>(b + 2 * kIoTileBytes, lane, h, nv);
+            rows_written();
+            if (owner && lane == 0) {
                 tma_store_3d(&u.p_map, b, col, row0, c.g);
                 tma_store_3d(&u.mu_map, b + kIoTileBytes, col, row0, c.g);
                 tma_store_3d(&u.nu_map, b + 2 * kIoTileBytes, col, row0, c.g);
@@ -491,40 +518,46 @@ struct EpiAdam {
             }
             half_store = false;
         }
-        io_commit();
+        if (owner) io_commit();
     }
     // fold mode: fp16 copy of the updated parameters - two 32-column chunks share one [32][64] staging tile (128-byte
     // rows: one L2 request per row and chunk pair) - and, for the decoder, this thread's share of the row's sum of squares
-    SC_DEVICE void leave_operands(const float (&pv)[32], int co, bool last) {
+    SC_DEVICE void leave_operands(const float (&pv)[W], int co, int h, bool last) {
         const int lane = threadIdx.x & 31;
         if (u.wsq_out) {
-            const int ncols = c.N - (c.col0 + co);
+            const int ncols = c.N - (c.col0 + co) - h * W;
 #pragma unroll
-            for (int j = 0; j < 32; ++j) wsq = (j < ncols) ? fmaf(pv[j], pv[j], wsq) : wsq;
+            for (int j = 0; j < W; ++j) wsq = (j < ncols) ? fmaf(pv[j], pv[j], wsq) : wsq;
         }
         if (!u.half_on) return;
         uint8_t* tile = io.buf + 6 * kIoTileBytes;
         const int hsel = (co >> 5) & 1;
         const uint32_t row = smem_u32(tile) + lane * 128;
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            uint32_t h[4];
+        for (int j = 0; j < W / 8; ++j) {
+            uint32_t hh[4];
 #pragma unroll
             for (int t = 0; t < 4; ++t) {
                 const __half2 x = __floats2half2_rn(pv[8 * j + 2 * t], pv[8 * j + 2 * t + 1]);
-                h[t] = *reinterpret_cast<const uint32_t*>(&x);
+                hh[t] = *reinterpret_cast<const uint32_t*>(&x);
             }
-            sts_128u(row + (((4 * hsel + j) ^ (lane & 7)) << 4), h[0], h[1], h[2], h[3]);
+            sts_128u(row + (((4 * hsel + h * (W / 8) + j) ^ (lane & 7)) << 4), hh[0], hh[1], hh[2], hh[3]);
         }
-        if (hsel == 1 || last) {  // the caller's fence + __syncwarp precede the store it issues for us
+        if (hsel == 1 || last) {  // the caller's fence + barrier precede the store it issues for us
             half_store_col = c.col0 + (co & ~63);
             half_store = true;
         }
     }
     SC_DEVICE void finish() {
-        if (p.fold && u.wsq_out && c.row < c.M)
-            u.wsq_out[((long long)c.g * p.wsq_parts + c.tile_n) * c.M + c.row] = wsq;
+        // two slots per column tile (wsq_parts = 2 x column tiles): one per warp of the quarter, or value and zero
+        if (p.fold && u.wsq_out && c.row < c.M) {
+            float* o = u.wsq_out + ((long long)c.g * p.wsq_parts + c.tile_n * 2) * c.M + c.row;
+            if (SPLIT == 1) { o[0] = wsq; o[c.M] = 0.f; }
+            else o[(long long)c.half * c.M] = wsq;
+        }
     }
 };
+using EpiAdam = EpiAdamT<1>;
+using EpiAdamS = EpiAdamT<2>;
 
 }  // namespace sc

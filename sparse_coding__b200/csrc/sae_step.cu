@@ -227,7 +227,7 @@ int check_rs(const ScStepArgs& a) {
 }
 
 // reduce-scatter destinations of the weight-gradient kernel and of finalize
-int fill_rs(EpiAdam::Params& e, const ScStepArgs& a) {
+int fill_rs(AdamParams& e, const ScStepArgs& a) {
     e.rs_world = a.rs_world;
     e.rs_rows = a.rs_rows;
     for (int r = 0; r < a.rs_world; ++r) {

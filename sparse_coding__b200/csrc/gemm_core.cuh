@@ -47,6 +47,7 @@ struct GemmShape {
     int tiles_m, tiles_n;
     int nprob;  // > 1: segment p is an independent problem p (own operands, own epilogue parameters) sharing
                 // the launch; groups are then laid out as [problem][member]
+    int res_stages;  // resident-A kernel (gemm_core2_res.cuh): stages of its B ring, set by the launcher
     int ksplit; // > 1 (CTA-pair kernel, one segment): every output tile is computed as ksplit partial tiles over
                 // disjoint ranges of the K loop, each by its own CTA pair; the epilogue sees RowCtx::split and must
                 // combine the partials itself (reduce-add).  For outputs with fewer tiles than CTA pairs.

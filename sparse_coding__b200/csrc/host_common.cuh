@@ -9,6 +9,7 @@
 
 #include "gemm_core.cuh"
 #include "gemm_core2.cuh"
+#include "gemm_core2_res.cuh"
 #include "tmap.h"
 
 namespace sc {
@@ -219,6 +220,35 @@ int run_gemm(int M, int N, int G, const Seg* segs, int nseg, const typename Epi:
     GemmPlan pl;
     SC_TRY(plan_gemm(&pl, M, N, G, segs, nseg, A_MN, B_MN, segs_are_problems, bn, ksplit));
     return launch_plan<A_MN, B_MN, Epi, F16>(pl, ep, stream);
+}
+
+// SC_B200_RESA=0: never use the resident-A kernel (A/B runs)
+inline bool use_resident_a() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("SC_B200_RESA");
+        v = (e && e[0] == '0') ? 0 : 1;
+    }
+    return v == 1;
+}
+
+// fp16 K-major GEMM with a short K loop: the resident-A kernel (gemm_core2_res.cuh) when it applies, else run_gemm
+template <class Epi>
+int run_gemm_short_k(int M, int N, int G, const Seg* seg, const typename Epi::Params& ep, cudaStream_t stream) {
+    if (M <= 0 || N <= 0 || G <= 0) return 0;
+    // measured at the headline shape (ms per step, resident / streaming): 0.472 / 0.477 with 8 column tiles per row tile,
+    // 0.831 / 0.828 with 16, 1.541 / 1.518 with 32 - beyond ~8 the contiguous tile ranges cost more than the saved
+    // operand traffic gives back
+    const bool ok = use_resident_a() && seg->a.elem_bytes == 2 && !seg->a.mn_major && !seg->b.mn_major &&
+                    seg->a.k <= 64 * kResMaxKBlocks && pick_bn(N) >= 128 && ceil_div(N, pick_bn(N)) <= 8;
+    if (!ok) return run_gemm<false, false, Epi, true>(M, N, G, seg, 1, ep, stream);
+    GemmPlan pl;
+    SC_TRY(plan_gemm(&pl, M, N, G, seg, 1, false, false));
+    cudaError_t e;
+    if (pl.bn == 256) e = launch_gemm_resa<256, Epi>(pl.maps, pl.sh, ep, pl.sms, stream);
+    else e = launch_gemm_resa<128, Epi>(pl.maps, pl.sh, ep, pl.sms, stream);
+    if (e != cudaSuccess) return cuda_fail(e, "gemm (resident A) launch");
+    return 0;
 }
 
 }  // namespace sc

@@ -235,16 +235,20 @@ using EpiEncodeTH = EpiEncodeTHT<2>;
 // G3 (transposed: rows = feature n, cols = batch b): dz' from q' = r D^T and the fp16 codes.
 // c^T and dz^T are [N][ldb] in memory, so the thread of an accumulator row (one feature, walking along the batch)
 // touches them ROW-wise: 32 x 32 fp16 staging tiles moved by TMA (box = 32 batch columns x 32 features), each lane
-// reading / writing its own 64-byte row with four 16-byte shared accesses.  The four c tiles a warp needs for a
-// 256-column accumulator tile sit in four slots; as soon as a slot has been read, the same chunk of the warp's NEXT
-// tile is requested into it, so the loads fly during the rest of this tile and the wait for the next accumulator.
+// reading / writing its own 64-byte row with four 16-byte shared accesses.  Three 2 KB slots per warp rotate: a
+// slot receives a c tile, dz overwrites it in place (a thread rewrites exactly the bytes it read), the tile is
+// stored from there, and once that store has read it the slot takes the c tile two chunks ahead - across tile
+// boundaries too (static schedule) - so loads fly during two chunks of arithmetic and 6 KB per warp is all the
+// staging this epilogue needs (the resident-A kernel has little shared memory to spare).
 template <int H>
 struct EpiBackCodeHT {
     // H warps per row quarter (4 H epilogue warps): 8 / H chunks of 32 columns per warp and 256-wide tile.
     static constexpr int kHalves = H;
-    static constexpr int kSlots = 8 / H;
-    static constexpr int kIoBufs = (kSlots + 2 + 1) / 2;  // per warp: kSlots c slots + 2 dz staging tiles of 2 KB
-    static_assert(kSlots <= kIoBars, "one load barrier per c slot");
+    static constexpr int kPerTile = 8 / H;
+    static constexpr int kSlots = 3;
+    static constexpr int kIoBytes = kSlots * 2048;  // per warp (kernels that count staging in 4 KB units round up)
+    static constexpr int kIoBufs = 2;
+    static_assert(kSlots <= kIoBars, "one load barrier per slot");
     struct alignas(64) Params {
         CUtensorMap c_map;    // fp16 io map of c^T  [G][N][B]
         CUtensorMap dz_map;   // fp16 io map of dz^T [G][N][B]  (scaled by B d / 2)
@@ -261,35 +265,43 @@ struct EpiBackCodeHT {
     const RowCtx c;
     const EpiIo io;
     float db, db1, s, s1, l1_term, bn, db_scale;
-    // chunk i of a tile covers accumulator columns (half + i * halves) * 32 ...
+    // warp state that outlives the tile, in the free bits of the warp's phase word: bits 8-9 the slot of the next
+    // chunk to consume, bits 10-11 how many chunks after the current one have been requested (0..2)
     SC_DEVICE void request(int slot, int g, int row0, int bcol) const {
         io_expect(io, 2048, slot);
         tma_load_3d(&p.c_map, io.bar + slot, io.buf + slot * 2048, bcol, row0, g);
     }
     SC_DEVICE EpiBackCodeHT(const Params& p_, const RowCtx& c_, const EpiIo& io_)
         : p(p_), c(c_), io(io_), db(0.f), db1(0.f), s(0.f), s1(0.f) {
-        const int lane = threadIdx.x & 31;
         // fold mode: the accumulator is r W_d^T (not normalised); dz is stored multiplied by ||W_d|| (see RowNorm)
         const RowNorm rn = row_norm_of(p.fold_inv, c.g, p.feats, c.row);
         l1_term = p.l1[c.g] * p.l1_scale * rn.ns;
         db_scale = rn.is;
         bn = (p.tied && c.row < c.M) ? p.bias[(long long)c.g * p.feats + c.row] : 0.f;
-        if (c.first && lane == 0) {
-            for (int i = 0; i < kSlots; ++i) {
-                const int bc = c.col0 + (c.half + i * c.halves) * 32;
-                if (bc < c.N && (c.half + i * c.halves) * 32 < c.bn) request(i, c.g, c.row, bc);
-            }
-        }
     }
     SC_DEVICE void prefetch(int) {}
+    // chunk j of this warp in a tile that starts at batch column col0 exists (live chunks are a prefix in j)
+    SC_DEVICE bool live(int col0, int j) const {
+        const int cw = (c.half + j * H) * 32;
+        return j < kPerTile && cw < c.bn && col0 + cw < c.N;
+    }
+    // the k-th (1 or 2) live chunk after chunk i of the current tile, in processing order
+    SC_DEVICE bool nth_next(int i, int k, int& g, int& row0, int& bcol) const {
+        for (int j = i + 1; live(c.col0, j); ++j)
+            if (--k == 0) { g = c.g; row0 = c.row - (threadIdx.x & 31); bcol = c.col0 + (c.half + j * H) * 32; return true; }
+        if (c.next_g < 0) return false;
+        for (int j = 0; live(c.next_col0, j); ++j)
+            if (--k == 0) { g = c.next_g; row0 = c.next_row0; bcol = c.next_col0 + (c.half + j * H) * 32; return true; }
+        return false;
+    }
     template <bool TIED>
-    SC_DEVICE void body(const uint8_t* ct, uint8_t* dt, const float (&v)[32]) {
+    SC_DEVICE void body(uint8_t* slot, const float (&v)[32]) {
         const int lane = threadIdx.x & 31;
-        const uint32_t cs = smem_u32(ct) + lane * 64, ds = smem_u32(dt) + lane * 64;
+        const uint32_t rs = smem_u32(slot) + lane * 64;
         const int sw = (lane >> 1) & 3;  // SWIZZLE_64B: 16-byte chunk j of row r sits at chunk j ^ ((r >> 1) & 3)
         uint4 hc[4];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) hc[j] = lds_128u(cs + ((j ^ sw) << 4));  // all loads in flight first
+        for (int j = 0; j < 4; ++j) hc[j] = lds_128u(rs + ((j ^ sw) << 4));  // all loads in flight first
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             const uint32_t w[4] = {hc[j].x, hc[j].y, hc[j].z, hc[j].w};
@@ -309,36 +321,43 @@ struct EpiBackCodeHT {
                 s = fmaf(cf.x, q0, s); s1 = fmaf(cf.y, q1, s1);
                 if (TIED) { s = fmaf(d0, cf.x - bn, s); s1 = fmaf(d1, cf.y - bn, s1); }
             }
-            sts_128u(ds + ((j ^ sw) << 4), o[0], o[1], o[2], o[3]);
+            sts_128u(rs + ((j ^ sw) << 4), o[0], o[1], o[2], o[3]);  // dz over the codes just read
         }
     }
     SC_DEVICE void chunk(int co, float (&v)[32], int /*next_co*/) {
         const int lane = threadIdx.x & 31;
-        const int i = (co >> 5) / c.halves;  // slot of this chunk
+        const int i = (co >> 5) / H;  // index of this chunk among the warp's chunks of the tile
         const int bcol = c.col0 + co;
-        const bool live = bcol < c.N;          // else the whole chunk lies beyond the batch: nothing was requested
-        // the two dz staging tiles alternate per STORED chunk (bit 8 of the warp's persistent phase word), not per
-        // chunk index: a ragged tile can have an odd number of live chunks, and the tile used now must be the one
-        // whose last store is two bulk groups back
-        uint8_t* dt = io.buf + kSlots * 2048 + ((*io.phase >> 8) & 1u) * 2048;
-        if (live) {
-            *io.phase ^= 1u << 8;
-            const uint8_t* ct = io.buf + i * 2048;
-            io_wait_loads(io, i);
-            io_wait_stores_read_n<1>();  // the dz tile stored two chunks ago has been read
-            if (p.tied) body<true>(ct, dt, v);
-            else body<false>(ct, dt, v);
-            fence_proxy_async_smem();
+        if (bcol >= c.N) return;      // the whole chunk lies beyond the batch (warp-uniform): nothing was requested
+        const int row0 = c.row - lane;
+        int cons = (*io.phase >> 8) & 3, ahead = (*io.phase >> 10) & 3;
+        if (ahead == 0) {  // nothing in flight for this chunk (first chunk of the kernel, or the look-ahead could not see it)
+            io_wait_stores_read_n<1>();
+            if (lane == 0) request(cons, c.g, row0, bcol);
+            ahead = 1;
         }
-        // every lane has read slot i (and written its dz row): store, and hand the slot to the next tile's chunk i
+        uint8_t* slot = io.buf + cons * 2048;
+        io_wait_loads(io, cons);
+        if (p.tied) body<true>(slot, v);
+        else body<false>(slot, v);
+        fence_proxy_async_smem();
         __syncwarp();
         if (lane == 0) {
-            if (live) {
-                tma_store_3d(&p.dz_map, dt, bcol, c.row - lane, c.g);
-                tma_store_commit();
-            }
-            if (c.next_g >= 0 && c.next_col0 + co < c.N) request(i, c.next_g, c.next_row0, c.next_col0 + co);
+            tma_store_3d(&p.dz_map, slot, bcol, row0, c.g);
+            tma_store_commit();
         }
+        --ahead;
+        cons = cons == 2 ? 0 : cons + 1;
+        // keep two chunks in flight: the slots they go to were stored at least one bulk group before the store above
+        bool waited = false;
+        for (int k = ahead + 1; k <= 2; ++k) {
+            int g, r0, bc;
+            if (!nth_next(i, k, g, r0, bc)) break;
+            if (!waited) { io_wait_stores_read_n<1>(); waited = true; }
+            if (lane == 0) request((cons + k - 1) % 3, g, r0, bc);
+            ahead = k;
+        }
+        *io.phase = (*io.phase & ~0xF00u) | (static_cast<uint32_t>(cons) << 8) | (static_cast<uint32_t>(ahead) << 10);
     }
     SC_DEVICE void finish() {
         if (c.row >= c.M) return;
@@ -347,9 +366,6 @@ struct EpiBackCodeHT {
         p.s_part[o] = s + s1;
     }
 };
-// Measured on the headline shape: H = 4 (16 epilogue warps, 640 threads, 96-register cap, 3 pipeline stages) is
-// 2.5 % slower per step than H = 2 - the epilogue and the mainloop are already balanced, more warps only add
-// per-tile overhead.
 using EpiBackCodeH = EpiBackCodeHT<2>;
 
 }  // namespace sc

@@ -342,7 +342,7 @@ int sae_step_f16_impl(const ScStepArgs& a) {
         SC_TRY(io_map_h(&ep.c_map, c_h, N, B, M, NB, ldb));
         ep.bias = a.bias; ep.l1_part = w.l1_part; ep.dict_size = a.dict_size;
         ep.fold_inv = fold_inv; ep.code_scale = a.out_code_scale;
-        SC_TRY((run_gemm<false, false, EpiEncodeTH, true>(N, B, M, &s, 1, ep, st)));
+        SC_TRY((run_gemm_short_k<EpiEncodeTH>(N, B, M, &s, ep, st)));
     }
     prof_mark(st, "G1_encode");
     for (int rep = 0; rep < (dup_k == 2 ? 2 : 1); ++rep)
@@ -373,7 +373,7 @@ int sae_step_f16_impl(const ScStepArgs& a) {
         ep.l1 = a.l1_alpha; ep.bias = a.bias; ep.db_part = w.db_part; ep.s_part = w.s_part;
         ep.l1_scale = 0.5f * (float)d; ep.tied = a.tied; ep.feats = N;
         ep.fold_inv = fold_inv;
-        SC_TRY((run_gemm<false, false, EpiBackCodeH, true>(N, B, M, &s, 1, ep, st)));
+        SC_TRY((run_gemm_short_k<EpiBackCodeH>(N, B, M, &s, ep, st)));
     }
     prof_mark(st, "G3_back_code");
     {

@@ -68,7 +68,7 @@ struct EpiProbe {
     SC_DEVICE void prefetch(int) {}
     SC_DEVICE void chunk(int co, float (&v)[32], int) {
         const int lane = threadIdx.x & 31;
-        if (MODE >= 13 && lane == 0) {  // tile load issued at the start of the chunk, consumed at its end
+        if (MODE == 13 && lane == 0) {  // tile load issued at the start of the chunk, consumed at its end
             io_expect(io, 2048, 0);
             tma_load_3d(&p.map, io.bar, io.buf + 4096, c.col0 + co, c.row - lane, c.g);
         }
@@ -83,20 +83,45 @@ struct EpiProbe {
         }
         uint8_t* tile = io.buf + ((*io.phase >> 8) & 1u) * 2048;
         *io.phase ^= 1u << 8;
-        if (MODE >= 13) {
+        if (MODE == 13) {
             io_wait_loads(io, 0);
             const uint4 t = lds_128u(smem_u32(io.buf + 4096) + lane * 64);
             acc += __uint_as_float(t.x & 0x3f800000u);
         }
-        if (MODE >= 12) io_wait_stores_read_n<1>();
+        // 14: as 12 without the proxy fence (wrong, timing only); 15: four staging tiles, wait for the store four back;
+        // 16: every store goes to the same global tile (L2 hit, no HBM write); 17: 11 + the proxy fence alone;
+        // 18: as 12 with a plain st.global of the row instead of the TMA store
+        if (MODE == 15) {
+            tile = io.buf + ((*io.phase >> 9) & 3u) * 2048;
+            *io.phase += 1u << 9;
+            io_wait_stores_read_n<3>();
+        } else if (MODE >= 12 && MODE != 17 && MODE != 18) {
+            io_wait_stores_read_n<1>();
+        }
         io_write_row_h(tile, lane, v);
-        if (MODE >= 12) {
+        if (MODE == 14) {
+            __syncwarp();
+            if (lane == 0) tma_store_3d(&p.map, tile, c.col0 + co, c.row - lane, c.g);
+            io_commit();
+        } else if (MODE == 16) {
+            io_store_tile(&p.map, tile, 0, (c.row - lane) & 127, 0);
+            io_commit();
+        } else if (MODE == 17) {
+            fence_proxy_async_smem();
+            __syncwarp();
+        } else if (MODE == 18) {
+            uint32_t h[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) { const __half2 x = __floats2half2_rn(v[2 * j], v[2 * j + 1]); h[j] = *reinterpret_cast<const uint32_t*>(&x); }
+            __half* dst = reinterpret_cast<__half*>(p.C) + ((long long)c.g * c.M + c.row) * (2 * ((c.N + 3) & ~3)) + c.col0 + co;
+            if (c.row < c.M && c.col0 + co + 32 <= c.N) { stg_256(dst, h); stg_256(dst + 16, h + 8); }
+        } else if (MODE >= 12) {
             io_store_tile(&p.map, tile, c.col0 + co, c.row - lane, c.g);
             io_commit();
         } else {
             __syncwarp();
         }
-        if (MODE >= 13) __syncwarp();
+        if (MODE == 13) __syncwarp();
     }
     SC_DEVICE void finish() {
         if (acc == 123.456f) p.C[0] = acc;
@@ -115,6 +140,7 @@ static cudaError_t run(const GemmMaps& maps, const GemmShape& sh, const EpiStore
         if (make_io_map_h(&pp.map, ep.C, sh.M, sh.N, sh.G, (long long)sh.M * ep.ld * 2, &err, ep.ld * 2)) { printf("io map: %s\n", err); return cudaErrorInvalidValue; }
 #define PROBE(mode, h) if (g_null == mode && g_h == h) return launch_gemm_2cta<BN, A_MN, B_MN, EpiProbe<mode, h>, 2>(maps, sh, *reinterpret_cast<typename EpiProbe<mode, h>::Params*>(&pp), sms, 0);
         PROBE(10, 2) PROBE(11, 2) PROBE(12, 2) PROBE(13, 2) PROBE(10, 4) PROBE(11, 4) PROBE(12, 4) PROBE(13, 4)
+        PROBE(14, 2) PROBE(15, 2) PROBE(16, 2) PROBE(17, 2) PROBE(18, 2)
         return cudaErrorInvalidValue;
     }
     if (g_null == 20 || g_null == 21) {  // the train step's transposed encode epilogue, timed alone

@@ -13,8 +13,9 @@ metric = member-activations per second = B * M_total / step_time.
   e2e   : through the public API with the batch in pinned HOST memory, H2D copy of the batch and
           D2H read of the loss scalars inside the timed region
   roofline    : dominant kernel's algorithmic flops / its CUDA-event time vs the measured TF32 dense peak
-  cpu_baseline: the CPU oracle (oracle/restated.py, a port of the reference's torch path) on the host cores
---impl reference times that same CPU port with all host threads and prints the same line shape.
+  cpu_baseline: the reference's own FunctionalEnsemble.step_batch (oracle/_ref, unmodified files) on the host cores,
+                on the same B rows per step; the CPU port (oracle/restated.py) beside it as port_value
+--impl reference times the reference's own code with all host threads on the same workload and prints the same line shape.
 """
 import argparse
 import json
@@ -75,24 +76,70 @@ def cpu_port_steps(batch, steps, warmup, threads):
     return batch * M_PER_GPU * steps / dt, dt / steps
 
 
+def reference_available():
+    """The reference's own modules under oracle/_ref (copied there by oracle/build_ref.py; they travel with the
+    snapshot - /root/reference is never read at run time)."""
+    from oracle import build_ref
+    return build_ref.available()
+
+
+def cpu_reference_steps(batch, steps, warmup, threads, budget_s=None):
+    """Time the UNMODIFIED reference - its FunctionalEnsemble.step_batch (autoencoders/ensemble.py:175-193) over
+    FunctionalSAE (sae_ensemble.py:13-77) with torchopt-style Adam - on the host cores: the same workload as the GPU
+    arm (M members, d, N, `batch` rows per step).  With `budget_s` the timed steps stop early once the budget is spent
+    (at least 2 are run).  Returns (member-activations / s, seconds per step, steps timed)."""
+    os.environ["SC_REFERENCE_ROOT"] = os.path.join(ROOT, "oracle", "_ref")
+    from oracle import ref_loader
+    import warnings
+    warnings.filterwarnings("ignore", message=".*batching rule.*")
+    ns = ref_loader.load()
+    torch.set_num_threads(threads)
+    torch.manual_seed(0)
+    models = [ns.FunctionalSAE.init(D_ACT, N_FEATS, float(l1)) for l1 in l1_values(M_PER_GPU)]
+    ens = ns.FunctionalEnsemble(models, ns.FunctionalSAE, ns.torchopt.adam, {"lr": 1e-3}, device="cpu")
+    data = make_chunk(batch * 4, D_ACT, 1, "cpu")
+    for i in range(warmup):
+        ens.step_batch(data[(i % 4) * batch:(i % 4 + 1) * batch])
+    done = 0
+    t0 = time.perf_counter()
+    for i in range(steps):
+        ens.step_batch(data[(i % 4) * batch:(i % 4 + 1) * batch])
+        done += 1
+        if budget_s is not None and done >= 2 and time.perf_counter() - t0 > budget_s:
+            break
+    dt = time.perf_counter() - t0
+    return batch * M_PER_GPU * done / dt, dt / done, done
+
+
 def run_reference(args):
+    """CPU arm: the reference's own code on the box's host cores, same workload (B rows per step, M members), the
+    driver's --steps / --warmup (the timed steps stop after ~150 s if that many do not fit; `steps` says how many ran)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     threads = os.cpu_count() or 1
-    sample_b = min(args.batch, 512)
-    steps = max(1, min(args.steps, 12))
-    warmup = max(1, min(args.warmup, 2))
-    val, sec = cpu_port_steps(sample_b, steps, warmup, threads)
-    sample = (f"{steps} steps of {sample_b} rows (of the B={args.batch} workload) x {M_PER_GPU} members, "
-              f"oracle/restated.py torch-CPU fp32, {threads} threads")
+    B = args.batch
+    warmup = max(1, args.warmup)
+    if reference_available():
+        kind = "reference"
+        val, sec, steps = cpu_reference_steps(B, args.steps, warmup, threads, budget_s=150.0)
+        what = "the reference's FunctionalEnsemble.step_batch (oracle/_ref/autoencoders/*.py, unmodified; optree / torchopt / torchtyping from oracle/shims)"
+        port_val, _ = cpu_port_steps(B, 2, 1, threads)
+    else:
+        kind = "port"
+        steps = max(2, min(args.steps, 40))
+        val, sec = cpu_port_steps(B, steps, warmup, threads)
+        what = "oracle/restated.py (CPU port of the reference path; oracle/_ref is missing)"
+        port_val = val
+    sample = f"{steps} steps of {B} rows x {M_PER_GPU} members after {warmup} warm-up, {what}, torch CPU fp32, {threads} threads"
     line = {
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
         "warmup": warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "pythia70m_l2_untied_sae", "d": D_ACT, "n_feats": N_FEATS, "members": M_PER_GPU,
-                   "batch": args.batch, "sample_batch": sample_b},
-        "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+        "config": {"workload": "pythia70m_l2_untied_sae", "d": D_ACT, "n_feats": N_FEATS, "members_per_gpu": M_PER_GPU,
+                   "batch": B},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": kind, "sample": sample,
+                         "port_value": port_val},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -362,10 +409,18 @@ def run_ours(args):
     roofline["by_batch"] = by_batch
 
     threads = os.cpu_count() or 1
-    cpu_b = min(B, 512)
-    cpu_val, cpu_sec = cpu_port_steps(cpu_b, 3, 1, threads)
-    cpu_baseline = {"value": cpu_val, "unit": UNIT, "cores": threads, "kind": "port",
-                    "sample": f"3 steps of {cpu_b} rows x {M} members after 1 warm-up, oracle/restated.py torch-CPU fp32"}
+    if reference_available():
+        cpu_val, cpu_sec, cpu_n = cpu_reference_steps(B, 3, 1, threads)
+        port_val, _ = cpu_port_steps(B, 2, 1, threads)
+        cpu_baseline = {"value": cpu_val, "unit": UNIT, "cores": threads, "kind": "reference", "port_value": port_val,
+                        "sample": f"{cpu_n} steps of {B} rows x {M} members after 1 warm-up: the reference's own "
+                                  "FunctionalEnsemble.step_batch (oracle/_ref, unmodified) on torch CPU fp32; port_value = "
+                                  "oracle/restated.py on the same batch"}
+    else:
+        cpu_val, cpu_sec = cpu_port_steps(B, 3, 1, threads)
+        cpu_baseline = {"value": cpu_val, "unit": UNIT, "cores": threads, "kind": "port",
+                        "sample": f"3 steps of {B} rows x {M} members after 1 warm-up, oracle/restated.py torch-CPU fp32 "
+                                  "(oracle/_ref missing)"}
 
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,

@@ -104,6 +104,13 @@ typedef struct {
      * ||W_d|| here, 1 in every other mode. */
     int32_t operands_valid;
     float* out_code_scale;
+    /* operand_format 1 range guard: fp16 holds |x| <= 65504.  Every conversion to fp16 in the engine saturates (no
+     * infinity is ever stored, so an outlier costs accuracy on that element instead of turning the step into NaNs),
+     * and when the batch holds a value beyond the range (or a non-finite one) the step does
+     * atomicMax(*range_flag, step_tag).  range_flag: device int32 or NULL; the caller reads it when it likes (no sync
+     * in the step) and switches to operand_format 0 - the host mirror does that in its "auto" mode. */
+    int32_t* range_flag;
+    int32_t step_tag;
 } ScStepArgs;
 
 size_t sc_sae_step_workspace_bytes(int32_t M, int32_t B, int32_t d, int32_t N, int32_t tied, int32_t x_per_member);

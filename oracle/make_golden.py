@@ -114,15 +114,34 @@ def fista_case(ns, seed):
     return out
 
 
+def metrics_extra_case(ns):
+    """fraction_variance_unexplained_top_activating (standard_metrics.py:314-340) and r_squared (:342-343) on the models
+    and data of inference.pt (read back from that fixture, so the two files describe the same inputs)."""
+    g = torch.load(os.path.join(OUT, "inference.pt"), weights_only=False)
+    ld = ns.UntiedSAE(g["We"], g["Wd"], g["b"])
+    tr, rot, scale = g["tied_centering"]
+    tied = ns.TiedSAE(g["We"].clone(), g["b"].clone(), centering=(tr, rot, scale), norm_encoder=True)
+    out = {}
+    for name, m in (("untied", ld), ("tied", tied)):
+        out[name] = {"r_squared": ns.r_squared(m, g["x"]),
+                     "fvu_top_2": ns.fraction_variance_unexplained_top_activating(m, g["x"], n_top=2),
+                     "fvu_top_7": ns.fraction_variance_unexplained_top_activating(m, g["x"], n_top=7)}
+    return out
+
+
 def main():
     ns = ref_loader.load()
     os.makedirs(OUT, exist_ok=True)
+    if "--metrics-extra-only" in sys.argv:  # added later: leaves the older fixtures byte-identical
+        torch.save(metrics_extra_case(ns), os.path.join(OUT, "metrics_extra.pt"))
+        return
     torch.save(ensemble_case(ns, "untied", 100), os.path.join(OUT, "ensemble_untied.pt"))
     torch.save(ensemble_case(ns, "tied", 200), os.path.join(OUT, "ensemble_tied.pt"))
     torch.save(ensemble_case(ns, "masked_untied", 500), os.path.join(OUT, "ensemble_masked_untied.pt"))
     torch.save(ensemble_case(ns, "masked_tied", 600), os.path.join(OUT, "ensemble_masked_tied.pt"))
     torch.save(inference_case(ns, 300), os.path.join(OUT, "inference.pt"))
     torch.save(fista_case(ns, 400), os.path.join(OUT, "fista.pt"))
+    torch.save(metrics_extra_case(ns), os.path.join(OUT, "metrics_extra.pt"))
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

@@ -1,10 +1,10 @@
-"""Load the UNMODIFIED reference hot-path modules on CPU.  TEST INFRASTRUCTURE.
+"""Load the UNMODIFIED reference hot-path modules on CPU.  TEST / BASELINE INFRASTRUCTURE.
 
-Only usable where /root/reference exists (the build container).  Nothing under
-`-m gpu`, `smoke()` or `bench.py` may import this module: the GPU box has no
-/root/reference.  It is used (a) by `-m "not gpu"` tests to validate
-`oracle/restated.py` against the real reference code and (b) by
-`oracle/make_golden.py` to generate the fixtures under tests/golden/.
+Two sources: /root/reference (the build container only: `-m "not gpu"` tests validate `oracle/restated.py`
+against the real reference code, `oracle/make_golden.py` generates the fixtures under tests/golden/), and
+oracle/_ref (byte-for-byte copies of the four hot-path modules made by oracle/build_ref.py; they travel to the GPU
+box, where `bench.py --impl reference` and its `cpu_baseline` leg time the reference's own
+FunctionalEnsemble.step_batch on the host cores).  Nothing under sparse_coding__b200/ imports this module.
 
 The reference imports three packages that are not installed (no network):
 optree, torchopt, torchtyping -> `oracle/shims/`.  `big_sweep.py` and
@@ -17,12 +17,21 @@ import importlib
 import os
 import sys
 
-REFERENCE_ROOT = os.environ.get("SC_REFERENCE_ROOT", "/root/reference")
-_SHIMS = os.path.join(os.path.dirname(os.path.abspath(__file__)), "shims")
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SHIMS = os.path.join(_HERE, "shims")
+_FULL = os.environ.get("SC_REFERENCE_ROOT", "/root/reference")
+_VENDORED = os.path.join(_HERE, "_ref")
+# the full tree when it is there (build container), else the four vendored modules
+REFERENCE_ROOT = _FULL if os.path.isfile(os.path.join(_FULL, "autoencoders", "ensemble.py")) else _VENDORED
 
 
 def available() -> bool:
     return os.path.isfile(os.path.join(REFERENCE_ROOT, "autoencoders", "ensemble.py"))
+
+
+def full_tree() -> bool:
+    """big_sweep.py / standard_metrics.py are there as well (only in the build container)."""
+    return os.path.isfile(os.path.join(REFERENCE_ROOT, "standard_metrics.py"))
 
 
 _loaded = {}
@@ -78,6 +87,16 @@ def load():
         g.update(extra_globals)
         exec(compile(mod, os.path.join(REFERENCE_ROOT, path), "exec"), g)
         return {n: g[n] for n in names}
+
+    if not full_tree():  # oracle/_ref: the four modules of the train step only
+        ns._modules = {k: v for k, v in sys.modules.items()
+                       if k == "autoencoders" or k.startswith("autoencoders.") or k in ("torchopt", "optree", "torchtyping")}
+        for k in ns._modules:
+            sys.modules.pop(k, None)
+        sys.modules.update(saved)
+        sys.path[:] = saved_path
+        _loaded["ns"] = ns
+        return ns
 
     class _Any:
         def __class_getitem__(cls, item):

@@ -54,6 +54,7 @@ class ScStepArgs(C.Structure):
         ("rs_grad_enc", C.c_void_p * 8), ("rs_grad_dec", C.c_void_p * 8),
         ("rs_grad_bias", C.c_void_p * 8), ("rs_losses", C.c_void_p * 8),
         ("operands_valid", C.c_int32), ("out_code_scale", C.c_void_p),
+        ("range_flag", C.c_void_p), ("step_tag", C.c_int32),
     ]
 
 

@@ -179,6 +179,8 @@ class FunctionalEnsemble:
         self.optim_states = state_dict["optim_states"]
         self.reference_faithful = state_dict.get("reference_faithful", True)
         self.init_functions()
+        if not self.reference_faithful:  # textbook Adam continues from the stored step count
+            self._step = int(self.optim_states[0].count["encoder"].max())
         return self
 
     def unstack(self, device=None):
@@ -189,7 +191,7 @@ class FunctionalEnsemble:
 
     def state_dict(self):
         """ensemble.py:150-161 (same nine keys)."""
-        return {
+        sd = {
             "device": self.device,
             "n_models": self.n_models,
             "params": self.params,
@@ -200,6 +202,9 @@ class FunctionalEnsemble:
             "optimizer_kwargs": self.optimizer_kwargs,
             "optim_states": self.optim_states,
         }
+        if not self.reference_faithful:  # a tenth key only for the non-default (textbook Adam) mode
+            sd["reference_faithful"] = False
+        return sd
 
     def _map_state(self, fn):
         st = self.optim_states[0]
@@ -277,6 +282,23 @@ class FunctionalEnsemble:
             hit = cache[key]
         return hit[1]
 
+    def _check_prefix_mask(self, dict_size):
+        """The fused step masks feature n of member m iff n >= dict_size[m]; the reference masks with
+        buffers["coef_mask"] (sae_ensemble.py:356, :425), which `init` writes as exactly that prefix mask.  A caller
+        who edits coef_mask to anything else would be silently ignored here, so check (once per buffer version)."""
+        cm = self.buffers.get("coef_mask")
+        if cm is None:
+            return
+        key = (cm.data_ptr(), cm._version, dict_size.data_ptr(), self.buffers["dict_size"]._version)
+        if getattr(self, "_mask_key", None) == key:
+            return
+        N = cm.shape[-1]
+        want = torch.arange(N, device=cm.device)[None, :] >= dict_size.to(cm.device)[:, None]
+        if not torch.equal(cm.to(torch.bool).reshape(self.n_models, N), want):
+            raise NotImplementedError("buffers['coef_mask'] is not the prefix mask arange(N) >= dict_size that init writes; "
+                                      "the fused step only implements that form")
+        self._mask_key = key
+
     def _centered_batch(self, x: torch.Tensor, expand: bool):
         """FunctionalTiedSAE.center (sae_ensemble.py:126-127) with per-member buffers.  Identity
         buffers (the default, :97-108) skip it; otherwise the batch is centred once per step with a
@@ -294,6 +316,46 @@ class FunctionalEnsemble:
         xm = x.unsqueeze(0) if expand else x
         xc = torch.einsum("mcu,mbu->mbc", rot, xm - tr[:, None, :]) * sc[:, None, :]
         return xc.contiguous(), True
+
+    # ------------------------------------------------------------------ fp16 range guard
+    def _poll_range_flag(self, device):
+        """fp16 operands hold |x| <= 65504.  The step saturates instead of overflowing and raises a device flag
+        (ScStepArgs.range_flag) when a batch leaves that range; the flag travels to pinned host memory every few steps
+        without a sync, and is looked at here before the next launch: "auto" then continues with TF32 operands (which
+        have fp32's range), an explicit "f16" keeps going and warns."""
+        if getattr(self, "_range_flag", None) is None or self._range_flag.device != torch.device(device):
+            self._range_flag = torch.zeros(1, dtype=torch.int32, device=device)
+            self._range_host = torch.zeros(1, dtype=torch.int32).pin_memory()
+            self._range_tag, self._range_seen, self._range_event = 0, 0, None
+        self._range_tag += 1
+        if self._range_event is not None and self._range_event.query():
+            self._range_event = None
+            self._handle_range_flag(int(self._range_host[0]))
+        if self._range_event is None and self._range_tag % 8 == 0:
+            self._range_host.copy_(self._range_flag, non_blocking=True)
+            self._range_event = torch.cuda.Event()
+            self._range_event.record(torch.cuda.current_stream(device))
+
+    def _handle_range_flag(self, tag):
+        if tag <= self._range_seen:
+            return
+        first, self._range_seen = tag, tag
+        import warnings
+        if self.operand_format == "auto":
+            self.operand_format = "tf32"
+            warnings.warn(f"a batch (step {first} of this ensemble) held activations beyond the fp16 range (|x| > 65504 or "
+                          "non-finite); they were saturated in that step.  operand_format 'auto' continues with TF32 operands.")
+        else:
+            warnings.warn(f"a batch (step {first}) held activations beyond the fp16 range (|x| > 65504 or non-finite); they "
+                          "were saturated.  Use operand_format 'tf32' for such data.")
+
+    def check_operand_range(self):
+        """One sync: look at the fp16 range flag now (what `_poll_range_flag` does lazily).  Returns True when every
+        batch so far was inside the fp16 range."""
+        if getattr(self, "_range_flag", None) is None:
+            return True
+        self._handle_range_flag(int(self._range_flag.item()))
+        return self._range_seen == 0
 
     def step_batch(self, minibatches, expand_dims=True):
         """ensemble.py:175-193.  Returns (loss_dict of [M] tensors, {"c": [M,B,N]})."""
@@ -351,8 +413,9 @@ class FunctionalEnsemble:
         M = self.n_models
         x = minibatches
         nat.require_cuda(x, "minibatches")
-        if self.no_stacking and expand_dims:
-            # reference ensemble.py:100-116 indexes batch[i] per member in this mode
+        if self.no_stacking and expand_dims and x.dim() == 3:
+            # reference ensemble.py:100-116 indexes batch[i] per member in this mode; a 2-D batch is expanded to
+            # [M,B,d] first (ensemble.py:177-178), which is the shared-batch path here
             expand_dims = False
         if expand_dims:
             if x.dim() != 2:
@@ -387,6 +450,7 @@ class FunctionalEnsemble:
             # the masked losses carry no bias-decay term (sae_ensemble.py:360-361, :429-430)
             bd = torch.zeros(M, dtype=torch.float32, device=x.device)
             dict_size = self.buffers["dict_size"].to(device=x.device, dtype=torch.int32).contiguous()
+            self._check_prefix_mask(dict_size)
 
         adam = self.adam_constants(advance=not grad_only)
         grads = None
@@ -404,6 +468,9 @@ class FunctionalEnsemble:
         fmt = self.operand_format
         if fmt not in ("auto", "tf32", "f16"):
             raise ValueError(f"operand_format {fmt!r}: expected 'auto', 'tf32' or 'f16'")
+        if fmt != "tf32":
+            self._poll_range_flag(x.device)
+            fmt = self.operand_format  # "auto" falls back to "tf32" once a batch has left the fp16 range
         f16 = fmt != "tf32" and bool(L.sc_sae_step_f16_supported(B, d, N))
         if fmt == "f16" and not f16:
             raise ValueError(f"operand_format 'f16' needs d, N multiples of 64 and >= 128 and B > 64 (got B={B} d={d} N={N})")
@@ -437,6 +504,7 @@ class FunctionalEnsemble:
             B_total=int(batch_total),
             operand_format=int(f16), out_c_half=nat.ptr(c_half), dict_size=nat.ptr(dict_size),
             operands_valid=int(ops_valid), out_code_scale=nat.ptr(code_scale),
+            range_flag=nat.ptr(self._range_flag) if f16 else None, step_tag=self._range_tag if f16 else 0,
         )
         if reduce_scatter is not None:
             rs = reduce_scatter

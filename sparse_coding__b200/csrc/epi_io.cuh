@@ -98,7 +98,7 @@ SC_DEVICE void io_write_row_h(uint8_t* tile, int r, const float (&v)[32]) {
         uint32_t h[4];
 #pragma unroll
         for (int t = 0; t < 4; ++t) {
-            const __half2 p = __floats2half2_rn(v[8 * j + 2 * t], v[8 * j + 2 * t + 1]);
+            const __half2 p = half2_sat(v[8 * j + 2 * t], v[8 * j + 2 * t + 1]);
             h[t] = *reinterpret_cast<const uint32_t*>(&p);
         }
         sts_128u(row + ((j ^ ((r >> 1) & 3)) << 4), h[0], h[1], h[2], h[3]);

@@ -538,7 +538,7 @@ struct EpiAdamT {
             uint32_t hh[4];
 #pragma unroll
             for (int t = 0; t < 4; ++t) {
-                const __half2 x = __floats2half2_rn(pv[8 * j + 2 * t], pv[8 * j + 2 * t + 1]);
+                const __half2 x = half2_sat(pv[8 * j + 2 * t], pv[8 * j + 2 * t + 1]);
                 hh[t] = *reinterpret_cast<const uint32_t*>(&x);
             }
             sts_128u(row + (((4 * hsel + h * (W / 8) + j) ^ (lane & 7)) << 4), hh[0], hh[1], hh[2], hh[3]);

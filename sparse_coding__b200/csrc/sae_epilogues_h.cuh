@@ -111,7 +111,7 @@ struct EpiDecodeH {
                 for (int t = 0; t < 4; ++t) {
                     const float r0 = v[8 * j + 2 * t] - xv[8 * j + 2 * t], r1 = v[8 * j + 2 * t + 1] - xv[8 * j + 2 * t + 1];
                     sum += r0 * r0 + r1 * r1;
-                    h[t] = __floats2half2_rn(r0, r1);
+                    h[t] = half2_sat(r0, r1);
                 }
                 reinterpret_cast<uint4*>(dst)[j] = *reinterpret_cast<uint4*>(h);
             }
@@ -121,7 +121,7 @@ struct EpiDecodeH {
                 if (j < ncols) {
                     const float r = v[j] - xv[j];
                     sum += r * r;
-                    dst[j] = __float2half_rn(r);
+                    dst[j] = half_sat(r);
                 }
             }
         }
@@ -315,7 +315,7 @@ struct EpiBackCodeHT {
                 const float t1 = cf.y > 0.f ? q1 + l1_term : q1;
                 const float d0 = __float_as_int(cf.x) < 0 ? 0.f : t0;
                 const float d1 = __float_as_int(cf.y) < 0 ? 0.f : t1;
-                const __half2 dh = __floats2half2_rn(d0, d1);
+                const __half2 dh = half2_sat(d0, d1);
                 o[t] = *reinterpret_cast<const uint32_t*>(&dh);
                 db += d0; db1 += d1;
                 s = fmaf(cf.x, q0, s); s1 = fmaf(cf.y, q1, s1);

@@ -17,7 +17,7 @@ __global__ void to_half_kernel(const float4* __restrict__ in, uint2* __restrict_
     pdl_wait();
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
         const float4 v = in[i];
-        __half2 h[2] = {__floats2half2_rn(v.x, v.y), __floats2half2_rn(v.z, v.w)};
+        __half2 h[2] = {half2_sat(v.x, v.y), half2_sat(v.z, v.w)};
         out[i] = *reinterpret_cast<uint2*>(h);
     }
 }
@@ -59,7 +59,7 @@ __global__ void prep_params_h_kernel(const float* __restrict__ enc, __half* __re
         uint2* dst = reinterpret_cast<uint2*>(enc_h + row);
         for (int i = lane; i < d4; i += 32) {
             const float4 v = src[i];
-            __half2 h[2] = {__floats2half2_rn(v.x, v.y), __floats2half2_rn(v.z, v.w)};
+            __half2 h[2] = {half2_sat(v.x, v.y), half2_sat(v.z, v.w)};
             dst[i] = *reinterpret_cast<uint2*>(h);
         }
     }
@@ -76,7 +76,7 @@ __global__ void prep_params_h_kernel(const float* __restrict__ enc, __half* __re
     uint2* dst = reinterpret_cast<uint2*>(D_h + row);
     for (int i = lane; i < d4; i += 32) {
         const float4 v = src[i];
-        __half2 h[2] = {__floats2half2_rn(v.x * inv, v.y * inv), __floats2half2_rn(v.z * inv, v.w * inv)};
+        __half2 h[2] = {half2_sat(v.x * inv, v.y * inv), half2_sat(v.z * inv, v.w * inv)};
         dst[i] = *reinterpret_cast<uint2*>(h);
     }
 }
@@ -93,7 +93,7 @@ __global__ void __launch_bounds__(256) step_prologue_h_kernel(const float* __res
                                                               __half* __restrict__ D_h, float* __restrict__ inv_norm, int N,
                                                               int d, float4* __restrict__ zero, long long zero_n4,
                                                               int fold, const float* __restrict__ wsq, int wsq_parts,
-                                                              int norm_blocks) {
+                                                              int norm_blocks, int* __restrict__ range_flag, int step_tag) {
     pdl_launch_dependents();
     pdl_wait();
     __shared__ float sh[8];
@@ -110,11 +110,15 @@ __global__ void __launch_bounds__(256) step_prologue_h_kernel(const float* __res
     }
     blk -= M;
     if (blk < x_blocks) {
+        bool out_of_range = false;
         for (long long i = blk * (long long)blockDim.x + threadIdx.x; i < x_n4; i += (long long)x_blocks * blockDim.x) {
             const float4 v = x[i];
-            __half2 h[2] = {__floats2half2_rn(v.x, v.y), __floats2half2_rn(v.z, v.w)};
+            // fp16 holds |x| <= 65504: larger (or non-finite) activations are saturated by the conversion and reported
+            out_of_range |= !(fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w))) <= 65504.f);
+            __half2 h[2] = {half2_sat(v.x, v.y), half2_sat(v.z, v.w)};
             x_h[i] = *reinterpret_cast<uint2*>(h);
         }
+        if (range_flag && __any_sync(0xffffffffu, out_of_range) && (threadIdx.x & 31) == 0) atomicMax(range_flag, step_tag);
         // split-K decode accumulates into this buffer (EpiReduceTile): clear it here instead of in a memset node
         for (long long i = blk * (long long)blockDim.x + threadIdx.x; i < zero_n4; i += (long long)x_blocks * blockDim.x)
             zero[i] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -147,7 +151,7 @@ __global__ void __launch_bounds__(256) step_prologue_h_kernel(const float* __res
         uint2* dst = reinterpret_cast<uint2*>(enc_h + row);
         for (int i = lane; i < d4; i += 32) {
             const float4 v = src[i];
-            __half2 h[2] = {__floats2half2_rn(v.x, v.y), __floats2half2_rn(v.z, v.w)};
+            __half2 h[2] = {half2_sat(v.x, v.y), half2_sat(v.z, v.w)};
             dst[i] = *reinterpret_cast<uint2*>(h);
         }
     }
@@ -165,7 +169,7 @@ __global__ void __launch_bounds__(256) step_prologue_h_kernel(const float* __res
     uint2* dst = reinterpret_cast<uint2*>(D_h + row);
     for (int i = lane; i < d4; i += 32) {
         const float4 v = src[i];
-        __half2 h[2] = {__floats2half2_rn(v.x * inv, v.y * inv), __floats2half2_rn(v.z * inv, v.w * inv)};
+        __half2 h[2] = {half2_sat(v.x * inv, v.y * inv), half2_sat(v.z * inv, v.w * inv)};
         dst[i] = *reinterpret_cast<uint2*>(h);
     }
 }
@@ -185,7 +189,7 @@ __global__ void __launch_bounds__(256) residual_h_kernel(const float4* __restric
         const float4 a = x_hat[m * n4 + i], b = x[m * x_mstride4 + i];
         const float r0 = a.x - b.x, r1 = a.y - b.y, r2 = a.z - b.z, r3 = a.w - b.w;
         acc += (r0 * r0 + r1 * r1) + (r2 * r2 + r3 * r3);
-        __half2 h[2] = {__floats2half2_rn(r0, r1), __floats2half2_rn(r2, r3)};
+        __half2 h[2] = {half2_sat(r0, r1), half2_sat(r2, r3)};
         r_h[m * n4 + i] = *reinterpret_cast<uint2*>(h);
     }
     const float t = block_sum(acc, sh);
@@ -328,11 +332,11 @@ int sae_step_f16_impl(const ScStepArgs& a) {
         if (a.tied)
             launch_k(step_prologue_h_kernel, dim3(blocks), dim3(256), 0, st, a.bias, w.bnorm, M, reinterpret_cast<const float4*>(a.x),
                      reinterpret_cast<uint2*>(w.x_h), x_n4, x_blocks, nullptr, nullptr, a.enc, w.D_h, w.inv_norm, N, d, zero, zero_n4,
-                     0, nullptr, 0, 0);
+                     0, nullptr, 0, 0, a.range_flag, a.step_tag);
         else
             launch_k(step_prologue_h_kernel, dim3(blocks), dim3(256), 0, st, a.bias, w.bnorm, M, reinterpret_cast<const float4*>(a.x),
                      reinterpret_cast<uint2*>(w.x_h), x_n4, x_blocks, a.enc, w.enc_h, a.dec, w.D_h, w.inv_norm, N, d, zero, zero_n4,
-                     fold ? 1 : 0, w.wsq, w.wsq_parts, norm_blocks);
+                     fold ? 1 : 0, w.wsq, w.wsq_parts, norm_blocks, a.range_flag, a.step_tag);
         SC_CUDA(cudaGetLastError(), "prologue launch");
     }
     prof_mark(st, "prologue");

@@ -5,6 +5,7 @@
 // "Shared memory matrix descriptor" and "Instruction descriptor" for .kind::tf32.
 #pragma once
 #include <cuda.h>
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -278,6 +279,16 @@ __host__ __device__ constexpr uint32_t make_idesc_f16(int m, int n, bool a_mn, b
 }
 
 // ----------------------------------------------------------------------------- numerics helpers
+// fp32 -> fp16, round to nearest even, SATURATING at +-65504 (F2FP.SATFINITE, the same single instruction as the plain
+// conversion): no fp16 tensor of the engine can hold an infinity, so an out-of-range value costs accuracy on that
+// element but never turns a GEMM into NaNs.  A NaN input stays a NaN.
+SC_DEVICE __half2 half2_sat(float lo, float hi) {
+    uint32_t r;
+    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+    return *reinterpret_cast<__half2*>(&r);
+}
+SC_DEVICE __half half_sat(float x) { return __low2half(half2_sat(x, 0.f)); }
+
 // Round-to-nearest-even fp32 -> TF32 (10 explicit mantissa bits), kept in an fp32 container.
 // The tensor core ignores the low 13 bits (truncation, biased); every operand this engine
 // feeds to tcgen05 is pre-rounded with this so products are unbiased (see DESIGN.md "Precision").

@@ -9,7 +9,7 @@ import torch
 from oracle import ref_loader
 
 warnings.filterwarnings("ignore")
-needs_ref = pytest.mark.skipif(not ref_loader.available(), reason="/root/reference not present on this machine")
+needs_ref = pytest.mark.skipif(not (ref_loader.available() and ref_loader.full_tree()), reason="/root/reference not present on this machine")
 
 
 def test_device_sampler_covers_every_row_once():

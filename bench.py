@@ -210,6 +210,171 @@ def measure_tf32_peak(device):
     return 2.0 * n ** 3 / (best * 1e-3) / 1e12
 
 
+
+# ------------------------------------------------------------------------------------------ secondary measurements
+def timed_ms(fn, warm, steps, device):
+    """Mean milliseconds per call of fn(i): CUDA events on the current stream after `warm` untimed calls."""
+    for i in range(warm):
+        fn(i)
+    torch.cuda.synchronize(device)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        fn(i)
+    e1.record()
+    torch.cuda.synchronize(device)
+    return e0.elapsed_time(e1) / steps
+
+
+def ensemble_ms(sc, sig, M, d, N, B, device, fmt="auto", read_c=False, warm=6, steps=30):
+    """ms per FunctionalEnsemble.step_batch of M members (L1 sweep) on fresh synthetic batches of B rows."""
+    torch.manual_seed(1)
+    models = [sig.init(d, N, float(l1), device=device) for l1 in l1_values(M)]
+    ens = sc.FunctionalEnsemble(models, sig, sc.torchopt_compat.adam, {"lr": 1e-3}, device=device)
+    ens.operand_format = fmt
+    data = torch.randn(4 * B, d, device=device)
+
+    def step(i):
+        _, aux = ens.step_batch(data[(i % 4) * B:(i % 4 + 1) * B])
+        if read_c:
+            aux["c"]
+    ms = timed_ms(step, warm, steps, device)
+    used = ens.last_operand_format
+    del ens, data, models
+    torch.cuda.empty_cache()
+    return ms, used
+
+
+def extras_one_gpu(sc, device, B, hbm_peak, tensor_peak, tf32_peak):
+    """The other BASELINE.json configurations and the variants of the headline step a reader would ask for, each a
+    short CUDA-event run on this GPU (rank 0, single-GPU runs only)."""
+    from oracle import restated as R
+    ex = {}
+    flops = lambda M, d, N, b: 10.0 * b * N * d * M
+    # headline step with aux["c"] read as float32 [M,B,N] every step (the reference returns it, sae_ensemble.py:73-75)
+    ms, _ = ensemble_ms(sc, sc.FunctionalSAE, M_PER_GPU, D_ACT, N_FEATS, B, device, read_c=True)
+    ex["with_c"] = {"ms_per_step": ms, "member_act_per_s": B * M_PER_GPU / ms * 1e3,
+                    "note": "aux['c'] materialised every step: + one fp16 -> fp32 transposing pass, 4*M*B*N bytes written"}
+    ms, used = ensemble_ms(sc, sc.FunctionalSAE, M_PER_GPU, D_ACT, N_FEATS, B, device, fmt="tf32")
+    ex["tf32"] = {"ms_per_step": ms, "member_act_per_s": B * M_PER_GPU / ms * 1e3, "operand_format": used,
+                  "step_tflops": flops(M_PER_GPU, D_ACT, N_FEATS, B) / ms * 1e-9,
+                  "frac_of_tf32_peak": flops(M_PER_GPU, D_ACT, N_FEATS, B) / ms * 1e-9 / tf32_peak}
+    # config 1: toy tied ensemble (generate_test_data shape), config 3: one GPU's share of the 32-member GPT-2 sweep
+    for name, sig, M, d, N, b in (("c1_toy_tied", sc.FunctionalTiedSAE, 4, 256, 512, 4096),
+                                  ("c3_share_tied", sc.FunctionalTiedSAE, 4, 768, 6144, 2048),
+                                  ("c3_share_untied", sc.FunctionalSAE, 4, 768, 6144, 2048)):
+        ms, used = ensemble_ms(sc, sig, M, d, N, b, device)
+        tf = flops(M, d, N, b) / ms * 1e-9
+        ex[name] = {"M": M, "d": d, "N": N, "B": b, "ms_per_step": ms, "member_act_per_s": b * M / ms * 1e3,
+                    "step_tflops": tf, "frac_of_tensor_peak": tf / tensor_peak, "operand_format": used}
+    # config 5 on one GPU: the single large dictionary, 8192 rows per step
+    ms, used = ensemble_ms(sc, sc.FunctionalSAE, 1, 2048, 65536, 8192, device, warm=3, steps=8)
+    tf = flops(1, 2048, 65536, 8192) / ms * 1e-9
+    ex["c5_one_gpu"] = {"d": 2048, "N": 65536, "B": 8192, "ms_per_step": ms, "activations_per_s": 8192 / ms * 1e3,
+                        "step_tflops": tf, "frac_of_tensor_peak": tf / tensor_peak, "operand_format": used}
+    # config 4: FISTA, 300 iterations on 8192 rows
+    Bf, d, N, iters = 8192, 512, 4096, 300
+    torch.manual_seed(2)
+    D = torch.randn(N, d, device=device)
+    D /= D.norm(dim=1, keepdim=True)
+    x = torch.randn(Bf, d, device=device)
+    a0 = torch.relu(x @ D.T - 1.0)
+    l1 = torch.tensor(1e-3, device=device)
+    run = lambda i: sc.FunctionalFista.fista(x, D, l1, a0, iters, device)
+    ms = timed_ms(run, 1, 2, device)
+    per_iter = ms / iters
+    t0 = time.perf_counter()
+    R.fista(x.cpu(), D.cpu(), 1e-3, a0.cpu(), 10)
+    cpu_iter = (time.perf_counter() - t0) / 10
+    ex["fista_c4"] = {"B": Bf, "d": d, "N": N, "iterations": iters, "seconds": ms * 1e-3, "ms_per_iteration": per_iter,
+                      "products": "3xTF32 (hi/lo split, fp32-accurate)",
+                      "tflops_fp32_equivalent": 4.0 * Bf * N * d / per_iter * 1e-9,
+                      "frac_of_tf32_peak_3_passes": 3 * 4.0 * Bf * N * d / per_iter * 1e-9 / tf32_peak,
+                      "alg_GBps": 16.0 * Bf * N / per_iter * 1e-6, "frac_of_hbm_peak": 16.0 * Bf * N / per_iter * 1e-6 / hbm_peak,
+                      "cpu_oracle_ms_per_iteration": cpu_iter * 1e3, "cpu_threads": torch.get_num_threads()}
+    return ex
+
+
+def dp_config5(sc, device, rank, world):
+    """BASELINE.json configs[4]: ONE dictionary d = 2048 x 65536 trained data-parallel, 8192 rows per GPU (weak
+    scaling), through both multi-GPU paths of sparse_coding__b200.dist - NCCL all-reduce of the gradients
+    (DataParallelEnsemble) and the reduce-scatter fused into the weight-gradient kernel's epilogue over peer memory
+    (FusedDataParallel).  Every rank calls this; rank 0 returns the record.  Times are CUDA events, max over ranks."""
+    import torch.distributed as dist
+    from sparse_coding__b200 import dist as scd
+    d, N, rows = 2048, 65536, 8192
+    flops = 10.0 * rows * N * d  # per GPU and step
+
+    def fresh():
+        torch.manual_seed(3)  # same initial dictionary on every rank
+        p, b = sc.FunctionalSAE.init(d, N, 1e-3, device=device)
+        return sc.FunctionalEnsemble([(p, b)], sc.FunctionalSAE, sc.torchopt_compat.adam, {"lr": 1e-3}, device=device)
+
+    def max_over_ranks(ms):
+        t = torch.tensor([ms], device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    torch.manual_seed(100 + rank)
+    local = torch.randn(4 * rows, d, device=device)
+    rec = {"d": d, "N": N, "rows_per_gpu": rows, "world": world, "scaling": "weak"}
+    # the same build's single-GPU step on the same rows (every rank runs it at the same time: same clocks, no traffic)
+    ens = fresh()
+    t1 = max_over_ranks(timed_ms(lambda i: ens.step_batch(local[(i % 4) * rows:(i % 4 + 1) * rows]), 3, 8, device))
+    rec["one_gpu_ms_per_step"] = t1
+    # loss of the first global step computed by ONE GPU on all rows (the parity oracle of SURVEY 8e)
+    gathered = [torch.empty(rows, d, device=device) for _ in range(world)]
+    dist.all_gather(gathered, local[:rows].contiguous())
+    ref_loss = None
+    if rank == 0:
+        ens0 = fresh()
+        _, l0, _ = ens0.compute_grads(torch.cat(gathered))
+        ref_loss = float(l0["loss"][0])
+        del ens0
+    del ens, gathered
+    torch.cuda.empty_cache()
+    for name, cls in (("nccl_allreduce", scd.DataParallelEnsemble), ("fused_reduce_scatter", scd.FusedDataParallel)):
+        try:
+            dp = cls(fresh())
+            first, _ = dp.step_batch(local[:rows])
+            first_loss = float(first["loss"][0])
+            dist.barrier()
+            ms = max_over_ranks(timed_ms(lambda i: dp.step_batch(local[(i % 4) * rows:(i % 4 + 1) * rows]), 2, 8, device))
+            rec[name] = {"ms_per_step": ms, "activations_per_s": rows * world / ms * 1e3,
+                         "tflops_per_gpu": flops / ms * 1e-9, "efficiency_vs_one_gpu": t1 / ms,
+                         "first_step_loss": first_loss}
+            del dp
+        except Exception as e:  # a fabric that cannot be set up must not take the headline line down
+            rec[name] = {"error": f"{type(e).__name__}: {e}"[:300]}
+        torch.cuda.empty_cache()
+        dist.barrier()
+    # what the NCCL path pays for its collective: the all-reduce of the flat gradient buffer, alone
+    flat = torch.zeros(2 * N * d + N + 3, device=device)
+    t_ar = max_over_ranks(timed_ms(lambda i: dist.all_reduce(flat), 2, 5, device))
+    grad_bytes = 4.0 * (2 * N * d + N)
+    rec["allreduce_alone_ms"] = t_ar
+    rec["allreduce_busbw_GBps"] = 2.0 * (world - 1) / world * grad_bytes / t_ar * 1e-6
+    # the fused path moves (W-1)/W of the gradient out (reduce-add) and (W-1)/W of the new parameters out (broadcast)
+    out_bytes = 2.0 * (world - 1) / world * grad_bytes
+    rec["fused_nvlink_bytes_out_per_gpu_per_step"] = out_bytes
+    if "ms_per_step" in rec.get("fused_reduce_scatter", {}):
+        f = rec["fused_reduce_scatter"]
+        f["nvlink_out_GBps_if_spread_over_the_step"] = out_bytes / f["ms_per_step"] * 1e-6
+        f["limiter"] = ("the step's own kernels: link traffic is %.0f GB/s of the 770 GB/s a peer copy reaches; the gap "
+                        "to the one-GPU step is two cross-rank barriers + the owner's Adam pass + broadcast stores"
+                        % f["nvlink_out_GBps_if_spread_over_the_step"])
+    if "ms_per_step" in rec.get("nccl_allreduce", {}):
+        n = rec["nccl_allreduce"]
+        n["limiter"] = ("exposed collective: all-reduce alone %.2f ms + sc_adam_apply on the full dictionary, after a "
+                        "gradient-only step" % t_ar)
+    if rank == 0 and ref_loss is not None:
+        rec["one_gpu_full_batch_loss"] = ref_loss
+        for name in ("nccl_allreduce", "fused_reduce_scatter"):
+            if "first_step_loss" in rec.get(name, {}):
+                rec[name]["loss_rel_dev_vs_one_gpu_full_batch"] = abs(rec[name]["first_step_loss"] - ref_loss) / abs(ref_loss)
+    return rec
+
+
 # ------------------------------------------------------------------------------------------ our arm
 def run_ours(args):
     import torch.distributed as dist
@@ -311,10 +476,18 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_value = B * M * world / (float(t.item()) / args.steps)
 
+    dp5 = None
+    if world > 1 and not args.no_extras:
+        del chunk
+        torch.cuda.empty_cache()
+        chunk = None
+        dp5 = dp_config5(sc, device, rank, world)
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
+    if chunk is None:
+        chunk = make_chunk(n_slices * B, D_ACT, 1, device)
 
     # per-kernel CUDA-event times over profiled steps of the same workload
     prof_steps = min(args.steps, 20)
@@ -439,6 +612,12 @@ def run_ours(args):
         "gpu_launches": (len(marks) // prof_steps + (0 if fmt == "f16" else 1)) * args.steps,
         "roofline": roofline, "cpu_baseline": cpu_baseline, "clocks": clocks.summary(),
     }
+    if dp5 is not None:
+        line["dp_config5"] = dp5
+    if world == 1 and not args.no_extras:
+        del ens, chunk
+        torch.cuda.empty_cache()
+        line["extra"] = extras_one_gpu(sc, device, B, hbm_peak, tensor_peak, tf32_peak)
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
@@ -452,6 +631,7 @@ def main():
     ap.add_argument("--batch", type=int, default=2048)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--quick", action="store_true", help="profiling runs: skip e2e, peak measurement and the CPU baseline")
+    ap.add_argument("--no-extras", action="store_true", help="skip the secondary records (other configs, config-5 data-parallel)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":

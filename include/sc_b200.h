@@ -195,6 +195,8 @@ typedef struct {
     void* workspace;
     size_t workspace_bytes;
     void* stream;
+    const float* l1_coef_dev; /* device scalar or NULL: when given it replaces l1_coef, so a caller that holds the
+                                 coefficient as a device tensor (buffers["l1_alpha"], big_sweep.py:186) need not sync */
 } ScFistaArgs;
 size_t sc_fista_workspace_bytes(int32_t B, int32_t d, int32_t N);
 int sc_fista(const ScFistaArgs* args);

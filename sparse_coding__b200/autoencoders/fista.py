@@ -50,13 +50,21 @@ def fista_native(batch, learned_dict, l1_coef, coefficients, num_iter, eta=None)
         eta_f = -1.0
     else:
         eta_f = float(eta.item() if isinstance(eta, torch.Tensor) else eta)
-    l1_f = float(l1_coef.item() if isinstance(l1_coef, torch.Tensor) else l1_coef)
+    # a coefficient that already lives on the device (buffers["l1_alpha"] of an ensemble member, big_sweep.py:186) is
+    # read there by the kernel: no .item() sync per member and step
+    l1_dev = None
+    if isinstance(l1_coef, torch.Tensor) and l1_coef.is_cuda:
+        l1_dev = l1_coef.detach().to(device=dev, dtype=torch.float32).reshape(1)
+        l1_f = 0.0
+    else:
+        l1_f = float(l1_coef.item() if isinstance(l1_coef, torch.Tensor) else l1_coef)
     need = L.sc_fista_workspace_bytes(B, d, N)
     ws_ptr, ws_bytes = _ws.aligned(need, dev)
     args = nat.ScFistaArgs(B=B, d=d, N=N, num_iter=int(num_iter), x=nat.ptr(x), D=nat.ptr(D), a0=nat.ptr(a0),
                            l1_coef=l1_f, eta=eta_f, momentum=mom.ctypes.data_as(C.POINTER(C.c_float)),
                            out_a=nat.ptr(out_a), out_res=nat.ptr(out_res), out_eta=nat.ptr(out_eta),
-                           workspace=ws_ptr, workspace_bytes=ws_bytes, stream=nat.stream_ptr(dev))
+                           workspace=ws_ptr, workspace_bytes=ws_bytes, stream=nat.stream_ptr(dev),
+                           l1_coef_dev=nat.ptr(l1_dev))
     with torch.cuda.device(dev):
         nat.check(L.sc_fista(C.byref(args)), "sc_fista")
     return out_a, out_res, out_eta

@@ -82,6 +82,7 @@ struct EpiFistaStep {
     struct alignas(64) Params {
         CUtensorMap yhi_map, ylo_map, a_map;  // io maps of [B][N]
         const float* eta;                      // device scalar
+        const float* l1_dev;                   // device scalar, used instead of l1 when not null
         float l1, mom;
     };
     const Params& p;
@@ -90,7 +91,7 @@ struct EpiFistaStep {
     float eta, thr;
     SC_DEVICE EpiFistaStep(const Params& p_, const RowCtx& c_, const EpiIo& io_) : p(p_), c(c_), io(io_) {
         eta = *p.eta;
-        thr = eta * p.l1;
+        thr = eta * (p.l1_dev ? *p.l1_dev : p.l1);
     }
     SC_DEVICE void request(int set, int row0, int col) const {  // lane 0
         uint8_t* b = io.buf + set * (3 * kIoTileBytes);
@@ -296,7 +297,7 @@ static int fista_impl(const ScFistaArgs& a) {
         if (rc == 0) rc = make_io_map(&e2.a_map, a.out_a, B, N, 1, 0, &err);
         if (rc != 0) return fail(rc, "%s", err ? err : "io tensor map creation failed");
     }
-    e2.eta = w.eta; e2.l1 = a.l1_coef;
+    e2.eta = w.eta; e2.l1 = a.l1_coef; e2.l1_dev = a.l1_coef_dev;
     for (int k = 0; k < a.num_iter; ++k) {
         EpiFistaRes::Params e1{a.x, w.res_hi, w.res_lo, nullptr};
         SC_TRY((launch_plan<false, true, EpiFistaRes>(p1, e1, st)));

@@ -236,7 +236,9 @@ static StepWsH carve_step_h(void* base, int M, int B, int d, int N, int tied, in
     w.x_hat = nullptr;
     {
         const long long tiles = (long long)M * ceil_div(B, 256) * ceil_div(d, pick_bn(d));
-        const int pairs = 74, kblocks = ceil_div(N, 64);
+        int sms = 148;
+        (void)device_sm_count(&sms);  // falls back to 148 when no device is current (workspace sizing on the host)
+        const int pairs = sms / 2, kblocks = ceil_div(N, 64);
         int sp = static_cast<int>(pairs / (tiles > 0 ? tiles : 1));
         if (sp > kblocks / 8) sp = kblocks / 8;
         if (sp > 8) sp = 8;

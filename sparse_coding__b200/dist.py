@@ -9,6 +9,10 @@
   flat gradient buffer with ONE all-reduce (NCCL over NVLink on GPUs), then applies Adam with
   `sc_adam_apply`.  The gradient through the decoder row-normalisation is linear in the batch, so
   all-reducing the projected per-rank gradients is exact.
+* FISTA and the metrics shard by ROWS: codes of different rows are independent given the dictionary, so
+  `fista_rows` runs each rank's rows with no data collective (only the step size is agreed on once), and the
+  `*_sharded` metrics add per-rank partial results - the [N] per-feature counts and the FVU sums - with one small
+  all-reduce each (standard_metrics.py:303-312,439-452).
 """
 from __future__ import annotations
 
@@ -230,3 +234,77 @@ class FusedDataParallel:
         out = self.update()
         self.fabric.barrier()   # every copy of the parameters is complete before anyone's next step reads it
         return out, aux
+
+
+# --------------------------------------------------------------------------------------------------------------------
+# Row-sharded FISTA and metrics.  Every function takes THIS rank's rows; results that describe rows stay local, results
+# that describe the dictionary (per-feature counts, FVU) are identical on every rank after one all-reduce.  The local
+# computation can be swapped (`*_fn` arguments): the gloo tests run the CPU oracle there, the default is the CUDA engine.
+
+def _world(group):
+    return dist.get_world_size(group) if dist.is_initialized() else 1
+
+
+def _all_reduce_(t, group):
+    if _world(group) > 1:
+        dist.all_reduce(t, group=group)
+    return t
+
+
+def fista_rows(local_batch, learned_dict, l1_coef, local_coefficients, num_iter, device=None, eta=None, group=None,
+               fista_fn=None, eta_fn=None):
+    """FunctionalFista.fista (fista.py:99-128) on this rank's rows of a row-sharded batch: (ahat_local, Res_local).
+    The step size eta = 1/lambda_max(D D^T) depends on the dictionary only; when it is not given, rank 0's value is
+    broadcast so that every rank iterates with bit-identical eta (no other communication: rows are independent)."""
+    if fista_fn is None:
+        from .autoencoders.fista import FunctionalFista, fista_native
+        fista_fn = lambda x, D, l1, a0, it, eta: FunctionalFista.fista(x, D, l1, a0, it, device, eta=eta)
+        if eta_fn is None:
+            eta_fn = lambda x, D, l1, a0: fista_native(x[:1], D, l1, a0[:1], 0)[2].reshape(1)
+    if eta is None:
+        if eta_fn is None:
+            raise ValueError("fista_rows: give eta or eta_fn together with a custom fista_fn")
+        eta_t = eta_fn(local_batch, learned_dict, l1_coef, local_coefficients).to(torch.float32).reshape(1).clone()
+        if _world(group) > 1:
+            dist.broadcast(eta_t, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+        eta = float(eta_t.item())
+    return fista_fn(local_batch, learned_dict, l1_coef, local_coefficients, num_iter, eta)
+
+
+def mean_nonzero_activations_sharded(model, local_batch, group=None, counts_fn=None):
+    """standard_metrics.py:303-306 over a row-sharded batch: [N] fraction of ALL rows on which each feature fires
+    (callers sum it for the mean L0).  One all-reduce of N + 1 floats."""
+    if counts_fn is None:
+        from . import standard_metrics as sm
+        counts_fn = sm.feature_nonzero_counts
+    xc = model.center(local_batch)
+    counts = counts_fn(model, xc).to(torch.float64)
+    pack = torch.cat([counts, counts.new_tensor([float(xc.shape[0])])])
+    _all_reduce_(pack, group)
+    return (pack[:-1] / pack[-1]).to(torch.float32)
+
+
+def n_ever_active_sharded(model, local_activations, threshold=10, group=None, counts_fn=None):
+    """batched_calc_feature_n_ever_active (standard_metrics.py:444-452) over row-sharded (already centred)
+    activations: per-feature non-zero counts are added across ranks before the threshold."""
+    if counts_fn is None:
+        from . import standard_metrics as sm
+        counts_fn = sm.feature_nonzero_counts
+    counts = counts_fn(model, local_activations).to(torch.float64)
+    _all_reduce_(counts, group)
+    return int((counts > threshold).sum().item())
+
+
+def fraction_variance_unexplained_sharded(model, local_batch, group=None, rss_fn=None):
+    """standard_metrics.py:308-312 over a row-sharded batch.  The denominator needs the column means of ALL rows: first
+    all-reduce (d + 1 numbers: column sums and the row count), then the two sums of squares (second all-reduce of 2)."""
+    if rss_fn is None:
+        from . import standard_metrics as sm
+        rss_fn = sm.residual_sum_of_squares
+    x = local_batch
+    first = torch.cat([x.sum(0, dtype=torch.float64), torch.tensor([float(x.shape[0])], dtype=torch.float64, device=x.device)])
+    _all_reduce_(first, group)
+    mean = (first[:-1] / first[-1]).to(x.dtype)
+    sums = torch.stack([rss_fn(model, x).to(torch.float64).reshape(()), (x - mean).pow(2).sum(dtype=torch.float64)])
+    _all_reduce_(sums, group)
+    return (sums[0] / sums[1]).to(torch.float32)

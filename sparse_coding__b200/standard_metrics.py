@@ -57,6 +57,28 @@ def total_variance_sum(batch) -> torch.Tensor:
     return out[0]
 
 
+def residual_sum_of_squares(model: LearnedDict, batch) -> torch.Tensor:
+    """sum((batch - predict(batch))^2): the numerator of fraction_variance_unexplained before the two means cancel
+    (row-sharded evaluation adds these per rank, dist.fraction_variance_unexplained_sharded)."""
+    eb = _encoder_and_bias(model)
+    identity = not isinstance(model, TiedSAE) or model._identity_centering()
+    if eb is not None and identity:
+        c_half, _ = _encode_native(batch, eb[0], eb[1], want_c=False, want_half=True)
+        if c_half is not None:
+            _, sq = _decode_native(None, model._dictionary_source(), normalise=True, target=batch, want_x_hat=False,
+                                   code_half=c_half)
+        else:
+            c, _ = _encode_native(batch, eb[0], eb[1])
+            _, sq = _decode_native(c, model._dictionary_source(), normalise=True, target=batch, want_x_hat=False)
+        return sq.reshape(())
+    return (batch - model.predict(batch)).pow(2).sum()
+
+
+def feature_nonzero_counts(model: LearnedDict, batch) -> torch.Tensor:
+    """[N] number of rows of `batch` (already centred) on which each feature is non-zero, codes never materialised."""
+    return _feature_stats(model, batch)["nonzero"]
+
+
 def fraction_variance_unexplained(model: LearnedDict, batch):
     """standard_metrics.py:308-312: mean((batch - predict(batch))^2) / mean((batch - batch.mean(0))^2)."""
     eb = _encoder_and_bias(model)

@@ -11,6 +11,7 @@ import torch.distributed as dist
 import torch.multiprocessing as mp
 
 from oracle import restated as R
+from sparse_coding__b200 import dist as scd
 from sparse_coding__b200.dist import DataParallelEnsemble, shard_members, shard_rows
 
 
@@ -117,3 +118,63 @@ def test_data_parallel_equals_full_batch_step(tmp_path):
             assert torch.allclose(r0["losses"][step][k], l[k], rtol=1e-4, atol=1e-7), (step, k)
     for k in orc.params:
         assert float((orc.params[k] - r0["params"][k]).abs().mean()) < 5e-6, k
+
+
+# ---------------------------------------------------------------------------------------------- row-sharded FISTA / metrics
+class _OracleModel:
+    """UntiedSAE stand-in on the CPU oracle (identity centring)."""
+
+    def __init__(self, We, b, Wd):
+        self.We, self.b, self.Wd = We, b, Wd
+
+    def center(self, x):
+        return x
+
+    def predict(self, x):
+        return R.untied_predict(self.We, self.b, self.Wd, x)
+
+
+def _rows_worker(rank, world, port, tmp):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    g = torch.load(os.path.join(tmp, "inputs.pt"), weights_only=False)
+    x, D, a0, We, b, Wd = (g[k] for k in ("x", "D", "a0", "We", "b", "Wd"))
+    lo, hi = shard_rows(x.shape[0], rank, world)
+    model = _OracleModel(We, b, Wd)
+    counts_fn = lambda m, xc: (R.untied_encode(m.We, m.b, xc) != 0).float().sum(0)
+    rss_fn = lambda m, xs: (xs - m.predict(xs)).pow(2).sum()
+    out = {}
+    # eta deliberately different per rank before the broadcast: rank 0's must win
+    eta_fn = lambda xs, Dd, l1, a: R.fista_eta(Dd).reshape(1) * (1.0 if rank == 0 else 0.5)
+    fista_fn = lambda xs, Dd, l1, a, it, eta: R.fista(xs, Dd, l1, a, it, eta=eta)
+    out["a"], out["res"] = scd.fista_rows(x[lo:hi], D, 1e-2, a0[lo:hi], 25, fista_fn=fista_fn, eta_fn=eta_fn)
+    out["mnz"] = scd.mean_nonzero_activations_sharded(model, x[lo:hi], counts_fn=counts_fn)
+    out["ever"] = scd.n_ever_active_sharded(model, x[lo:hi], threshold=3, counts_fn=counts_fn)
+    out["fvu"] = scd.fraction_variance_unexplained_sharded(model, x[lo:hi], rss_fn=rss_fn)
+    out["rows"] = (lo, hi)
+    torch.save(out, os.path.join(tmp, f"rows{rank}.pt"))
+    dist.destroy_process_group()
+
+
+def test_row_sharded_fista_and_metrics_equal_the_unsharded_ones(tmp_path):
+    """FISTA rows are independent given D and eta; the metrics need the [N] counts and the two
+    FVU sums added across ranks.  World 2 over gloo with the CPU oracle as the local engine, ragged split (101 rows)."""
+    torch.manual_seed(3)
+    n, d, N = 101, 12, 20
+    D = R.row_normalise(torch.randn(N, d))[0]
+    x = torch.randn(n, d) + 0.3
+    We, b, Wd = torch.randn(N, d) / d ** 0.5, 0.05 * torch.randn(N) - 0.2, torch.randn(N, d)
+    a0 = torch.relu(x @ D.T)
+    torch.save({"x": x, "D": D, "a0": a0, "We": We, "b": b, "Wd": Wd}, tmp_path / "inputs.pt")
+    world = 2
+    mp.spawn(_rows_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    r = [torch.load(tmp_path / f"rows{k}.pt", weights_only=False) for k in range(world)]
+    a_ref, res_ref = R.fista(x, D, 1e-2, a0, 25)
+    assert torch.allclose(torch.cat([r[0]["a"], r[1]["a"]]), a_ref, atol=1e-6)
+    assert torch.allclose(torch.cat([r[0]["res"], r[1]["res"]]), res_ref, atol=1e-6)
+    c = R.untied_encode(We, b, x)
+    for k in range(world):
+        assert torch.allclose(r[k]["mnz"], R.mean_nonzero_activations(c), atol=1e-6)
+        assert r[k]["ever"] == int(((c != 0).float().sum(0) > 3).sum())
+        want = R.fraction_variance_unexplained(x, R.untied_predict(We, b, Wd, x))
+        assert abs(float(r[k]["fvu"]) - float(want)) <= 1e-5 * abs(float(want))

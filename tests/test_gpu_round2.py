@@ -158,3 +158,31 @@ def test_fista_config4_full_batch_sampled_rows():
     # whole batch: the returned residual is consistent with the returned codes, and the codes are non-negative
     assert float((x.cuda() - a @ D.cuda() - res).abs().max()) < 1e-4
     assert float(a.min()) >= 0.0
+
+
+def test_row_sharded_entry_points_on_one_rank_match_the_plain_functions():
+    """dist.fista_rows / *_sharded with the CUDA engine as the local computation (world 1, no process group): the
+    same numbers as the unsharded functions, and the two halves of a batch processed separately combine to them."""
+    import sparse_coding__b200 as sc
+    from sparse_coding__b200 import dist as scd, standard_metrics as sm
+    torch.manual_seed(30)
+    n, d, N = 1000, 128, 256
+    x = make_sparse_data(n, d, 2 * d, 6, seed=31).cuda()
+    We, Wd, b = torch.randn(N, d).cuda() / d ** 0.5, torch.randn(N, d).cuda(), (0.05 * torch.randn(N) - 0.1).cuda()
+    m = sc.UntiedSAE(We, Wd, b)
+    assert torch.allclose(scd.mean_nonzero_activations_sharded(m, x), sm.mean_nonzero_activations(m, x), atol=1e-6)
+    assert scd.n_ever_active_sharded(m, x, threshold=10) == sm.batched_calc_feature_n_ever_active(m, x, threshold=10)
+    fvu = float(sm.fraction_variance_unexplained(m, x))
+    assert abs(float(scd.fraction_variance_unexplained_sharded(m, x)) - fvu) <= 1e-4 * fvu
+    # partial results of two row shards add up (what the all-reduce does across ranks)
+    c0, c1 = sm.feature_nonzero_counts(m, x[:400]), sm.feature_nonzero_counts(m, x[400:])
+    assert torch.equal(c0 + c1, sm.feature_nonzero_counts(m, x))
+    r0, r1 = sm.residual_sum_of_squares(m, x[:400]), sm.residual_sum_of_squares(m, x[400:])
+    assert abs(float(r0 + r1) - float(sm.residual_sum_of_squares(m, x))) <= 1e-4 * float(r0 + r1)
+    D = R.row_normalise(torch.randn(N, d))[0].cuda()
+    a0 = torch.relu(x @ D.T)
+    a, res = scd.fista_rows(x, D, 1e-2, a0, 20, device="cuda")
+    a_full, res_full = sc.FunctionalFista.fista(x, D, 1e-2, a0, 20, "cuda")
+    assert float((a - a_full).abs().max()) < 1e-5 and float((res - res_full).abs().max()) < 1e-5
+    a_half, _ = scd.fista_rows(x[:500], D, 1e-2, a0[:500], 20, device="cuda")
+    assert float((a_half - a_full[:500]).abs().max()) < 1e-5

@@ -271,6 +271,15 @@ int sc_profile_end(const char** names, float* ms, int cap);
 int sc_gemm_tf32(const float* A, const float* Bm, float* C, int32_t G, int32_t M, int32_t N, int32_t K,
                  int32_t a_mn, int32_t b_mn, void* stream);
 
+/* C[g] = A[g] B[g]^T at fp32 accuracy for the small dense products AROUND the hot path that the reference does with
+ * torch.einsum / torch.mm in fp32: the centring transform of FunctionalTiedSAE / TiedSAE (sae_ensemble.py:126-131,
+ * learned_dict.py:176-184: (x - t) Rot^T and its inverse) and the dictionary update of fista.py:131-138 (Res^T ahat).
+ * Operands are split into TF32 hi + lo parts and multiplied as hi*lo + lo*hi + hi*hi into one accumulator (relative
+ * 2^-21).  Layout flags and alignment rules as sc_gemm_tf32; workspace holds the four split copies. */
+size_t sc_gemm_f32_workspace_bytes(int32_t G, int32_t M, int32_t N, int32_t K);
+int sc_gemm_f32(const float* A, const float* Bm, float* C, int32_t G, int32_t M, int32_t N, int32_t K, int32_t a_mn,
+                int32_t b_mn, void* workspace, size_t workspace_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -25,6 +25,7 @@ EXPORTS = [
     "sc_encode_workspace_bytes", "sc_encode", "sc_decode_workspace_bytes", "sc_decode",
     "sc_fista_workspace_bytes", "sc_fista", "sc_gemm_tf32", "sc_adam_apply", "sc_row_normalise", "sc_column_variance",
     "sc_profile_begin", "sc_profile_end", "sc_encode_noalloc", "sc_sae_step_f16_supported", "sc_codes_to_float",
+    "sc_gemm_f32_workspace_bytes", "sc_gemm_f32",
     "sc_gather_rows", "sc_column_mean_workspace_bytes", "sc_column_mean", "sc_infer_f16_supported", "sc_dp_adam_broadcast",
 ]
 
@@ -138,6 +139,10 @@ def lib() -> C.CDLL:
         L.sc_decode.argtypes = [C.POINTER(ScDecodeArgs)]
         L.sc_fista.argtypes = [C.POINTER(ScFistaArgs)]
         L.sc_gemm_tf32.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p] + [C.c_int32] * 6 + [C.c_void_p]
+        L.sc_gemm_f32_workspace_bytes.restype = C.c_size_t
+        L.sc_gemm_f32_workspace_bytes.argtypes = [C.c_int32] * 4
+        L.sc_gemm_f32.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p] + [C.c_int32] * 6 + [C.c_void_p, C.c_size_t, C.c_void_p]
+        L.sc_gemm_f32.restype = C.c_int
         L.sc_row_normalise.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]
         L.sc_column_variance.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]
         L.sc_sae_step_f16_supported.argtypes = [C.c_int32] * 3
@@ -214,3 +219,30 @@ class Workspace:
         base = b.data_ptr()
         off = (-base) % 1024
         return C.c_void_p(base + off), b.numel() - off
+
+
+_gemm_ws = Workspace()
+
+
+def gemm_f32(A: torch.Tensor, B: torch.Tensor, a_mn: bool = False, b_mn: bool = False) -> torch.Tensor:
+    """C[g] = A[g] B[g]^T at fp32 accuracy through sc_gemm_f32 (3xTF32 on the tcgen05 core): the engine's stand-in for
+    the small torch.einsum / torch.mm products around the hot path.  A is [G,M,K] (or [G,K,M] with a_mn), B is [G,N,K]
+    (or [G,K,N] with b_mn); 2-D operands are taken as G = 1 and the result is 2-D then."""
+    squeeze = A.dim() == 2
+    A3, B3 = (A.unsqueeze(0) if A.dim() == 2 else A), (B.unsqueeze(0) if B.dim() == 2 else B)
+    require_cuda(A3, "A")
+    require_cuda(B3, "B")
+    A3, B3 = A3.contiguous(), B3.contiguous()
+    G = A3.shape[0]
+    M, K = (A3.shape[2], A3.shape[1]) if a_mn else (A3.shape[1], A3.shape[2])
+    N, Kb = (B3.shape[2], B3.shape[1]) if b_mn else (B3.shape[1], B3.shape[2])
+    if Kb != K or B3.shape[0] != G:
+        raise ValueError(f"gemm_f32: operand shapes {tuple(A.shape)} / {tuple(B.shape)} do not match")
+    L = lib()
+    out = torch.empty((G, M, N), dtype=torch.float32, device=A3.device)
+    need = L.sc_gemm_f32_workspace_bytes(G, M, N, K)
+    ws_ptr, ws_bytes = _gemm_ws.aligned(need, A3.device)
+    with torch.cuda.device(A3.device):
+        check(L.sc_gemm_f32(ptr(A3), ptr(B3), ptr(out), G, M, N, K, int(a_mn), int(b_mn), ws_ptr, ws_bytes,
+                            stream_ptr(A3.device)), "sc_gemm_f32")
+    return out[0] if squeeze else out

@@ -301,8 +301,9 @@ class FunctionalEnsemble:
 
     def _centered_batch(self, x: torch.Tensor, expand: bool):
         """FunctionalTiedSAE.center (sae_ensemble.py:126-127) with per-member buffers.  Identity
-        buffers (the default, :97-108) skip it; otherwise the batch is centred once per step with a
-        plain library GEMM - a constant pre-transform of the input, not part of the trained graph."""
+        buffers (the default, :97-108) skip it; otherwise the batch is centred once per step with one batched
+        [B x d x d] product on the tcgen05 core at fp32 accuracy (sc_gemm_f32) - a constant pre-transform of the
+        input, not part of the trained graph."""
         b = self.buffers
         rot, tr, sc = b["center_rot"], b["center_trans"], b["center_scale"]
         key = (rot.data_ptr(), rot._version, tr.data_ptr(), tr._version, sc.data_ptr(), sc._version)
@@ -313,8 +314,9 @@ class FunctionalEnsemble:
             self._center_key = key
         if self._center_identity:
             return x, not expand
+        from .learned_dict import center_native
         xm = x.unsqueeze(0) if expand else x
-        xc = torch.einsum("mcu,mbu->mbc", rot, xm - tr[:, None, :]) * sc[:, None, :]
+        xc = center_native(xm, rot.to(torch.float32), tr.to(torch.float32), sc.to(torch.float32))
         return xc.contiguous(), True
 
     # ------------------------------------------------------------------ fp16 range guard

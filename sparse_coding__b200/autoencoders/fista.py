@@ -94,7 +94,7 @@ class FunctionalFista(DictSignature):
     def quadraticBasisUpdate(learned_dict, Res, ahat, lowestActivation, HessianDiag, stepSize=0.001, Noneg=False):
         """fista.py:131-138, kept verbatim in meaning: only shape-valid when N == d, and the final
         normalisation is over dim 0 (column norms)."""
-        dBasis = stepSize * torch.mm(Res.t(), ahat) / ahat.size(0)
+        dBasis = stepSize * nat.gemm_f32(Res, ahat, a_mn=True, b_mn=True) / ahat.size(0)   # Res^T ahat, [d, N]
         dBasis = dBasis / (HessianDiag + lowestActivation)
         learned_dict = learned_dict + (dBasis.t())
         if Noneg:
@@ -106,7 +106,7 @@ class FunctionalFista(DictSignature):
         """What fista.py:131-138 is after, valid for any N and d: the same preconditioned gradient
         step on the reconstruction error, dBasis[n] = stepSize * mean_b(a_bn Res_b) / (H_n + lowestActivation), with
         every ATOM (row of the [N, d] dictionary) renormalised to unit length afterwards."""
-        dBasis = stepSize * torch.mm(ahat.t(), Res) / ahat.size(0)            # [N, d]
+        dBasis = stepSize * nat.gemm_f32(ahat, Res, a_mn=True, b_mn=True) / ahat.size(0)   # ahat^T Res, [N, d]
         dBasis = dBasis / (HessianDiag + lowestActivation)[:, None]
         learned_dict = learned_dict + dBasis
         if Noneg:

@@ -18,6 +18,21 @@ from .. import _native as nat
 _ws = nat.Workspace()
 
 
+
+def center_native(batch, rot, trans, scale):
+    """((batch - trans) Rot^T) * scale (learned_dict.py:164-165, sae_ensemble.py:125-127) with the d x d product on the
+    tcgen05 core at fp32 accuracy (sc_gemm_f32).  rot may be [d,d] or, for an ensemble, [M,d,d] with batch [M,B,d]."""
+    if rot.dim() == 3:
+        return nat.gemm_f32(batch - trans[:, None, :], rot) * scale[:, None, :]
+    return nat.gemm_f32(batch - trans[None, :], rot) * scale[None, :]
+
+
+def uncenter_native(batch, rot, trans, scale):
+    """(batch / scale) Rot + trans (learned_dict.py:167-168, sae_ensemble.py:129-131)."""
+    if rot.dim() == 3:
+        return nat.gemm_f32(batch / scale[:, None, :], rot, b_mn=True) + trans[:, None, :]
+    return nat.gemm_f32(batch / scale[None, :], rot, b_mn=True) + trans[None, :]
+
 def _prep(t: torch.Tensor, name: str) -> torch.Tensor:
     nat.require_cuda(t, name)
     t = t.detach()
@@ -243,15 +258,15 @@ class TiedSAE(LearnedDict):
         """learned_dict.py:164-165; identity centring (the default) is skipped."""
         if self._identity_centering():
             return batch
-        return torch.einsum("cu,bu->bc", self.center_rot.to(batch.device), batch - self.center_trans.to(batch.device)[None, :]) \
-            * self.center_scale.to(batch.device)[None, :]
+        return center_native(batch, self.center_rot.to(batch.device), self.center_trans.to(batch.device),
+                             self.center_scale.to(batch.device))
 
     def uncenter(self, batch):
         """learned_dict.py:167-168."""
         if self._identity_centering():
             return batch
-        return torch.einsum("cu,bc->bu", self.center_rot.to(batch.device), batch / self.center_scale.to(batch.device)[None, :]) \
-            + self.center_trans.to(batch.device)[None, :]
+        return uncenter_native(batch, self.center_rot.to(batch.device), self.center_trans.to(batch.device),
+                               self.center_scale.to(batch.device))
 
     def get_learned_dict(self):
         return _row_normalise_native(self.encoder)

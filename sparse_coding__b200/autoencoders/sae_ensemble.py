@@ -94,14 +94,14 @@ class FunctionalTiedSAE(DictSignature):
     @staticmethod
     def center(buffers, batch):
         """sae_ensemble.py:125-127."""
-        return torch.einsum("cu,bu->bc", buffers["center_rot"], batch - buffers["center_trans"][None, :]) \
-            * buffers["center_scale"][None, :]
+        from .learned_dict import center_native
+        return center_native(batch, buffers["center_rot"], buffers["center_trans"], buffers["center_scale"])
 
     @staticmethod
     def uncenter(buffers, batch):
         """sae_ensemble.py:129-131."""
-        return torch.einsum("cu,bc->bu", buffers["center_rot"], batch / buffers["center_scale"][None, :]) \
-            + buffers["center_trans"][None, :]
+        from .learned_dict import uncenter_native
+        return uncenter_native(batch, buffers["center_rot"], buffers["center_trans"], buffers["center_scale"])
 
     @staticmethod
     def loss(params, buffers, batch):

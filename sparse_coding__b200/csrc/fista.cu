@@ -326,4 +326,36 @@ int sc_fista(const ScFistaArgs* args) {
     return sc::fista_impl(*args);
 }
 
+size_t sc_gemm_f32_workspace_bytes(int32_t G, int32_t M, int32_t N, int32_t K) {
+    if (G <= 0 || M <= 0 || N <= 0 || K <= 0) return 0;
+    sc::Carver c(nullptr);
+    c.floats((size_t)G * M * K); c.floats((size_t)G * M * K);
+    c.floats((size_t)G * N * K); c.floats((size_t)G * N * K);
+    return c.off;
+}
+
+int sc_gemm_f32(const float* A, const float* Bm, float* C, int32_t G, int32_t M, int32_t N, int32_t K, int32_t a_mn,
+                int32_t b_mn, void* workspace, size_t workspace_bytes, void* stream) {
+    using namespace sc;
+    if (!A || !Bm || !C || !workspace) return fail(-1, "NULL operand");
+    if (M <= 0 || N <= 0 || K <= 0 || G <= 0) return fail(-1, "bad shape");
+    if ((a_mn ? M : K) & 3 || (b_mn ? N : K) & 3 || (N & 3)) return fail(-1, "leading dimensions must be multiples of 4");
+    if (workspace_bytes < sc_gemm_f32_workspace_bytes(G, M, N, K)) return fail(-1, "workspace too small");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    Carver c(workspace);
+    const long long na = (long long)G * M * K, nb = (long long)G * N * K;
+    float *a_hi = c.floats(na), *a_lo = c.floats(na), *b_hi = c.floats(nb), *b_lo = c.floats(nb);
+    SC_TRY(split(A, a_hi, a_lo, nullptr, na, st));
+    SC_TRY(split(Bm, b_hi, b_lo, nullptr, nb, st));
+    auto opa = [&](const float* p) { return a_mn ? mnmajor(p, M, K, G, (long long)M * K) : kmajor(p, M, K, G, (long long)M * K); };
+    auto opb = [&](const float* p) { return b_mn ? mnmajor(p, N, K, G, (long long)N * K) : kmajor(p, N, K, G, (long long)N * K); };
+    // cross terms first: the tensor core adds each instruction's products into the accumulator with truncation
+    Seg s[3] = {{opa(a_hi), opb(b_lo)}, {opa(a_lo), opb(b_hi)}, {opa(a_hi), opb(b_hi)}};
+    EpiStore::Params ep{C, N, (long long)M * N};
+    if (!a_mn && !b_mn) return run_gemm<false, false, EpiStore>(M, N, G, s, 3, ep, st);
+    if (a_mn && !b_mn) return run_gemm<true, false, EpiStore>(M, N, G, s, 3, ep, st);
+    if (!a_mn && b_mn) return run_gemm<false, true, EpiStore>(M, N, G, s, 3, ep, st);
+    return run_gemm<true, true, EpiStore>(M, N, G, s, 3, ep, st);
+}
+
 }  // extern "C"

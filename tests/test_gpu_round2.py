@@ -186,3 +186,23 @@ def test_row_sharded_entry_points_on_one_rank_match_the_plain_functions():
     assert float((a - a_full).abs().max()) < 1e-5 and float((res - res_full).abs().max()) < 1e-5
     a_half, _ = scd.fista_rows(x[:500], D, 1e-2, a0[:500], 20, device="cuda")
     assert float((a_half - a_full[:500]).abs().max()) < 1e-5
+
+
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (True, True), (False, True), (True, False)])
+def test_gemm_f32_is_fp32_accurate(a_mn, b_mn):
+    """sc_gemm_f32 (3xTF32): the products the reference does with torch.einsum / torch.mm around the hot path."""
+    from sparse_coding__b200 import _native as nat
+    torch.manual_seed(40)
+    G, M, N, K = 3, 203, 64, 100
+    A, B = torch.randn(G, M, K), torch.randn(G, N, K)
+    ref = torch.einsum("gmk,gnk->gmn", A.double(), B.double())
+    Ad = (A.transpose(1, 2).contiguous() if a_mn else A).cuda()
+    Bd = (B.transpose(1, 2).contiguous() if b_mn else B).cuda()
+    if a_mn and M % 4:
+        with pytest.raises(RuntimeError):
+            nat.gemm_f32(Ad, Bd, a_mn=a_mn, b_mn=b_mn)
+        A, Ad = A[:, :200], Ad[:, :, :200].contiguous()
+        ref = ref[:, :200]
+    out = nat.gemm_f32(Ad, Bd, a_mn=a_mn, b_mn=b_mn)
+    # fp32-level (|ref| up to ~40, K = 100; plain TF32 would be ~1e-2): the lo*lo terms and the accumulator truncation remain
+    assert float((out.cpu().double() - ref).abs().max()) < 1e-4

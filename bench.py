@@ -287,9 +287,10 @@ def extras_one_gpu(sc, device, B, hbm_peak, tensor_peak, tf32_peak):
     R.fista(x.cpu(), D.cpu(), 1e-3, a0.cpu(), 10)
     cpu_iter = (time.perf_counter() - t0) / 10
     ex["fista_c4"] = {"B": Bf, "d": d, "N": N, "iterations": iters, "seconds": ms * 1e-3, "ms_per_iteration": per_iter,
-                      "products": "3xTF32 (hi/lo split, fp32-accurate)",
+                      "products": "fp16 hi/lo pairs, three kind::f16 passes per product (fp32-accurate; the TF32 pair is the "
+                                  "fallback for shapes the fp16 kernels do not take)",
                       "tflops_fp32_equivalent": 4.0 * Bf * N * d / per_iter * 1e-9,
-                      "frac_of_tf32_peak_3_passes": 3 * 4.0 * Bf * N * d / per_iter * 1e-9 / tf32_peak,
+                      "frac_of_tensor_peak_3_passes": 3 * 4.0 * Bf * N * d / per_iter * 1e-9 / tensor_peak,
                       "alg_GBps": 16.0 * Bf * N / per_iter * 1e-6, "frac_of_hbm_peak": 16.0 * Bf * N / per_iter * 1e-6 / hbm_peak,
                       "cpu_oracle_ms_per_iteration": cpu_iter * 1e3, "cpu_threads": torch.get_num_threads()}
     return ex

@@ -241,7 +241,9 @@ int run_gemm_short_k(int M, int N, int G, const Seg* seg, const typename Epi::Pa
     // operand traffic gives back
     const bool ok = use_resident_a() && seg->a.elem_bytes == 2 && !seg->a.mn_major && !seg->b.mn_major &&
                     seg->a.k <= 64 * kResMaxKBlocks && pick_bn(N) >= 128 && ceil_div(N, pick_bn(N)) <= 8;
-    if (!ok) return run_gemm<false, false, Epi, true>(M, N, G, seg, 1, ep, stream);
+    const int kblocks = ceil_div(seg->a.k, 64);
+    const bool fits = pick_bn(N) == 256 ? GemmCfgRes<256, Epi>::stages(kblocks) >= 2 : GemmCfgRes<128, Epi>::stages(kblocks) >= 2;
+    if (!ok || !fits) return run_gemm<false, false, Epi, true>(M, N, G, seg, 1, ep, stream);
     GemmPlan pl;
     SC_TRY(plan_gemm(&pl, M, N, G, seg, 1, false, false));
     cudaError_t e;

@@ -160,7 +160,7 @@ inline int plan_gemm(GemmPlan* pl, int M, int N, int G, const Seg* segs, int nse
     memset(pl, 0, sizeof *pl);
     SC_TRY(device_sm_count(&pl->sms));
     pl->bn = bn > 0 ? bn : pick_bn(N);
-    if (ksplit > 1 && (nseg != 1 || segs[0].a.elem_bytes != 2)) return fail(-3, "split-K needs one fp16 segment");
+    if (ksplit > 1 && segs[0].a.elem_bytes != 2) return fail(-3, "split-K needs fp16 operands (CTA-pair kernel)");
     pl->sh.ksplit = ksplit > 1 ? ksplit : 1;
     pl->eb = segs[0].a.elem_bytes == 2 ? 2 : 4;
     pl->cta2 = use_cta_pairs() || pl->eb == 2;

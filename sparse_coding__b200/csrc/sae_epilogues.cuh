@@ -375,6 +375,8 @@ AdamSub sub[2];   // one per batched problem (untied: [0] encoder, [1] decoder)
     CUtensorMap rs_map[2][8];      // [problem][owner]: io map of the owner's [1][rs_rows][d] accumulation buffer
     int fin_on;                    // 1: the idle warps of this launch also do the step's finalize work
     int fold;                      // 1: fold mode
+    int acc_split;                 // 1: split-K launch (GemmShape::ksplit > 1): every partial tile is reduce-ADDED into the
+                                   // (zeroed) gradient buffer behind grad_map; Adam follows in a pass of its own
     int wsq_parts;                 // partial slots per feature in wsq_out: column tiles x SPLIT
     FinalizeArgs fin;
 };
@@ -484,9 +486,12 @@ struct EpiAdamT {
             if (p.fold) {
 #pragma unroll
                 for (int j = 0; j < W; ++j) v[j] = clamped ? v[j] * inv : fmaf(-s, pv[j], v[j]);
-            } else {
+            } else if (c.split == 0) {
 #pragma unroll
                 for (int j = 0; j < W; ++j) v[j] = clamped ? v[j] * inv : (v[j] - s * (pv[j] * inv)) * inv;
+            } else {  // partial tile of a split K loop: the projection is linear, its s D term goes in once (split 0)
+#pragma unroll
+                for (int j = 0; j < W; ++j) v[j] *= inv;
             }
         }
         if (u.grad_only) {
@@ -498,6 +503,8 @@ struct EpiAdamT {
                     // clipped by the map of the last owner
                     const int rk = min(row0 / p.rs_rows, p.rs_world - 1);
                     tma_reduce_add_3d(&p.rs_map[c.prob][rk], b, col, row0 - rk * p.rs_rows, 0);
+                } else if (p.acc_split) {
+                    tma_reduce_add_3d(&u.grad_map, b, col, row0, c.g);
                 } else {
                     tma_store_3d(&u.grad_map, b, col, row0, c.g);
                 }

@@ -199,6 +199,10 @@ __global__ void __launch_bounds__(256) residual_h_kernel(const float4* __restric
 struct StepWsH {
     __half *x_h, *enc_h, *D_h, *r_h, *dz_h;
     float *inv_norm, *l1_part, *mse_part, *db_part, *s_part, *bnorm, *x_hat;
+    float *gacc_enc, *gacc_dec;  // split-K weight gradients of small ensembles: fp32 accumulation buffers [M][N][d]
+    int g45_split;               // > 1: the weight-gradient GEMMs run split-K into them, Adam follows as its own pass
+    float* zero_from;            // start and length (bytes) of the workspace span the prologue has to clear
+    size_t zero_bytes;
     float* wsq;  // fold mode: [M][wsq_parts][N] partial sums of w^2 of the updated decoder rows (Adam epilogue -> next prologue)
     int wsq_parts;
     int g2_split;  // > 1: G2 runs split-K into x_hat
@@ -250,6 +254,28 @@ static StepWsH carve_step_h(void* base, int M, int B, int d, int N, int tied, in
             }
         }
     }
+    // Weight gradients: M ceil(N/256) ceil(d/bn) tiles per problem with the LONGEST K loop of the step (K = B).  Small
+    // ensembles leave most CTA pairs idle there (toy config: 8 tiles on 74 pairs); split K so that the partial tiles
+    // fill the machine, reduce-add them into fp32 buffers and run Adam as an elementwise pass afterwards.
+    w.g45_split = 1;
+    w.gacc_enc = w.gacc_dec = nullptr;
+    {
+        int sms = 148;
+        (void)device_sm_count(&sms);
+        const long long tiles = (long long)M * ceil_div(N, 256) * ceil_div(d, pick_bn(d)) * (tied ? 1 : 2);
+        const int kblocks = ceil_div(B, 64);
+        int sp = static_cast<int>((sms / 2) / (tiles > 0 ? tiles : 1));
+        if (sp > kblocks / 8) sp = kblocks / 8;
+        if (sp > 8) sp = 8;
+        while (sp > 1 && (long long)(sp - 1) * ceil_div(kblocks, sp) >= kblocks) --sp;  // no empty K range
+        if (sp >= 2) {
+            w.g45_split = sp;
+            w.gacc_enc = c.floats(Mz * Nz * dz_);
+            if (!tied) w.gacc_dec = c.floats(Mz * Nz * dz_);
+        }
+    }
+    w.zero_from = w.x_hat ? w.x_hat : w.gacc_enc;
+    w.zero_bytes = w.zero_from ? static_cast<size_t>(c.base + c.off - reinterpret_cast<uint8_t*>(w.zero_from)) : 0;
     w.bytes = c.off;
     return w;
 }
@@ -315,7 +341,8 @@ int sae_step_f16_impl(const ScStepArgs& a) {
     // Fold mode (untied full step): the Adam epilogue of this step leaves the fp16 operand copies and the decoder row
     // norms of the UPDATED parameters in the workspace, and the next step (operands_valid) skips the pass over the fp32
     // weights: its prologue only turns the epilogue's partial sums of w^2 into 1/||W_d row||.
-    const bool fold = !a.tied && !grad_mode && fold_enabled();
+    const bool g45_split = w.g45_split > 1 && !grad_mode;
+    const bool fold = !a.tied && !grad_mode && !g45_split && fold_enabled();
     const float* fold_inv = fold ? w.inv_norm : nullptr;
     const bool params_ready = fold && a.operands_valid != 0;
 
@@ -329,8 +356,9 @@ int sae_step_f16_impl(const ScStepArgs& a) {
         // operands left by the previous step: only the batch conversion, the bias norms and the zeroing remain
         const int norm_blocks = params_ready ? ceil_div((long long)M * N, 256) : 0;
         const int blocks = M + x_blocks + (params_ready ? norm_blocks : ceil_div(N, 8) * M);
-        float4* zero = w.g2_split > 1 ? reinterpret_cast<float4*>(w.x_hat) : nullptr;
-        const long long zero_n4 = w.g2_split > 1 ? (long long)M * Bd / 4 : 0;
+        // split-K GEMMs accumulate into workspace buffers (x_hat of G2, the weight-gradient buffers): cleared here
+        float4* zero = reinterpret_cast<float4*>(w.zero_from);
+        const long long zero_n4 = static_cast<long long>(w.zero_bytes / 16);
         if (a.tied)
             launch_k(step_prologue_h_kernel, dim3(blocks), dim3(256), 0, st, a.bias, w.bnorm, M, reinterpret_cast<const float4*>(a.x),
                      reinterpret_cast<uint2*>(w.x_h), x_n4, x_blocks, nullptr, nullptr, a.enc, w.D_h, w.inv_norm, N, d, zero, zero_n4,
@@ -385,7 +413,9 @@ int sae_step_f16_impl(const ScStepArgs& a) {
     {
         AdamParams e{};
         e.tiles_b = w.tiles_b; e.a = ad; e.g_scale = sc_;
-        e.fold = fold ? 1 : 0; e.wsq_parts = w.wsq_parts;  // unused slots of the four-warp variant stay zero
+        e.fold = fold ? 1 : 0; e.wsq_parts = w.wsq_parts;
+        e.acc_split = g45_split ? 1 : 0;
+        const int ks = g45_split ? w.g45_split : 0;
         auto fill = [&](AdamSub& u, float* p, float* mu, float* nu, float* grad, bool projected) -> int {
             u.fold_inv = fold_inv;
             u.wsq_out = (fold && projected) ? w.wsq : nullptr;
@@ -411,17 +441,27 @@ int sae_step_f16_impl(const ScStepArgs& a) {
         if (!a.tied) {
             Seg s45[2] = {{codesT_k(w.dz_h), mnmajor_h(w.x_h, d, B, xg, Bd)},
                           {codesT_k(c_h), mnmajor_h(w.r_h, d, B, M, Bd)}};
-            SC_TRY(fill(e.sub[0], a.enc, a.enc_mu, a.enc_nu, a.grad_enc, false));
-            SC_TRY(fill(e.sub[1], a.dec, a.dec_mu, a.dec_nu, grad_mode ? a.grad_dec : nullptr, true));
-            if (adam_split()) SC_TRY((run_gemm<false, true, EpiAdamS, true>(N, d, M, s45, 2, e, st, true)));
-            else SC_TRY((run_gemm<false, true, EpiAdam, true>(N, d, M, s45, 2, e, st, true)));
+            SC_TRY(fill(e.sub[0], a.enc, a.enc_mu, a.enc_nu, g45_split ? w.gacc_enc : a.grad_enc, false));
+            SC_TRY(fill(e.sub[1], a.dec, a.dec_mu, a.dec_nu, g45_split ? w.gacc_dec : (grad_mode ? a.grad_dec : nullptr), true));
+            if (adam_split() && !g45_split) SC_TRY((run_gemm<false, true, EpiAdamS, true>(N, d, M, s45, 2, e, st, true)));
+            else SC_TRY((run_gemm<false, true, EpiAdam, true>(N, d, M, s45, 2, e, st, true, 0, ks)));
         } else {
             Seg s[2] = {{codesT_k(c_h), mnmajor_h(w.r_h, d, B, M, Bd)},
                         {codesT_k(w.dz_h), mnmajor_h(w.x_h, d, B, xg, Bd)}};
-            SC_TRY(fill(e.sub[0], a.enc, a.enc_mu, a.enc_nu, a.grad_enc, true));
+            SC_TRY(fill(e.sub[0], a.enc, a.enc_mu, a.enc_nu, g45_split ? w.gacc_enc : a.grad_enc, true));
             e.sub[1] = e.sub[0];
-            if (adam_split()) SC_TRY((run_gemm<false, true, EpiAdamS, true>(N, d, M, s, 2, e, st)));
-            else SC_TRY((run_gemm<false, true, EpiAdam, true>(N, d, M, s, 2, e, st)));
+            if (adam_split() && !g45_split) SC_TRY((run_gemm<false, true, EpiAdamS, true>(N, d, M, s, 2, e, st)));
+            else SC_TRY((run_gemm<false, true, EpiAdam, true>(N, d, M, s, 2, e, st, false, 0, ks)));
+        }
+        if (g45_split) {  // Adam from the accumulated gradients (elementwise, the tensors are small in this regime)
+            const long long n4 = (long long)M * Nd / 4;
+            const int grid = static_cast<int>(n4 / 256 + 1 < 1184 ? n4 / 256 + 1 : 1184);
+            launch_k(adam_apply_kernel, dim3(grid), dim3(256), 0, st, reinterpret_cast<float4*>(a.enc), reinterpret_cast<float4*>(a.enc_mu),
+                     reinterpret_cast<float4*>(a.enc_nu), reinterpret_cast<const float4*>(w.gacc_enc), n4, ad);
+            if (!a.tied)
+                launch_k(adam_apply_kernel, dim3(grid), dim3(256), 0, st, reinterpret_cast<float4*>(a.dec), reinterpret_cast<float4*>(a.dec_mu),
+                         reinterpret_cast<float4*>(a.dec_nu), reinterpret_cast<const float4*>(w.gacc_dec), n4, ad);
+            SC_CUDA(cudaGetLastError(), "adam apply launch");
         }
     }
     prof_mark(st, "G45_dW_adam");  // includes the finalize work (loss scalars + bias Adam) on the idle warps

@@ -240,14 +240,16 @@ using EpiEncodeTH = EpiEncodeTHT<2>;
 // stored from there, and once that store has read it the slot takes the c tile two chunks ahead - across tile
 // boundaries too (static schedule) - so loads fly during two chunks of arithmetic and 6 KB per warp is all the
 // staging this epilogue needs (the resident-A kernel has little shared memory to spare).
-template <int H>
+template <int H, int SLOTS = 3>
 struct EpiBackCodeHT {
     // H warps per row quarter (4 H epilogue warps): 8 / H chunks of 32 columns per warp and 256-wide tile.
+    // SLOTS staging slots per warp: SLOTS - 1 chunks of look-ahead (3: what fits beside a resident A operand).
     static constexpr int kHalves = H;
     static constexpr int kPerTile = 8 / H;
-    static constexpr int kSlots = 3;
+    static constexpr int kSlots = SLOTS;
+    static constexpr int kAhead = SLOTS - 1;
     static constexpr int kIoBytes = kSlots * 2048;  // per warp (kernels that count staging in 4 KB units round up)
-    static constexpr int kIoBufs = 2;
+    static constexpr int kIoBufs = (SLOTS + 1) / 2;
     static_assert(kSlots <= kIoBars, "one load barrier per slot");
     struct alignas(64) Params {
         CUtensorMap c_map;    // fp16 io map of c^T  [G][N][B]
@@ -265,8 +267,8 @@ struct EpiBackCodeHT {
     const RowCtx c;
     const EpiIo io;
     float db, db1, s, s1, l1_term, bn, db_scale;
-    // warp state that outlives the tile, in the free bits of the warp's phase word: bits 8-9 the slot of the next
-    // chunk to consume, bits 10-11 how many chunks after the current one have been requested (0..2)
+    // warp state that outlives the tile, in the free bits of the warp's phase word: bits 8-10 the slot of the next
+    // chunk to consume, bits 12-14 how many chunks after the current one have been requested (0..kAhead)
     SC_DEVICE void request(int slot, int g, int row0, int bcol) const {
         io_expect(io, 2048, slot);
         tma_load_3d(&p.c_map, io.bar + slot, io.buf + slot * 2048, bcol, row0, g);
@@ -285,7 +287,7 @@ struct EpiBackCodeHT {
         const int cw = (c.half + j * H) * 32;
         return j < kPerTile && cw < c.bn && col0 + cw < c.N;
     }
-    // the k-th (1 or 2) live chunk after chunk i of the current tile, in processing order
+    // the k-th (1..kAhead) live chunk after chunk i of the current tile, in processing order
     SC_DEVICE bool nth_next(int i, int k, int& g, int& row0, int& bcol) const {
         for (int j = i + 1; live(c.col0, j); ++j)
             if (--k == 0) { g = c.g; row0 = c.row - (threadIdx.x & 31); bcol = c.col0 + (c.half + j * H) * 32; return true; }
@@ -330,7 +332,7 @@ struct EpiBackCodeHT {
         const int bcol = c.col0 + co;
         if (bcol >= c.N) return;      // the whole chunk lies beyond the batch (warp-uniform): nothing was requested
         const int row0 = c.row - lane;
-        int cons = (*io.phase >> 8) & 3, ahead = (*io.phase >> 10) & 3;
+        int cons = (*io.phase >> 8) & 7, ahead = (*io.phase >> 12) & 7;
         if (ahead == 0) {  // nothing in flight for this chunk (first chunk of the kernel, or the look-ahead could not see it)
             io_wait_stores_read_n<1>();
             if (lane == 0) request(cons, c.g, row0, bcol);
@@ -347,17 +349,17 @@ struct EpiBackCodeHT {
             tma_store_commit();
         }
         --ahead;
-        cons = cons == 2 ? 0 : cons + 1;
-        // keep two chunks in flight: the slots they go to were stored at least one bulk group before the store above
+        cons = cons == kSlots - 1 ? 0 : cons + 1;
+        // keep kAhead chunks in flight: the slots they go to were stored at least one bulk group before the store above
         bool waited = false;
-        for (int k = ahead + 1; k <= 2; ++k) {
+        for (int k = ahead + 1; k <= kAhead; ++k) {
             int g, r0, bc;
             if (!nth_next(i, k, g, r0, bc)) break;
             if (!waited) { io_wait_stores_read_n<1>(); waited = true; }
-            if (lane == 0) request((cons + k - 1) % 3, g, r0, bc);
+            if (lane == 0) request((cons + k - 1) % kSlots, g, r0, bc);
             ahead = k;
         }
-        *io.phase = (*io.phase & ~0xF00u) | (static_cast<uint32_t>(cons) << 8) | (static_cast<uint32_t>(ahead) << 10);
+        *io.phase = (*io.phase & ~0x7700u) | (static_cast<uint32_t>(cons) << 8) | (static_cast<uint32_t>(ahead) << 12);
     }
     SC_DEVICE void finish() {
         if (c.row >= c.M) return;
@@ -368,6 +370,8 @@ struct EpiBackCodeHT {
 };
 // Measured at the headline shape: 16 epilogue warps (H = 4, 96-register cap) are 1 - 1.5 % slower per step than 8, with
 // the 12 KB-per-warp staging of round 1 as well as with the 6 KB rotating slots (0.488 / 0.491 vs 0.483 ms).
+// Four slots (three chunks of look-ahead, streaming kernel) measured 0.483 - 0.486 ms per step against 0.478 - 0.480 with
+// three slots beside a resident A operand.
 using EpiBackCodeH = EpiBackCodeHT<2>;
 
 }  // namespace sc

@@ -6,6 +6,7 @@ autoencoders/ensemble.py:15-193 (same constructor, attributes, state_dict keys a
 from __future__ import annotations
 
 import ctypes as C
+import weakref
 from collections.abc import Mapping
 from typing import Dict, List, Optional
 
@@ -490,7 +491,11 @@ class FunctionalEnsemble:
         ops_key = None
         if f16 and not tied and not grad_only:
             ops_key = (ws_ptr.value, M, d, N, enc.data_ptr(), enc._version, dec.data_ptr(), dec._version)
-        ops_valid = ops_key is not None and getattr(self, "_ops_key", None) == ops_key
+        # the tensor OBJECTS must be the same as well: a caller who assigns a new tensor into .params (big_sweep.py:198)
+        # can get the old one's address back from the caching allocator, with an equal version counter
+        last_refs = getattr(self, "_ops_refs", (None, None))
+        same_objects = last_refs[0] is not None and last_refs[0]() is enc and last_refs[1]() is dec
+        ops_valid = ops_key is not None and same_objects and getattr(self, "_ops_key", None) == ops_key
         self._ops_key = None  # re-armed below once the step has been enqueued
         args = nat.ScStepArgs(
             M=M, B=B, d=d, N=N, tied=int(tied), x_per_member=int(per_member),
@@ -521,6 +526,7 @@ class FunctionalEnsemble:
             nat.check(L.sc_sae_step(C.byref(args)), "sc_sae_step")
         if ops_key is not None:
             self._ops_key = ops_key
+            self._ops_refs = (weakref.ref(enc), weakref.ref(dec))
         loss_dict = {"loss": losses[0], "l_reconstruction": losses[1], "l_l1": losses[2]}
         if masked:
             pass  # loss, l_reconstruction, l_l1 only

@@ -498,10 +498,15 @@ def test_operand_handover_matches_rebuild(shape):
     data = make_sparse_data(6 * B, d, 2 * d, 6, seed=9).cuda()
     for i in range(6):
         x = data[i * B:(i + 1) * B]
-        if i == 3:  # a caller edits the decoder in place (big_sweep.py:198 style): the engine has to pick it up
+        if i == 3:  # a caller edits the decoder in place: the engine has to pick it up
             for e in (ens_a, ens_b):
                 e.params["decoder"][:, 5:9].mul_(1.5)
                 e.params["encoder"][:, 2].add_(0.01)
+        if i == 4:  # ... or assigns a NEW tensor (big_sweep.py:198), which may even reuse the old one's address
+            for e in (ens_a, ens_b):
+                new = e.params["decoder"].clone()
+                new[:, 11:13] *= 0.5
+                e.params["decoder"] = new
         ens_b._ops_key = None  # always rebuild
         la, aa = ens_a.step_batch(x)
         lb, ab = ens_b.step_batch(x)

@@ -363,6 +363,8 @@ struct alignas(64) AdamSub {
     float* wsq_out;                     // [G][wsq_parts][N] partial sums of w^2 of the updated decoder (decoder problem only)
     CUtensorMap half_map;               // fp16 io map (box 64 x 32) of the [G][N][d] copy of the updated parameter
     int half_on;
+    CUtensorMap half_t_map;             // fp16 io map (box 32 x 64) of the TRANSPOSED copy [G][d][N] (decoder: the decode
+    int half_t_on;                      // GEMM reads the dictionary K-major from it)
 };
 struct alignas(64) AdamParams {
 AdamSub sub[2];   // one per batched problem (untied: [0] encoder, [1] decoder)
@@ -395,7 +397,7 @@ struct EpiAdamT {
     static constexpr int kHalves = SPLIT;
     static constexpr int kColSplit = SPLIT;
     static constexpr int W = 32 / SPLIT;  // columns per thread and chunk
-    static constexpr int kIoBufs = 7;  // 2 sets x (p, mu, nu) x 4 KB + one fp16 tile [32][64] (fold mode)
+    static constexpr int kIoBufs = 8;  // 2 sets x (p, mu, nu) x 4 KB + fp16 tiles [32][64] and (transposed) [64][32] (fold mode)
     using Sub = AdamSub;
     using Params = AdamParams;
     // warp 3 of CTA `cta` of `nctas` (no role in the GEMM)
@@ -521,7 +523,10 @@ struct EpiAdamT {
                 tma_store_3d(&u.p_map, b, col, row0, c.g);
                 tma_store_3d(&u.mu_map, b + kIoTileBytes, col, row0, c.g);
                 tma_store_3d(&u.nu_map, b + 2 * kIoTileBytes, col, row0, c.g);
-                if (half_store) tma_store_3d(&u.half_map, io.buf + 6 * kIoTileBytes, half_store_col, row0, c.g);
+                if (half_store) {
+                    tma_store_3d(&u.half_map, io.buf + 6 * kIoTileBytes, half_store_col, row0, c.g);
+                    if (u.half_t_on) tma_store_3d(&u.half_t_map, io.buf + 7 * kIoTileBytes, row0, half_store_col, c.g);
+                }
             }
             half_store = false;
         }
@@ -549,6 +554,16 @@ struct EpiAdamT {
                 hh[t] = *reinterpret_cast<const uint32_t*>(&x);
             }
             sts_128u(row + (((4 * hsel + h * (W / 8) + j) ^ (lane & 7)) << 4), hh[0], hh[1], hh[2], hh[3]);
+        }
+        if (u.half_t_on) {
+            // transposed copy: element (row = lane, column j) goes to row (32 hsel + j) of a [64][32] fp16 tile, 64-byte
+            // rows with the 64-byte swizzle; the 32 lanes write one whole row per instruction
+            const uint32_t tt = smem_u32(io.buf + 7 * kIoTileBytes) + ((lane & 7) << 1);
+#pragma unroll
+            for (int j = 0; j < W; ++j) {
+                const int r = 32 * hsel + h * W + j;
+                sts_u16(tt + r * 64 + ((((lane >> 3) ^ (r >> 1)) & 3) << 4), __half_as_ushort(half_sat(pv[j])));
+            }
         }
         if (hsel == 1 || last) {  // the caller's fence + barrier precede the store it issues for us
             half_store_col = c.col0 + (co & ~63);

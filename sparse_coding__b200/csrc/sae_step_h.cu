@@ -93,7 +93,8 @@ __global__ void __launch_bounds__(256) step_prologue_h_kernel(const float* __res
                                                               __half* __restrict__ D_h, float* __restrict__ inv_norm, int N,
                                                               int d, float4* __restrict__ zero, long long zero_n4,
                                                               int fold, const float* __restrict__ wsq, int wsq_parts,
-                                                              int norm_blocks, int* __restrict__ range_flag, int step_tag) {
+                                                              int norm_blocks, int* __restrict__ range_flag, int step_tag,
+                                                              __half* __restrict__ D_ht) {
     pdl_launch_dependents();
     pdl_wait();
     __shared__ float sh[8];
@@ -166,6 +167,9 @@ __global__ void __launch_bounds__(256) step_prologue_h_kernel(const float* __res
     float inv = 1.f / fmaxf(nrm, 1e-8f);
     if (lane == 0) inv_norm[(long long)m * N + n] = nrm < 1e-8f ? -inv : inv;
     if (fold) inv = 1.f;  // fold mode: the copy stays un-normalised (RowNorm in sae_epilogues.cuh)
+    if (fold && D_ht) {   // ... and the decode GEMM reads it transposed, [d][N] (only steps that rebuild the copies come here)
+        for (int i = lane; i < d; i += 32) D_ht[((long long)m * d + i) * N + n] = half_sat(W[row + i]);
+    }
     uint2* dst = reinterpret_cast<uint2*>(D_h + row);
     for (int i = lane; i < d4; i += 32) {
         const float4 v = src[i];
@@ -198,6 +202,7 @@ __global__ void __launch_bounds__(256) residual_h_kernel(const float4* __restric
 
 struct StepWsH {
     __half *x_h, *enc_h, *D_h, *r_h, *dz_h;
+    __half* dec_ht;  // fold mode: transposed fp16 copy [M][d][N] of the decoder (K-major operand of the decode GEMM)
     float *inv_norm, *l1_part, *mse_part, *db_part, *s_part, *bnorm, *x_hat;
     float *gacc_enc, *gacc_dec;  // split-K weight gradients of small ensembles: fp32 accumulation buffers [M][N][d]
     int g45_split;               // > 1: the weight-gradient GEMMs run split-K into them, Adam follows as its own pass
@@ -219,6 +224,7 @@ static StepWsH carve_step_h(void* base, int M, int B, int d, int N, int tied, in
     // what a step may leave for the next one (ScStepArgs.operands_valid) comes first: its offsets depend on M, N, d only
     w.enc_h = tied ? nullptr : halves(Mz * Nz * dz_);
     w.D_h = halves(Mz * Nz * dz_);
+    w.dec_ht = tied ? nullptr : halves(Mz * Nz * dz_);
     w.wsq_parts = ceil_div(d, pick_bn(d)) * 2;  // one slot per column tile and epilogue warp of a row quarter
     w.wsq = c.floats(Mz * w.wsq_parts * Nz);
     w.inv_norm = c.floats(Mz * Nz);
@@ -344,6 +350,9 @@ int sae_step_f16_impl(const ScStepArgs& a) {
     const bool g45_split = w.g45_split > 1 && !grad_mode;
     const bool fold = !a.tied && !grad_mode && !g45_split && fold_enabled();
     const float* fold_inv = fold ? w.inv_norm : nullptr;
+    // the decode GEMM reads the dictionary K-major from a transposed copy the Adam epilogue also leaves (SC_B200_DICT_T=0: no)
+    static const bool dict_t_env = !(getenv("SC_B200_DICT_T") && getenv("SC_B200_DICT_T")[0] == '0');
+    const bool dict_t = fold && dict_t_env;
     const bool params_ready = fold && a.operands_valid != 0;
 
     // SC_B200_DUP=k (debug): launch kernel k (0 prologue, 1 G1, 2 G2, 3 G3; all idempotent) twice, so that the
@@ -362,11 +371,11 @@ int sae_step_f16_impl(const ScStepArgs& a) {
         if (a.tied)
             launch_k(step_prologue_h_kernel, dim3(blocks), dim3(256), 0, st, a.bias, w.bnorm, M, reinterpret_cast<const float4*>(a.x),
                      reinterpret_cast<uint2*>(w.x_h), x_n4, x_blocks, nullptr, nullptr, a.enc, w.D_h, w.inv_norm, N, d, zero, zero_n4,
-                     0, nullptr, 0, 0, a.range_flag, a.step_tag);
+                     0, nullptr, 0, 0, a.range_flag, a.step_tag, nullptr);
         else
             launch_k(step_prologue_h_kernel, dim3(blocks), dim3(256), 0, st, a.bias, w.bnorm, M, reinterpret_cast<const float4*>(a.x),
                      reinterpret_cast<uint2*>(w.x_h), x_n4, x_blocks, a.enc, w.enc_h, a.dec, w.D_h, w.inv_norm, N, d, zero, zero_n4,
-                     fold ? 1 : 0, w.wsq, w.wsq_parts, norm_blocks, a.range_flag, a.step_tag);
+                     fold ? 1 : 0, w.wsq, w.wsq_parts, norm_blocks, a.range_flag, a.step_tag, dict_t ? w.dec_ht : nullptr);
         SC_CUDA(cudaGetLastError(), "prologue launch");
     }
     prof_mark(st, "prologue");
@@ -379,24 +388,28 @@ int sae_step_f16_impl(const ScStepArgs& a) {
         SC_TRY((run_gemm_short_k<EpiEncodeTH>(N, B, M, &s, ep, st)));
     }
     prof_mark(st, "G1_encode");
+    // fold mode: the dictionary comes K-major from its transposed copy (both operands MN-major cost 12 % of the mainloop)
+    const Operand g2_dict = dict_t ? kmajor_h(w.dec_ht, d, N, M, Nd) : mnmajor_h(w.D_h, d, N, M, Nd);
     for (int rep = 0; rep < (dup_k == 2 ? 2 : 1); ++rep)
     if (w.g2_split > 1) {  // G2, split K: partial tiles reduce-added into x_hat, then the residual pass
-        Seg s{codesT_mn(c_h), mnmajor_h(w.D_h, d, N, M, Nd)};
+        Seg s{codesT_mn(c_h), g2_dict};
         EpiReduceTile::Params ep{};
         {
             const char* err = nullptr;
             const int rc = make_io_map(&ep.out_map, w.x_hat, B, d, M, Bd, &err);
             if (rc != 0) return fail(rc, "%s", err ? err : "io tensor map creation failed");
         }
-        SC_TRY((run_gemm<true, true, EpiReduceTile, true>(B, d, M, &s, 1, ep, st, false, 0, w.g2_split)));
+        if (dict_t) SC_TRY((run_gemm<true, false, EpiReduceTile, true>(B, d, M, &s, 1, ep, st, false, 0, w.g2_split)));
+        else SC_TRY((run_gemm<true, true, EpiReduceTile, true>(B, d, M, &s, 1, ep, st, false, 0, w.g2_split)));
         launch_k(residual_h_kernel, dim3(w.n_mse, M), dim3(256), 0, st, reinterpret_cast<const float4*>(w.x_hat),
                  reinterpret_cast<const float4*>(a.x), reinterpret_cast<uint2*>(w.r_h), w.mse_part, Bd / 4, w.n_mse,
                  a.x_per_member ? Bd / 4 : 0LL);
         SC_CUDA(cudaGetLastError(), "residual launch");
     } else {   // G2
-        Seg s{codesT_mn(c_h), mnmajor_h(w.D_h, d, N, M, Nd)};
+        Seg s{codesT_mn(c_h), g2_dict};
         EpiDecodeH::Params ep{a.x, w.r_h, w.mse_part, a.x_per_member ? Bd : 0, Bd};
-        SC_TRY((run_gemm<true, true, EpiDecodeH, true>(B, d, M, &s, 1, ep, st)));
+        if (dict_t) SC_TRY((run_gemm<true, false, EpiDecodeH, true>(B, d, M, &s, 1, ep, st)));
+        else SC_TRY((run_gemm<true, true, EpiDecodeH, true>(B, d, M, &s, 1, ep, st)));
     }
     prof_mark(st, "G2_decode_mse");
     for (int rep = 0; rep < (dup_k == 3 ? 2 : 1); ++rep) {   // G3 (transposed)
@@ -422,7 +435,9 @@ int sae_step_f16_impl(const ScStepArgs& a) {
             u.half_on = fold ? 1 : 0;
             if (fold) {
                 const char* err = nullptr;
-                const int rc = make_io_map_h64(&u.half_map, projected ? w.D_h : w.enc_h, N, d, M, Nd, &err);
+                int rc = make_io_map_h64(&u.half_map, projected ? w.D_h : w.enc_h, N, d, M, Nd, &err);
+                u.half_t_on = (projected && dict_t) ? 1 : 0;
+                if (rc == 0 && projected && dict_t) rc = make_io_map_ht(&u.half_t_map, w.dec_ht, d, N, M, Nd, &err);
                 if (rc != 0) return fail(rc, "%s", err ? err : "io tensor map creation failed");
             }
             SC_TRY(io_map(&u.p_map, p, N, d, M, Nd));

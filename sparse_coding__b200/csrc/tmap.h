@@ -46,4 +46,9 @@ int make_io_map_h(CUtensorMap* out, const void* base, int64_t rows, int64_t cols
 int make_io_map_h64(CUtensorMap* out, const void* base, int64_t rows, int64_t cols, int64_t g, int64_t gstride,
                     const char** err);
 
+// fp16 [G][rows][cols] map with box {32 cols, 64 rows} = 64-byte rows, 64-byte swizzle: the TRANSPOSED copy of a
+// [32 x 64] register tile (rows of the map = columns of the accumulator)
+int make_io_map_ht(CUtensorMap* out, const void* base, int64_t rows, int64_t cols, int64_t g, int64_t gstride,
+                   const char** err);
+
 }  // namespace sc

@@ -150,6 +150,7 @@ def run_reference(args):
 class ClockSampler:
     def __init__(self, index):
         self.index, self.samples, self.reasons, self.stop = index, [], set(), False
+        self.power = []
         self.max_mhz = None
         try:
             import pynvml
@@ -167,6 +168,7 @@ class ClockSampler:
         while not self.stop and self.nv is not None:
             try:
                 self.samples.append(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM))
+                self.power.append(self.nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0)
                 r = self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.h) if hasattr(
                     self.nv, "nvmlDeviceGetCurrentClocksEventReasons") else self.nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
                 for bit, nm in names.items():
@@ -174,7 +176,7 @@ class ClockSampler:
                         self.reasons.add(nm)
             except Exception:
                 pass
-            time.sleep(0.02)
+            time.sleep(0.005)
 
     def __enter__(self):
         self.t.start()
@@ -186,7 +188,8 @@ class ClockSampler:
 
     def summary(self):
         med = float(np.median(self.samples)) if self.samples else None
-        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples),
+                "power_w": float(np.median(self.power)) if self.power else None}
 
 
 def measure_tf32_peak(device):

@@ -222,24 +222,26 @@ int run_gemm(int M, int N, int G, const Seg* segs, int nseg, const typename Epi:
     return launch_plan<A_MN, B_MN, Epi, F16>(pl, ep, stream);
 }
 
-// SC_B200_RESA=0: never use the resident-A kernel (A/B runs)
-inline bool use_resident_a() {
+// SC_B200_RESA: bit mask of the GEMMs that may use the resident-A kernel (1: encode, 2: dL/dz; 0: never).  Default 2:
+// same-box runs at the headline shape give 0.482 ms per step with neither, 0.485 with the encode GEMM only, 0.478 with
+// the dL/dz GEMM only, 0.479 with both.
+inline bool use_resident_a(int which) {
     static int v = -1;
     if (v < 0) {
         const char* e = getenv("SC_B200_RESA");
-        v = (e && e[0] == '0') ? 0 : 1;
+        v = e ? atoi(e) : 2;
     }
-    return v == 1;
+    return (v & which) != 0;
 }
 
 // fp16 K-major GEMM with a short K loop: the resident-A kernel (gemm_core2_res.cuh) when it applies, else run_gemm
 template <class Epi>
-int run_gemm_short_k(int M, int N, int G, const Seg* seg, const typename Epi::Params& ep, cudaStream_t stream) {
+int run_gemm_short_k(int M, int N, int G, const Seg* seg, const typename Epi::Params& ep, cudaStream_t stream, int which) {
     if (M <= 0 || N <= 0 || G <= 0) return 0;
-    // measured at the headline shape (ms per step, resident / streaming): 0.472 / 0.477 with 8 column tiles per row tile,
-    // 0.831 / 0.828 with 16, 1.541 / 1.518 with 32 - beyond ~8 the contiguous tile ranges cost more than the saved
+    // measured with the dL/dz GEMM (ms per step, resident / streaming): 0.478 / 0.482 with 8 column tiles per row tile,
+    // 0.827 / 0.824 with 16, 1.527 / 1.500 with 32 - beyond ~8 the contiguous tile ranges cost more than the saved
     // operand traffic gives back
-    const bool ok = use_resident_a() && seg->a.elem_bytes == 2 && !seg->a.mn_major && !seg->b.mn_major &&
+    const bool ok = use_resident_a(which) && seg->a.elem_bytes == 2 && !seg->a.mn_major && !seg->b.mn_major &&
                     seg->a.k <= 64 * kResMaxKBlocks && pick_bn(N) >= 128 && ceil_div(N, pick_bn(N)) <= 8;
     const int kblocks = ceil_div(seg->a.k, 64);
     const bool fits = pick_bn(N) == 256 ? GemmCfgRes<256, Epi>::stages(kblocks) >= 2 : GemmCfgRes<128, Epi>::stages(kblocks) >= 2;

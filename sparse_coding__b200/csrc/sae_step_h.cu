@@ -385,7 +385,7 @@ int sae_step_f16_impl(const ScStepArgs& a) {
         SC_TRY(io_map_h(&ep.c_map, c_h, N, B, M, NB, ldb));
         ep.bias = a.bias; ep.l1_part = w.l1_part; ep.dict_size = a.dict_size;
         ep.fold_inv = fold_inv; ep.code_scale = a.out_code_scale;
-        SC_TRY((run_gemm_short_k<EpiEncodeTH>(N, B, M, &s, ep, st)));
+        SC_TRY((run_gemm_short_k<EpiEncodeTH>(N, B, M, &s, ep, st, 1)));
     }
     prof_mark(st, "G1_encode");
     // fold mode: the dictionary comes K-major from its transposed copy (both operands MN-major cost 12 % of the mainloop)
@@ -420,7 +420,7 @@ int sae_step_f16_impl(const ScStepArgs& a) {
         ep.l1 = a.l1_alpha; ep.bias = a.bias; ep.db_part = w.db_part; ep.s_part = w.s_part;
         ep.l1_scale = 0.5f * (float)d; ep.tied = a.tied; ep.feats = N;
         ep.fold_inv = fold_inv;
-        SC_TRY((run_gemm_short_k<EpiBackCodeH>(N, B, M, &s, ep, st)));
+        SC_TRY((run_gemm_short_k<EpiBackCodeH>(N, B, M, &s, ep, st, 2)));
     }
     prof_mark(st, "G3_back_code");
     {

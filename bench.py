@@ -515,9 +515,9 @@ def run_ours(args):
     eb = 2.0 if fmt == "f16" else 4.0  # bytes per element of the GEMM operands / intermediates c, r, dz
     MBN, MNd, MBd, Bd = eb * M * B * N_FEATS, eb * M * N_FEATS * D_ACT, eb * M * B * D_ACT, eb * B * D_ACT
     adam_bytes = 2 * 6 * 4.0 * M * N_FEATS * D_ACT  # encoder + decoder: read and write p, mu, nu in fp32
-    # fp16 mode: the Adam epilogue also writes the fp16 copies of both updated dictionaries for the next step (2 * MNd),
-    # which replaces the separate pass that re-read the fp32 weights
-    handover = 2 * MNd if fmt == "f16" else 0.0
+    # fp16 mode: the Adam epilogue also writes the fp16 copies of the updated dictionaries for the next step (encoder,
+    # decoder and the decoder transposed: 3 * MNd), which replaces the separate pass that re-read the fp32 weights
+    handover = 3 * MNd if fmt == "f16" else 0.0
     launch_bytes = {"G1_encode": MBN + MNd + Bd, "G2_decode_mse": MBN + MNd + MBd + 4.0 * B * D_ACT,
                     "G3_back_code": 2 * MBN + MNd + MBd, "G45_dW_adam": 2 * MBN + adam_bytes + MBd + Bd + handover}
     tf32_peak = measure_tf32_peak(device)

@@ -9,6 +9,7 @@
 
 #include <cuda_fp16.h>
 
+#include <algorithm>
 #include <vector>
 
 #include "epi_store.cuh"
@@ -196,6 +197,12 @@ int main(int argc, char** argv) {
         for (auto& v : hA[s]) v = g_eb == 2 ? __half2float(__float2half((rand() / (float)RAND_MAX) * 2.f - 1.f)) : host_rn_tf32((rand() / (float)RAND_MAX) * 2.f - 1.f);
         for (auto& v : hB[s]) v = g_eb == 2 ? __half2float(__float2half((rand() / (float)RAND_MAX) * 2.f - 1.f)) : host_rn_tf32((rand() / (float)RAND_MAX) * 2.f - 1.f);
     }
+    if (getenv("SC_SELFTEST_ZERO")) {  // all-zero operands: same instruction stream, no data toggling (power probe)
+        for (int s = 0; s < nseg; ++s) {
+            std::fill(hA[s].begin(), hA[s].end(), 0.f);
+            std::fill(hB[s].begin(), hB[s].end(), 0.f);
+        }
+    }
     auto A = [&](int s, int g, int m, int k) { return hA[s][g * szA + (a_mn ? (size_t)k * ldA + m : (size_t)m * ldA + k)]; };
     auto B = [&](int s, int g, int n, int k) { return hB[s][g * szB + (b_mn ? (size_t)k * ldB + n : (size_t)n * ldB + k)]; };
 
@@ -251,7 +258,7 @@ int main(int argc, char** argv) {
     // timing (only meaningful for big shapes)
     cudaEvent_t e0, e1;
     CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
-    const int reps = 20;
+    const int reps = getenv("SC_SELFTEST_REPS") ? atoi(getenv("SC_SELFTEST_REPS")) : 20;
     CK(cudaEventRecord(e0));
     for (int r = 0; r < reps; ++r) { DISPATCH(64) DISPATCH(128) DISPATCH(256) }
     CK(cudaEventRecord(e1));

@@ -176,7 +176,7 @@ class ClockSampler:
                         self.reasons.add(nm)
             except Exception:
                 pass
-            time.sleep(0.005)
+            time.sleep(0.001)
 
     def __enter__(self):
         self.t.start()
@@ -187,6 +187,9 @@ class ClockSampler:
         self.t.join(timeout=1)
 
     def summary(self):
+        # the first sample is taken as the timed region starts, before the load shows in the clock / power readings
+        if len(self.samples) > 2:
+            self.samples, self.power = self.samples[1:], self.power[1:]
         med = float(np.median(self.samples)) if self.samples else None
         return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples),
                 "power_w": float(np.median(self.power)) if self.power else None}

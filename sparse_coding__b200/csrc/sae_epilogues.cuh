@@ -389,7 +389,9 @@ AdamSub sub[2];   // one per batched problem (untied: [0] encoder, [1] decoder)
 // per scheduler issues in the time the tile's HBM traffic takes, two warps per scheduler overlap each other's
 // latencies.  Warp half 0 of the quarter owns the TMA traffic; one 64-thread named barrier per chunk orders the
 // other warp's row writes before the tile stores.
-template <int SPLIT>
+// FIO = 1 adds the two fp16 staging tiles of fold mode (8 KB per quarter: one operand-pipeline stage less); launches
+// that never hand operands over (TF32 mode, tied, gradient-only, split-K) use FIO = 0.
+template <int SPLIT, int FIO = 0>
 struct EpiAdamT {
     // HBM-bound epilogue: what matters is how many tile loads and stores are in flight.  Per quarter TWO sets of
     // p / mu / nu staging tiles: while one set is computed on and stored, the other is already loading the next chunk -
@@ -397,7 +399,7 @@ struct EpiAdamT {
     static constexpr int kHalves = SPLIT;
     static constexpr int kColSplit = SPLIT;
     static constexpr int W = 32 / SPLIT;  // columns per thread and chunk
-    static constexpr int kIoBufs = 8;  // 2 sets x (p, mu, nu) x 4 KB + fp16 tiles [32][64] and (transposed) [64][32] (fold mode)
+    static constexpr int kIoBufs = 6 + 2 * FIO;  // 2 sets x (p, mu, nu) x 4 KB (+ fp16 tiles [32][64] and, transposed, [64][32])
     using Sub = AdamSub;
     using Params = AdamParams;
     // warp 3 of CTA `cta` of `nctas` (no role in the GEMM)
@@ -479,7 +481,7 @@ struct EpiAdamT {
         }
         // the owner has seen the previous chunk's stores read their tiles: only now may the other warp of the quarter
         // overwrite the fp16 tile those stores included
-        if (SPLIT == 2 && p.fold) bar_sync_named(5 + c.warp_q, 64);
+        if (SPLIT == 2 && FIO && p.fold) bar_sync_named(5 + c.warp_q, 64);
         if (p.g_scale != 1.f || p.fold) {
 #pragma unroll
             for (int j = 0; j < W; ++j) v[j] *= gsc;
@@ -514,7 +516,7 @@ struct EpiAdamT {
         } else {
 #pragma unroll
             for (int j = 0; j < W; ++j) adam_update(pv[j], mv[j], nv[j], v[j], p.a);
-            if (p.fold) leave_operands(pv, co, h, next_co < 0);
+            if (FIO && p.fold) leave_operands(pv, co, h, next_co < 0);
             io_write_cols<W>(b, lane, h, pv);
             io_write_cols<W>(b + kIoTileBytes, lane, h, mv);
             io_write_cols<W>(b + 2 * kIoTileBytes, lane, h, nv);
@@ -579,7 +581,8 @@ struct EpiAdamT {
         }
     }
 };
-using EpiAdam = EpiAdamT<1>;
-using EpiAdamS = EpiAdamT<2>;
+using EpiAdam = EpiAdamT<1, 0>;
+using EpiAdamF = EpiAdamT<1, 1>;  // fold mode
+using EpiAdamS = EpiAdamT<2, 1>;  // fold mode, column-split experiment
 
 }  // namespace sc

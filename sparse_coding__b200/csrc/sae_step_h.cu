@@ -458,15 +458,15 @@ int sae_step_f16_impl(const ScStepArgs& a) {
                           {codesT_k(c_h), mnmajor_h(w.r_h, d, B, M, Bd)}};
             SC_TRY(fill(e.sub[0], a.enc, a.enc_mu, a.enc_nu, g45_split ? w.gacc_enc : a.grad_enc, false));
             SC_TRY(fill(e.sub[1], a.dec, a.dec_mu, a.dec_nu, g45_split ? w.gacc_dec : (grad_mode ? a.grad_dec : nullptr), true));
-            if (adam_split() && !g45_split) SC_TRY((run_gemm<false, true, EpiAdamS, true>(N, d, M, s45, 2, e, st, true)));
+            if (fold && adam_split()) SC_TRY((run_gemm<false, true, EpiAdamS, true>(N, d, M, s45, 2, e, st, true)));
+            else if (fold) SC_TRY((run_gemm<false, true, EpiAdamF, true>(N, d, M, s45, 2, e, st, true)));
             else SC_TRY((run_gemm<false, true, EpiAdam, true>(N, d, M, s45, 2, e, st, true, 0, ks)));
         } else {
             Seg s[2] = {{codesT_k(c_h), mnmajor_h(w.r_h, d, B, M, Bd)},
                         {codesT_k(w.dz_h), mnmajor_h(w.x_h, d, B, xg, Bd)}};
             SC_TRY(fill(e.sub[0], a.enc, a.enc_mu, a.enc_nu, g45_split ? w.gacc_enc : a.grad_enc, true));
             e.sub[1] = e.sub[0];
-            if (adam_split() && !g45_split) SC_TRY((run_gemm<false, true, EpiAdamS, true>(N, d, M, s, 2, e, st)));
-            else SC_TRY((run_gemm<false, true, EpiAdam, true>(N, d, M, s, 2, e, st, false, 0, ks)));
+            SC_TRY((run_gemm<false, true, EpiAdam, true>(N, d, M, s, 2, e, st, false, 0, ks)));  // tied: never fold mode
         }
         if (g45_split) {  // Adam from the accumulated gradients (elementwise, the tensors are small in this regime)
             const long long n4 = (long long)M * Nd / 4;

@@ -98,7 +98,9 @@ typedef struct {
      * encoder / decoder and the decoder's row norms in the workspace, so the next step does not have to re-read the
      * fp32 weights.  operands_valid = 1 tells the step that this hand-over is intact: same workspace, same M, d, N, and
      * nothing but sc_sae_step has written the parameters since the previous full step; 0 (always safe) rebuilds the
-     * copies.
+     * copies.  The library itself remembers per workspace whether its last fp16 step ran in this mode (it is used up
+     * to 3072 rows per step; larger batches run the preparation pass, which is cheaper there); an operand_format 0 step
+     * in the same workspace overwrites the copies, pass 0 after one.
      * In this mode the stored codes are c / ||W_d|| per feature; out_code_scale ([M,N] floats; operand_format 1 only;
      * required with out_c, otherwise optional) receives the factor that sc_codes_to_float applies to the stored codes:
      * ||W_d|| here, 1 in every other mode. */

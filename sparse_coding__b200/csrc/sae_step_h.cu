@@ -6,6 +6,8 @@
 // The codes and dz are kept TRANSPOSED, c^T / dz^T = [M][N][ldb] with ldb = B rounded up to 8 (TMA strides are
 // multiples of 16 bytes): G1 and G3 are computed with the feature as the accumulator row, so their epilogues
 // touch whole rows, G2 reads c^T MN-major and the weight-gradient GEMMs read c^T / dz^T K-major.
+#include <mutex>
+
 #include "../../include/sc_b200.h"
 #include "host_common.cuh"
 #include "sae_epilogues_h.cuh"
@@ -140,41 +142,58 @@ __global__ void __launch_bounds__(256) step_prologue_h_kernel(const float* __res
         }
         return;
     }
+    // eight dictionary rows per block, one warp each; the transposed copy leaves through shared memory so that every
+    // thread stores eight consecutive features (16 bytes) of one activation dimension
+    extern __shared__ __align__(16) uint8_t prologue_smem[];
+    __half* tile = reinterpret_cast<__half*>(prologue_smem);  // [8 rows][d] when D_ht is wanted
     const int row_blocks = (N + 7) >> 3;
     const int m = blk / row_blocks;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int n = (blk - m * row_blocks) * 8 + warp;
-    if (n >= N) return;
-    const long long row = ((long long)m * N + n) * d;
+    const int n0 = (blk - m * row_blocks) * 8;
+    const int n = n0 + warp;
     const int d4 = d >> 2;
-    if (enc_h) {
-        const float4* src = reinterpret_cast<const float4*>(enc + row);
-        uint2* dst = reinterpret_cast<uint2*>(enc_h + row);
+    if (n < N) {
+        const long long row = ((long long)m * N + n) * d;
+        if (enc_h) {
+            const float4* src = reinterpret_cast<const float4*>(enc + row);
+            uint2* dst = reinterpret_cast<uint2*>(enc_h + row);
+            for (int i = lane; i < d4; i += 32) {
+                const float4 v = src[i];
+                __half2 h[2] = {half2_sat(v.x, v.y), half2_sat(v.z, v.w)};
+                dst[i] = *reinterpret_cast<uint2*>(h);
+            }
+        }
+        const float4* src = reinterpret_cast<const float4*>(W + row);
+        float ss = 0.f;
         for (int i = lane; i < d4; i += 32) {
             const float4 v = src[i];
-            __half2 h[2] = {half2_sat(v.x, v.y), half2_sat(v.z, v.w)};
-            dst[i] = *reinterpret_cast<uint2*>(h);
+            ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
         }
+        ss = warp_sum(ss);
+        const float nrm = sqrtf(ss);
+        float inv = 1.f / fmaxf(nrm, 1e-8f);
+        if (lane == 0) inv_norm[(long long)m * N + n] = nrm < 1e-8f ? -inv : inv;
+        if (fold) inv = 1.f;  // fold mode: the copies stay un-normalised (RowNorm in sae_epilogues.cuh)
+        uint2* dst = reinterpret_cast<uint2*>(D_h + row);
+        for (int i = lane; i < d4; i += 32) {
+            const float4 v = src[i];
+            __half2 h[2] = {half2_sat(v.x * inv, v.y * inv), half2_sat(v.z * inv, v.w * inv)};
+            dst[i] = *reinterpret_cast<uint2*>(h);
+            if (D_ht) reinterpret_cast<uint2*>(tile + warp * d)[i] = *reinterpret_cast<uint2*>(h);
+        }
+    } else if (D_ht) {
+        for (int i = lane; i < d; i += 32) tile[warp * d + i] = __float2half(0.f);
     }
-    const float4* src = reinterpret_cast<const float4*>(W + row);
-    float ss = 0.f;
-    for (int i = lane; i < d4; i += 32) {
-        const float4 v = src[i];
-        ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
-    }
-    ss = warp_sum(ss);
-    const float nrm = sqrtf(ss);
-    float inv = 1.f / fmaxf(nrm, 1e-8f);
-    if (lane == 0) inv_norm[(long long)m * N + n] = nrm < 1e-8f ? -inv : inv;
-    if (fold) inv = 1.f;  // fold mode: the copy stays un-normalised (RowNorm in sae_epilogues.cuh)
-    if (fold && D_ht) {   // ... and the decode GEMM reads it transposed, [d][N] (only steps that rebuild the copies come here)
-        for (int i = lane; i < d; i += 32) D_ht[((long long)m * d + i) * N + n] = half_sat(W[row + i]);
-    }
-    uint2* dst = reinterpret_cast<uint2*>(D_h + row);
-    for (int i = lane; i < d4; i += 32) {
-        const float4 v = src[i];
-        __half2 h[2] = {half2_sat(v.x * inv, v.y * inv), half2_sat(v.z * inv, v.w * inv)};
-        dst[i] = *reinterpret_cast<uint2*>(h);
+    if (D_ht) {  // (block-uniform)
+        __syncthreads();
+        // D_ht[m][j][n0 .. n0 + 7]: N is a multiple of 8 in fp16 mode, so the eight features exist or none does
+        if (n0 + 8 <= N)
+            for (int j = threadIdx.x; j < d; j += blockDim.x) {
+                __half col[8];
+#pragma unroll
+                for (int r = 0; r < 8; ++r) col[r] = tile[r * d + j];
+                *reinterpret_cast<uint4*>(D_ht + ((long long)m * d + j) * N + n0) = *reinterpret_cast<const uint4*>(col);
+            }
     }
 }
 
@@ -224,7 +243,7 @@ static StepWsH carve_step_h(void* base, int M, int B, int d, int N, int tied, in
     // what a step may leave for the next one (ScStepArgs.operands_valid) comes first: its offsets depend on M, N, d only
     w.enc_h = tied ? nullptr : halves(Mz * Nz * dz_);
     w.D_h = halves(Mz * Nz * dz_);
-    w.dec_ht = tied ? nullptr : halves(Mz * Nz * dz_);
+    w.dec_ht = halves(Mz * Nz * dz_);
     w.wsq_parts = ceil_div(d, pick_bn(d)) * 2;  // one slot per column tile and epilogue warp of a row quarter
     w.wsq = c.floats(Mz * w.wsq_parts * Nz);
     w.inv_norm = c.floats(Mz * Nz);
@@ -300,14 +319,42 @@ static bool adam_split() {
     return v == 1;
 }
 
-// SC_B200_FOLD=0 keeps the operand-preparation pass in every step (A/B runs)
-static bool fold_enabled() {
+// Operand hand-over (fold mode) or the operand-preparation pass in every step?  The hand-over saves a constant (the
+// pass over the fp32 weights); what it costs - a pipeline stage of the weight-gradient kernel for its fp16 staging
+// tiles - grows with the batch.  Same-box step times, hand-over / preparation pass: 0.4715 / 0.483 ms at 2048 rows,
+// 0.830 / 0.826 at 4096, 1.507 / 1.481 at 8192.  SC_B200_FOLD: 0 never, 1 (default) up to 3072 rows, 2 always.
+static bool fold_enabled(int B) {
     static int v = -1;
     if (v < 0) {
         const char* e = getenv("SC_B200_FOLD");
-        v = (e && e[0] == '0') ? 0 : 1;
+        v = e ? atoi(e) : 1;
     }
-    return v == 1;
+    return v == 2 || (v == 1 && B <= 3072);
+}
+
+// What the last fp16 step left in a workspace: the caller's operands_valid only says that nobody else touched the
+// parameters - whether the copies in THIS workspace are hand-over copies (un-normalised, fold mode) or the preparation
+// pass's (normalised) depends on which mode that step ran in, and the mode depends on the batch size.
+struct HandoverRecord {
+    const void* ws;
+    int M, d, N;
+    bool fold;
+};
+static HandoverRecord g_handover[16];
+static int g_handover_next = 0;
+static std::mutex g_handover_mutex;
+static bool handover_intact(const void* ws, int M, int d, int N) {
+    std::lock_guard<std::mutex> lock(g_handover_mutex);
+    for (const HandoverRecord& r : g_handover)
+        if (r.ws == ws) return r.fold && r.M == M && r.d == d && r.N == N;
+    return false;
+}
+static void handover_record(const void* ws, int M, int d, int N, bool fold) {
+    std::lock_guard<std::mutex> lock(g_handover_mutex);
+    for (HandoverRecord& r : g_handover)
+        if (r.ws == ws) { r = HandoverRecord{ws, M, d, N, fold}; return; }
+    g_handover[g_handover_next] = HandoverRecord{ws, M, d, N, fold};
+    g_handover_next = (g_handover_next + 1) % 16;
 }
 
 static bool f16_supported(int B, int d, int N) {
@@ -348,12 +395,14 @@ int sae_step_f16_impl(const ScStepArgs& a) {
     // norms of the UPDATED parameters in the workspace, and the next step (operands_valid) skips the pass over the fp32
     // weights: its prologue only turns the epilogue's partial sums of w^2 into 1/||W_d row||.
     const bool g45_split = w.g45_split > 1 && !grad_mode;
-    const bool fold = !a.tied && !grad_mode && !g45_split && fold_enabled();
+    const bool fold = !a.tied && !grad_mode && !g45_split && fold_enabled(B);
     const float* fold_inv = fold ? w.inv_norm : nullptr;
-    // the decode GEMM reads the dictionary K-major from a transposed copy the Adam epilogue also leaves (SC_B200_DICT_T=0: no)
+    // the decode GEMM reads the dictionary K-major from a transposed fp16 copy, made by the prologue when it rebuilds the
+    // operand copies and kept current by the Adam epilogue in fold mode (SC_B200_DICT_T=0: MN-major from the plain copy)
     static const bool dict_t_env = !(getenv("SC_B200_DICT_T") && getenv("SC_B200_DICT_T")[0] == '0');
-    const bool dict_t = fold && dict_t_env;
-    const bool params_ready = fold && a.operands_valid != 0;
+    const bool dict_t = dict_t_env && (size_t)d * 16 <= 48 * 1024;  // the prologue's transposing tile: 16 d bytes of shared memory
+    const bool params_ready = fold && a.operands_valid != 0 && handover_intact(a.workspace, M, d, N);
+    handover_record(a.workspace, M, d, N, fold);
 
     // SC_B200_DUP=k (debug): launch kernel k (0 prologue, 1 G1, 2 G2, 3 G3; all idempotent) twice, so that the
     // difference in step time is that kernel's marginal cost inside the real launch chain
@@ -369,13 +418,15 @@ int sae_step_f16_impl(const ScStepArgs& a) {
         float4* zero = reinterpret_cast<float4*>(w.zero_from);
         const long long zero_n4 = static_cast<long long>(w.zero_bytes / 16);
         if (a.tied)
-            launch_k(step_prologue_h_kernel, dim3(blocks), dim3(256), 0, st, a.bias, w.bnorm, M, reinterpret_cast<const float4*>(a.x),
-                     reinterpret_cast<uint2*>(w.x_h), x_n4, x_blocks, nullptr, nullptr, a.enc, w.D_h, w.inv_norm, N, d, zero, zero_n4,
-                     0, nullptr, 0, 0, a.range_flag, a.step_tag, nullptr);
+            launch_k(step_prologue_h_kernel, dim3(blocks), dim3(256), dict_t ? (size_t)d * 16 : 0, st, a.bias, w.bnorm, M,
+                     reinterpret_cast<const float4*>(a.x), reinterpret_cast<uint2*>(w.x_h), x_n4, x_blocks, nullptr, nullptr,
+                     a.enc, w.D_h, w.inv_norm, N, d, zero, zero_n4, 0, nullptr, 0, 0, a.range_flag, a.step_tag,
+                     dict_t ? w.dec_ht : nullptr);
         else
-            launch_k(step_prologue_h_kernel, dim3(blocks), dim3(256), 0, st, a.bias, w.bnorm, M, reinterpret_cast<const float4*>(a.x),
-                     reinterpret_cast<uint2*>(w.x_h), x_n4, x_blocks, a.enc, w.enc_h, a.dec, w.D_h, w.inv_norm, N, d, zero, zero_n4,
-                     fold ? 1 : 0, w.wsq, w.wsq_parts, norm_blocks, a.range_flag, a.step_tag, dict_t ? w.dec_ht : nullptr);
+            launch_k(step_prologue_h_kernel, dim3(blocks), dim3(256), (dict_t && !params_ready) ? (size_t)d * 16 : 0, st, a.bias,
+                     w.bnorm, M, reinterpret_cast<const float4*>(a.x), reinterpret_cast<uint2*>(w.x_h), x_n4, x_blocks, a.enc,
+                     w.enc_h, a.dec, w.D_h, w.inv_norm, N, d, zero, zero_n4, fold ? 1 : 0, w.wsq, w.wsq_parts, norm_blocks,
+                     a.range_flag, a.step_tag, dict_t ? w.dec_ht : nullptr);
         SC_CUDA(cudaGetLastError(), "prologue launch");
     }
     prof_mark(st, "prologue");

@@ -528,3 +528,24 @@ def test_operand_handover_matches_rebuild(shape):
         _, fw = R.sae_forward(P["encoder"][m], P["encoder_bias"][m], P["decoder"][m], orc.buffers["l1_alpha"][m],
                               orc.buffers["bias_decay"][m], x.cpu())
         assert rel_err(aa["c"][m].cpu(), fw["c"]) < 3e-3
+
+
+def test_operand_handover_survives_a_change_of_mode():
+    """The hand-over is only used up to 3072 rows per step (beyond that the preparation pass is cheaper), and the two
+    modes leave different copies in the same workspace: steps of 256, 3200 and again 256 rows must agree with an
+    ensemble that rebuilds its operand copies before every step."""
+    M, d, N = 2, 128, 192
+    ens_a, _ = _pair("untied", d, N, [1e-3, 1e-2], seed=3)
+    ens_b, _ = _pair("untied", d, N, [1e-3, 1e-2], seed=3)
+    if ens_a.operand_format == "tf32":
+        pytest.skip("fp16 operand mode switched off")
+    data = make_sparse_data(4000, d, 2 * d, 6, seed=10).cuda()
+    for i, rows in enumerate((256, 256, 3200, 3200, 256, 256, 512)):
+        x = data[:rows] if i % 2 == 0 else data[4000 - rows:]
+        ens_b._ops_key = None
+        la, _ = ens_a.step_batch(x)
+        lb, _ = ens_b.step_batch(x)
+        for k in la:
+            assert torch.allclose(la[k], lb[k], rtol=2e-5, atol=1e-7), (i, rows, k, la[k], lb[k])
+    for k in ens_a.params:
+        assert rel_err(ens_a.params[k], ens_b.params[k]) < 1e-4, k

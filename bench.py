@@ -150,7 +150,7 @@ def run_reference(args):
 class ClockSampler:
     def __init__(self, index):
         self.index, self.samples, self.reasons, self.stop = index, [], set(), False
-        self.power = []
+
         self.max_mhz = None
         try:
             import pynvml
@@ -168,7 +168,6 @@ class ClockSampler:
         while not self.stop and self.nv is not None:
             try:
                 self.samples.append(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM))
-                self.power.append(self.nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0)
                 r = self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.h) if hasattr(
                     self.nv, "nvmlDeviceGetCurrentClocksEventReasons") else self.nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
                 for bit, nm in names.items():
@@ -189,10 +188,9 @@ class ClockSampler:
     def summary(self):
         # the first sample is taken as the timed region starts, before the load shows in the clock / power readings
         if len(self.samples) > 2:
-            self.samples, self.power = self.samples[1:], self.power[1:]
+            self.samples = self.samples[1:]
         med = float(np.median(self.samples)) if self.samples else None
-        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples),
-                "power_w": float(np.median(self.power)) if self.power else None}
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
 
 
 def measure_tf32_peak(device):

@@ -199,6 +199,9 @@ typedef struct {
     void* stream;
     const float* l1_coef_dev; /* device scalar or NULL: when given it replaces l1_coef, so a caller that holds the
                                  coefficient as a device tensor (buffers["l1_alpha"], big_sweep.py:186) need not sync */
+    int32_t pair_format;      /* 0: fp16 (hi, lo) operand pairs when d and N are multiples of 64 (values must stay below
+                                 65504 in magnitude: codes are bounded by the row norms of x for a unit-row dictionary),
+                                 else TF32 pairs; 1: always TF32 pairs (fp32 range) */
 } ScFistaArgs;
 size_t sc_fista_workspace_bytes(int32_t B, int32_t d, int32_t N);
 int sc_fista(const ScFistaArgs* args);

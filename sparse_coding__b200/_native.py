@@ -89,7 +89,7 @@ class ScFistaArgs(C.Structure):
         ("momentum", C.POINTER(C.c_float)),
         ("out_a", C.c_void_p), ("out_res", C.c_void_p), ("out_eta", C.c_void_p),
         ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t), ("stream", C.c_void_p),
-        ("l1_coef_dev", C.c_void_p),
+        ("l1_coef_dev", C.c_void_p), ("pair_format", C.c_int32),
     ]
 
 

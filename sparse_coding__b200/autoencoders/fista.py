@@ -31,6 +31,14 @@ def momentum_sequence(num_iter: int) -> np.ndarray:
     return out
 
 
+def _pair_format(x, a0):
+    """0 (fp16 operand pairs, twice the tensor rate) unless the data could leave fp16's range: every FISTA iterate is
+    bounded by a small multiple of the largest row norm of x for a unit-row dictionary, the warm start is checked
+    directly.  One tiny reduction + sync per call (a call is hundreds of GEMMs)."""
+    bound = max(float(torch.linalg.vector_norm(x, dim=1).max()), float(a0.abs().max()))
+    return 0 if bound < 8192.0 else 1
+
+
 def fista_native(batch, learned_dict, l1_coef, coefficients, num_iter, eta=None):
     """(ahat, Res) of fista.py:99-128 on the GPU."""
     L = nat.lib()
@@ -64,7 +72,7 @@ def fista_native(batch, learned_dict, l1_coef, coefficients, num_iter, eta=None)
                            l1_coef=l1_f, eta=eta_f, momentum=mom.ctypes.data_as(C.POINTER(C.c_float)),
                            out_a=nat.ptr(out_a), out_res=nat.ptr(out_res), out_eta=nat.ptr(out_eta),
                            workspace=ws_ptr, workspace_bytes=ws_bytes, stream=nat.stream_ptr(dev),
-                           l1_coef_dev=nat.ptr(l1_dev))
+                           l1_coef_dev=nat.ptr(l1_dev), pair_format=_pair_format(x, a0))
     with torch.cuda.device(dev):
         nat.check(L.sc_fista(C.byref(args)), "sc_fista")
     return out_a, out_res, out_eta

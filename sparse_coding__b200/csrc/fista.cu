@@ -471,7 +471,7 @@ static int fista_impl(const ScFistaArgs& a) {
     const long long BN_ = (long long)B * N, Nd = (long long)N * d;
 
     SC_TRY(split(a.D, w.D_hi, w.D_lo, nullptr, Nd, st));
-    const bool f16 = fista_f16(B, d, N);
+    const bool f16 = a.pair_format == 0 && fista_f16(B, d, N);
     if (!f16) SC_TRY(split(a.a0, w.y_hi, w.y_lo, nullptr, BN_, st));
     SC_CUDA(cudaMemcpyAsync(a.out_a, a.a0, BN_ * sizeof(float), cudaMemcpyDeviceToDevice, st), "copy a0");
 

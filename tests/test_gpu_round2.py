@@ -206,3 +206,18 @@ def test_gemm_f32_is_fp32_accurate(a_mn, b_mn):
     out = nat.gemm_f32(Ad, Bd, a_mn=a_mn, b_mn=b_mn)
     # fp32-level (|ref| up to ~40, K = 100; plain TF32 would be ~1e-2): the lo*lo terms and the accumulator truncation remain
     assert float((out.cpu().double() - ref).abs().max()) < 1e-4
+
+
+def test_fista_large_magnitudes_take_the_tf32_pairs():
+    """fp16 operand pairs hold |v| < 65504: activations with row norms beyond 8192 make the host mirror ask for TF32
+    pairs (ScFistaArgs.pair_format = 1), and the codes still match the float64 oracle at the scaled tolerance."""
+    import sparse_coding__b200 as sc
+    B, d, N = 128, 128, 256
+    torch.manual_seed(50)
+    D = R.row_normalise(torch.randn(N, d))[0]
+    x = 3.0e4 * make_sparse_data(B, d, 2 * d, 6, seed=51)
+    a0 = torch.relu(x @ D.T)
+    a_ref, _ = R.fista(x.double(), D.double(), 1e-2, a0.double(), 20)
+    a, _ = sc.FunctionalFista.fista(x.cuda(), D.cuda(), 1e-2, a0.cuda(), 20, "cuda")
+    assert torch.isfinite(a).all()
+    assert float((a.cpu().double() - a_ref).abs().max()) < 1e-6 * float(a_ref.abs().max()) + 1e-4

@@ -111,6 +111,60 @@ def cpu_reference_steps(batch, steps, warmup, threads, budget_s=None):
     return batch * M_PER_GPU * done / dt, dt / done, done
 
 
+def gpu_reference_steps(batch, steps, warmup, allow_tf32):
+    """The same UNMODIFIED reference code (oracle/_ref) with device="cuda": the reference as its users run it - torch
+    eager + functorch vmap/grad + torchopt-style Adam, cuBLAS SGEMM (true fp32, or TF32 when `allow_tf32`).  Not the
+    contract's reference arm (that one is the CPU run): `bench.py --impl reference --ref-device cuda` prints it as an
+    extra comparison line.  Device-timed with CUDA events.  Returns (member-activations / s, seconds per step)."""
+    os.environ["SC_REFERENCE_ROOT"] = os.path.join(ROOT, "oracle", "_ref")
+    from oracle import ref_loader
+    import warnings
+    warnings.filterwarnings("ignore", message=".*batching rule.*")
+    ns = ref_loader.load()
+    torch.backends.cuda.matmul.allow_tf32 = bool(allow_tf32)
+    torch.backends.cudnn.allow_tf32 = bool(allow_tf32)
+    dev = torch.device("cuda", 0)
+    torch.manual_seed(0)
+    models = [ns.FunctionalSAE.init(D_ACT, N_FEATS, float(l1)) for l1 in l1_values(M_PER_GPU)]
+    ens = ns.FunctionalEnsemble(models, ns.FunctionalSAE, ns.torchopt.adam, {"lr": 1e-3}, device=dev)
+    data = make_chunk(batch * 4, D_ACT, 1, dev)
+    for i in range(warmup):
+        ens.step_batch(data[(i % 4) * batch:(i % 4 + 1) * batch])
+    torch.cuda.synchronize(dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        ens.step_batch(data[(i % 4) * batch:(i % 4 + 1) * batch])
+    e1.record()
+    torch.cuda.synchronize(dev)
+    sec = e0.elapsed_time(e1) * 1e-3 / steps
+    torch.backends.cuda.matmul.allow_tf32 = False
+    return batch * M_PER_GPU / sec, sec
+
+
+def run_reference_on_gpu(args):
+    """Extra comparison (not the contract's arm): the reference's own code on the B200 through torch."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    if not reference_available():
+        print(json.dumps({"impl": "reference", "ref_device": "cuda", "unavailable": "oracle/_ref is missing"}))
+        return
+    B, steps, warmup = args.batch, max(2, min(args.steps, 100)), max(3, min(args.warmup, 10))
+    out = {}
+    for name, tf32 in (("fp32", False), ("tf32_allowed", True)):
+        val, sec = gpu_reference_steps(B, steps, warmup, tf32)
+        out[name] = {"value": val, "ms_per_step": sec * 1e3}
+    print(json.dumps({
+        "impl": "reference", "ref_device": "cuda", "metric": METRIC, "unit": UNIT, "value": out["fp32"]["value"],
+        "ms_per_step": out["fp32"]["ms_per_step"], "tf32_allowed": out["tf32_allowed"], "steps": steps, "warmup": warmup,
+        "n_gpus": 1, "higher_is_better": True, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "pythia70m_l2_untied_sae", "d": D_ACT, "n_feats": N_FEATS, "members_per_gpu": M_PER_GPU,
+                   "batch": B},
+        "note": "the reference's FunctionalEnsemble.step_batch (oracle/_ref, unmodified; optree / torchopt / torchtyping "
+                "from oracle/shims) on cuda:0 through torch eager + functorch: cuBLAS SGEMM, ~100 ATen launches per step",
+    }))
+
+
 def run_reference(args):
     """CPU arm: the reference's own code on the box's host cores, same workload (B rows per step, M members), the
     driver's --steps / --warmup (the timed steps stop after ~150 s if that many do not fit; `steps` says how many ran)."""
@@ -641,12 +695,17 @@ def main():
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--batch", type=int, default=2048)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--ref-device", default="cpu", choices=["cpu", "cuda"],
+                    help="with --impl reference: cpu (the contract's arm) or cuda (extra: the reference through torch on the GPU)")
     ap.add_argument("--quick", action="store_true", help="profiling runs: skip e2e, peak measurement and the CPU baseline")
     ap.add_argument("--no-extras", action="store_true", help="skip the secondary records (other configs, config-5 data-parallel)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
-        run_reference(args)
+        if args.ref_device == "cuda":
+            run_reference_on_gpu(args)
+        else:
+            run_reference(args)
     else:
         run_ours(args)
 

@@ -24,24 +24,35 @@ __global__ void to_half_kernel(const float4* __restrict__ in, uint2* __restrict_
     }
 }
 
-// aux output: c [M][B][N] fp32 from the engine's c^T [M][N][ldb] fp16 (32 x 32 tiles through shared memory)
+// aux output: c [M][B][N] fp32 from the engine's c^T [M][N][ldb] fp16 (64 x 64 tiles through shared memory)
 // row_scale [M][N] (or nullptr): what the stored codes of feature n have to be multiplied by (fold mode keeps c / ||W_d||)
 __global__ void __launch_bounds__(256) codes_to_float_kernel(const __half* __restrict__ cT, float* __restrict__ out, int B,
                                                              int N, int ldb, const float* __restrict__ row_scale) {
     pdl_launch_dependents();
     pdl_wait();
-    __shared__ float t[32][33];
-    const int g = blockIdx.z, n0 = blockIdx.y * 32, b0 = blockIdx.x * 32;
-    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-    for (int i = ty; i < 32; i += 8) {
-        const int n = n0 + i, b = b0 + tx;
-        const float sc = (row_scale && n < N) ? row_scale[(long long)g * N + n] : 1.f;
-        t[i][tx] = (n < N && b < B) ? __half2float(cT[((long long)g * N + n) * ldb + b]) * sc : 0.f;
+    // 64 x 64 tile: 128-byte rows in (half2 per lane), two 128-byte row halves out per warp and batch row
+    __shared__ float t[64][65];
+    const int g = blockIdx.z, n0 = blockIdx.y * 64, b0 = blockIdx.x * 64;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int i = warp; i < 64; i += 8) {
+        const int n = n0 + i, b = b0 + 2 * lane;
+        float v0 = 0.f, v1 = 0.f;
+        if (n < N && b < B) {  // ldb is B rounded up to 8, so the pair at an even b < B lies inside the row
+            const float sc = row_scale ? row_scale[(long long)g * N + n] : 1.f;
+            const float2 v = __half22float2(*reinterpret_cast<const __half2*>(cT + ((long long)g * N + n) * ldb + b));
+            v0 = v.x * sc;
+            v1 = v.y * sc;
+        }
+        t[i][2 * lane] = v0;
+        t[i][2 * lane + 1] = v1;
     }
     __syncthreads();
-    for (int i = ty; i < 32; i += 8) {
-        const int b = b0 + i, n = n0 + tx;
-        if (b < B && n < N) out[((long long)g * B + b) * N + n] = t[tx][i];
+    for (int i = warp; i < 64; i += 8) {
+        const int b = b0 + i;
+        if (b >= B) continue;
+        float* row = out + ((long long)g * B + b) * N + n0;
+        if (n0 + lane < N) row[lane] = t[lane][i];
+        if (n0 + lane + 32 < N) row[lane + 32] = t[lane + 32][i];
     }
 }
 
@@ -532,7 +543,7 @@ int sae_step_f16_impl(const ScStepArgs& a) {
     }
     prof_mark(st, "G45_dW_adam");  // includes the finalize work (loss scalars + bias Adam) on the idle warps
     if (a.out_c) {  // caller wants the fp32 aux tensor as well
-        launch_k(codes_to_float_kernel, dim3(ceil_div(B, 32), ceil_div(N, 32), M), dim3(256), 0, st, c_h, a.out_c, B, N, w.ldb,
+        launch_k(codes_to_float_kernel, dim3(ceil_div(B, 64), ceil_div(N, 64), M), dim3(256), 0, st, c_h, a.out_c, B, N, w.ldb,
                  static_cast<const float*>(a.out_code_scale));
         SC_CUDA(cudaGetLastError(), "c conversion launch");
     }
@@ -546,8 +557,8 @@ extern "C" int sc_sae_step_f16_supported(int32_t B, int32_t d, int32_t N) { retu
 extern "C" int sc_codes_to_float(const void* codes_t, const float* code_scale, float* out, int32_t M, int32_t B, int32_t N,
                                  void* stream) {
     if (!codes_t || !out || M <= 0 || B <= 0 || N <= 0) return sc::fail(-1, "sc_codes_to_float: bad arguments");
-    if (M > 65535 || (N + 31) / 32 > 65535) return sc::fail(-1, "sc_codes_to_float: M or N too large for one launch");
-    sc::launch_k(sc::codes_to_float_kernel, dim3(sc::ceil_div(B, 32), sc::ceil_div(N, 32), M), dim3(256), 0,
+    if (M > 65535 || (N + 63) / 64 > 65535) return sc::fail(-1, "sc_codes_to_float: M or N too large for one launch");
+    sc::launch_k(sc::codes_to_float_kernel, dim3(sc::ceil_div(B, 64), sc::ceil_div(N, 64), M), dim3(256), 0,
                  static_cast<cudaStream_t>(stream), static_cast<const __half*>(codes_t), out, B, N, (B + 7) & ~7, code_scale);
     const cudaError_t e = cudaGetLastError();
     return e == cudaSuccess ? 0 : sc::cuda_fail(e, "codes conversion launch");

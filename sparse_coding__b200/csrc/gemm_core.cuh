@@ -86,6 +86,12 @@ template <class E, class = void>
 struct EpiColSplitOf { static constexpr int v = 1; };
 template <class E>
 struct EpiColSplitOf<E, decltype((void)E::kColSplit)> { static constexpr int v = E::kColSplit; };
+// Columns per chunk() call (Epi::kChunkW: 32 or 64).  64 halves the per-chunk bookkeeping (fences, TMA issue, barrier
+// arming) of epilogues that move a staging tile per chunk.
+template <class E, class = void>
+struct EpiChunkWOf { static constexpr int v = 32; };
+template <class E>
+struct EpiChunkWOf<E, decltype((void)E::kChunkW)> { static constexpr int v = E::kChunkW; };
 // number of owners of staging memory: one per epilogue warp, or one per row quarter when the columns are split
 template <class E>
 struct EpiIoOwnersOf { static constexpr int v = EpiColSplitOf<E>::v == 2 ? 4 : 4 * EpiHalvesOf<E>::v; };
@@ -140,6 +146,22 @@ SC_DEVICE void epilogue_tile(const typename Epi::Params& ep, const RowCtx& ctx, 
             tmem_ld16(taddr + c * 32 + ctx.half * 16, v);
             tmem_ld_wait();
             epi.chunk(c * 32, v, (c + 1 < BN / 32) ? (c + 1) * 32 : -1);
+        }
+    } else if constexpr (EpiChunkWOf<Epi>::v == 64) {
+        constexpr int kUnits = BN / 64, kChunks = (kUnits + kH - 1) / kH;
+        static_assert(BN % 64 == 0, "64-column chunks need a tile width that is a multiple of 64");
+        mbar_wait(full_bar, parity);
+        tc_fence_after();
+#pragma unroll 1
+        for (int i = 0; i < kChunks; ++i) {
+            const int c = ctx.half + i * kH;
+            if (c < kUnits) {
+                float v[64];
+                tmem_ld32(taddr + c * 64, *reinterpret_cast<float(*)[32]>(&v[0]));
+                tmem_ld32(taddr + c * 64 + 32, *reinterpret_cast<float(*)[32]>(&v[32]));
+                tmem_ld_wait();
+                epi.chunk(c * 64, v, (c + kH < kUnits) ? (c + kH) * 64 : -1);
+            }
         }
     } else {
         constexpr int kChunks = (BN / 32 + kH - 1) / kH;

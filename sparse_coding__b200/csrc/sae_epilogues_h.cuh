@@ -240,19 +240,23 @@ using EpiEncodeTH = EpiEncodeTHT<2>;
 // stored from there, and once that store has read it the slot takes the c tile two chunks ahead - across tile
 // boundaries too (static schedule) - so loads fly during two chunks of arithmetic and 6 KB per warp is all the
 // staging this epilogue needs (the resident-A kernel has little shared memory to spare).
-template <int H, int SLOTS = 3>
+template <int H, int SLOTS = 3, int W = 32>
 struct EpiBackCodeHT {
-    // H warps per row quarter (4 H epilogue warps): 8 / H chunks of 32 columns per warp and 256-wide tile.
+    // H warps per row quarter (4 H epilogue warps): 256 / W / H chunks of W columns per warp and 256-wide tile.
     // SLOTS staging slots per warp: SLOTS - 1 chunks of look-ahead (3: what fits beside a resident A operand).
+    // W = 64: chunks of 64 batch columns (128-byte rows, SWIZZLE_128B, 4 KB slots) - half the per-chunk bookkeeping.
+    static_assert(W == 32 || W == 64, "chunk width");
     static constexpr int kHalves = H;
-    static constexpr int kPerTile = 8 / H;
+    static constexpr int kChunkW = W;
+    static constexpr int kPerTile = 256 / W / H;
     static constexpr int kSlots = SLOTS;
     static constexpr int kAhead = SLOTS - 1;
-    static constexpr int kIoBytes = kSlots * 2048;  // per warp (kernels that count staging in 4 KB units round up)
-    static constexpr int kIoBufs = (SLOTS + 1) / 2;
+    static constexpr int kSlotBytes = 32 * W * 2;
+    static constexpr int kIoBytes = kSlots * kSlotBytes;  // per warp (kernels that count staging in 4 KB units round up)
+    static constexpr int kIoBufs = (kIoBytes + 4095) / 4096;
     static_assert(kSlots <= kIoBars, "one load barrier per slot");
     struct alignas(64) Params {
-        CUtensorMap c_map;    // fp16 io map of c^T  [G][N][B]
+        CUtensorMap c_map;    // fp16 io map of c^T  [G][N][B]  (box W batch columns x 32 features)
         CUtensorMap dz_map;   // fp16 io map of dz^T [G][N][B]  (scaled by B d / 2)
         const float* l1;      // [G]
         const float* bias;    // [G][N] (tied only)
@@ -270,8 +274,8 @@ struct EpiBackCodeHT {
     // warp state that outlives the tile, in the free bits of the warp's phase word: bits 8-10 the slot of the next
     // chunk to consume, bits 12-14 how many chunks after the current one have been requested (0..kAhead)
     SC_DEVICE void request(int slot, int g, int row0, int bcol) const {
-        io_expect(io, 2048, slot);
-        tma_load_3d(&p.c_map, io.bar + slot, io.buf + slot * 2048, bcol, row0, g);
+        io_expect(io, kSlotBytes, slot);
+        tma_load_3d(&p.c_map, io.bar + slot, io.buf + slot * kSlotBytes, bcol, row0, g);
     }
     SC_DEVICE EpiBackCodeHT(const Params& p_, const RowCtx& c_, const EpiIo& io_)
         : p(p_), c(c_), io(io_), db(0.f), db1(0.f), s(0.f), s1(0.f) {
@@ -284,51 +288,55 @@ struct EpiBackCodeHT {
     SC_DEVICE void prefetch(int) {}
     // chunk j of this warp in a tile that starts at batch column col0 exists (live chunks are a prefix in j)
     SC_DEVICE bool live(int col0, int j) const {
-        const int cw = (c.half + j * H) * 32;
+        const int cw = (c.half + j * H) * W;
         return j < kPerTile && cw < c.bn && col0 + cw < c.N;
     }
     // the k-th (1..kAhead) live chunk after chunk i of the current tile, in processing order
     SC_DEVICE bool nth_next(int i, int k, int& g, int& row0, int& bcol) const {
         for (int j = i + 1; live(c.col0, j); ++j)
-            if (--k == 0) { g = c.g; row0 = c.row - (threadIdx.x & 31); bcol = c.col0 + (c.half + j * H) * 32; return true; }
+            if (--k == 0) { g = c.g; row0 = c.row - (threadIdx.x & 31); bcol = c.col0 + (c.half + j * H) * W; return true; }
         if (c.next_g < 0) return false;
         for (int j = 0; live(c.next_col0, j); ++j)
-            if (--k == 0) { g = c.next_g; row0 = c.next_row0; bcol = c.next_col0 + (c.half + j * H) * 32; return true; }
+            if (--k == 0) { g = c.next_g; row0 = c.next_row0; bcol = c.next_col0 + (c.half + j * H) * W; return true; }
         return false;
     }
     template <bool TIED>
-    SC_DEVICE void body(uint8_t* slot, const float (&v)[32]) {
+    SC_DEVICE void body(uint8_t* slot, const float (&v)[W]) {
         const int lane = threadIdx.x & 31;
-        const uint32_t rs = smem_u32(slot) + lane * 64;
-        const int sw = (lane >> 1) & 3;  // SWIZZLE_64B: 16-byte chunk j of row r sits at chunk j ^ ((r >> 1) & 3)
-        uint4 hc[4];
+        const uint32_t rs = smem_u32(slot) + lane * (2 * W);
+        // SWIZZLE_64B (W = 32): 16-byte piece j of row r sits at piece j ^ ((r >> 1) & 3); SWIZZLE_128B (W = 64): j ^ (r & 7)
+        const int sw = W == 32 ? (lane >> 1) & 3 : lane & 7;
 #pragma unroll
-        for (int j = 0; j < 4; ++j) hc[j] = lds_128u(rs + ((j ^ sw) << 4));  // all loads in flight first
+        for (int jb = 0; jb < W / 8; jb += 4) {
+            uint4 hc[4];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const uint32_t w[4] = {hc[j].x, hc[j].y, hc[j].z, hc[j].w};
-            uint32_t o[4];
+            for (int j = 0; j < 4; ++j) hc[j] = lds_128u(rs + (((jb + j) ^ sw) << 4));  // all loads in flight first
 #pragma unroll
-            for (int t = 0; t < 4; ++t) {
-                const float2 cf = __half22float2(*reinterpret_cast<const __half2*>(&w[t]));
-                const float q0 = v[8 * j + 2 * t], q1 = v[8 * j + 2 * t + 1];
-                // sign bit set <=> z < 0 (code -0);  > 0 <=> c > 0
-                const float t0 = cf.x > 0.f ? q0 + l1_term : q0;
-                const float t1 = cf.y > 0.f ? q1 + l1_term : q1;
-                const float d0 = __float_as_int(cf.x) < 0 ? 0.f : t0;
-                const float d1 = __float_as_int(cf.y) < 0 ? 0.f : t1;
-                const __half2 dh = half2_sat(d0, d1);
-                o[t] = *reinterpret_cast<const uint32_t*>(&dh);
-                db += d0; db1 += d1;
-                s = fmaf(cf.x, q0, s); s1 = fmaf(cf.y, q1, s1);
-                if (TIED) { s = fmaf(d0, cf.x - bn, s); s1 = fmaf(d1, cf.y - bn, s1); }
+            for (int j = 0; j < 4; ++j) {
+                const uint32_t w[4] = {hc[j].x, hc[j].y, hc[j].z, hc[j].w};
+                uint32_t o[4];
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                    const float2 cf = __half22float2(*reinterpret_cast<const __half2*>(&w[t]));
+                    const float q0 = v[8 * (jb + j) + 2 * t], q1 = v[8 * (jb + j) + 2 * t + 1];
+                    // sign bit set <=> z < 0 (code -0);  > 0 <=> c > 0
+                    const float t0 = cf.x > 0.f ? q0 + l1_term : q0;
+                    const float t1 = cf.y > 0.f ? q1 + l1_term : q1;
+                    const float d0 = __float_as_int(cf.x) < 0 ? 0.f : t0;
+                    const float d1 = __float_as_int(cf.y) < 0 ? 0.f : t1;
+                    const __half2 dh = half2_sat(d0, d1);
+                    o[t] = *reinterpret_cast<const uint32_t*>(&dh);
+                    db += d0; db1 += d1;
+                    s = fmaf(cf.x, q0, s); s1 = fmaf(cf.y, q1, s1);
+                    if (TIED) { s = fmaf(d0, cf.x - bn, s); s1 = fmaf(d1, cf.y - bn, s1); }
+                }
+                sts_128u(rs + (((jb + j) ^ sw) << 4), o[0], o[1], o[2], o[3]);  // dz over the codes just read
             }
-            sts_128u(rs + ((j ^ sw) << 4), o[0], o[1], o[2], o[3]);  // dz over the codes just read
         }
     }
-    SC_DEVICE void chunk(int co, float (&v)[32], int /*next_co*/) {
+    SC_DEVICE void chunk(int co, float (&v)[W], int /*next_co*/) {
         const int lane = threadIdx.x & 31;
-        const int i = (co >> 5) / H;  // index of this chunk among the warp's chunks of the tile
+        const int i = (co / W) / H;  // index of this chunk among the warp's chunks of the tile
         const int bcol = c.col0 + co;
         if (bcol >= c.N) return;      // the whole chunk lies beyond the batch (warp-uniform): nothing was requested
         const int row0 = c.row - lane;
@@ -338,7 +346,7 @@ struct EpiBackCodeHT {
             if (lane == 0) request(cons, c.g, row0, bcol);
             ahead = 1;
         }
-        uint8_t* slot = io.buf + cons * 2048;
+        uint8_t* slot = io.buf + cons * kSlotBytes;
         io_wait_loads(io, cons);
         if (p.tied) body<true>(slot, v);
         else body<false>(slot, v);
@@ -351,13 +359,32 @@ struct EpiBackCodeHT {
         --ahead;
         cons = cons == kSlots - 1 ? 0 : cons + 1;
         // keep kAhead chunks in flight: the slots they go to were stored at least one bulk group before the store above
-        bool waited = false;
-        for (int k = ahead + 1; k <= kAhead; ++k) {
-            int g, r0, bc;
-            if (!nth_next(i, k, g, r0, bc)) break;
-            if (!waited) { io_wait_stores_read_n<1>(); waited = true; }
-            if (lane == 0) request((cons + k - 1) % kSlots, g, r0, bc);
-            ahead = k;
+        constexpr int kFullW = kPerTile * H * W;
+        if (ahead == kAhead - 1 && c.bn == kFullW && c.col0 + kFullW <= c.N &&
+            (i + kAhead < kPerTile || c.next_g < 0 || c.next_col0 + kFullW <= c.N)) {
+            // steady state on full tiles (ncu: the general search below was a third of this epilogue's instructions):
+            // exactly one request, the chunk kAhead places on - in this tile or at the start of the next one
+            static_assert(kAhead <= kPerTile, "look-ahead reaches at most into the next tile");
+            const int j = i + kAhead;
+            const bool here = j < kPerTile;
+            if (here || c.next_g >= 0) {
+                io_wait_stores_read_n<1>();
+                const int jj = here ? j : j - kPerTile;
+                const int sl = cons + kAhead - 1 >= kSlots ? cons + kAhead - 1 - kSlots : cons + kAhead - 1;
+                if (lane == 0)
+                    request(sl, here ? c.g : c.next_g, here ? row0 : c.next_row0,
+                            (here ? c.col0 : c.next_col0) + (c.half + jj * H) * W);
+                ahead = kAhead;
+            }
+        } else {
+            bool waited = false;
+            for (int k = ahead + 1; k <= kAhead; ++k) {
+                int g, r0, bc;
+                if (!nth_next(i, k, g, r0, bc)) break;
+                if (!waited) { io_wait_stores_read_n<1>(); waited = true; }
+                if (lane == 0) request((cons + k - 1) % kSlots, g, r0, bc);
+                ahead = k;
+            }
         }
         *io.phase = (*io.phase & ~0x7700u) | (static_cast<uint32_t>(cons) << 8) | (static_cast<uint32_t>(ahead) << 12);
     }
@@ -373,5 +400,6 @@ struct EpiBackCodeHT {
 // Four slots (three chunks of look-ahead, streaming kernel) measured 0.483 - 0.486 ms per step against 0.478 - 0.480 with
 // three slots beside a resident A operand.
 using EpiBackCodeH = EpiBackCodeHT<2>;
+using EpiBackCodeH64 = EpiBackCodeHT<2, 3, 64>;  // streaming kernel only (12 KB of staging per warp)
 
 }  // namespace sc

@@ -474,15 +474,32 @@ int sae_step_f16_impl(const ScStepArgs& a) {
         else SC_TRY((run_gemm<true, true, EpiDecodeH, true>(B, d, M, &s, 1, ep, st)));
     }
     prof_mark(st, "G2_decode_mse");
+    // G3 chunk width: 64 batch columns per epilogue chunk (streaming kernel, 12 KB of staging per warp) or 32 (6 KB per
+    // warp, which fits beside a resident A operand).  SC_B200_G3W=32|64.
+    static const int g3w_env = getenv("SC_B200_G3W") ? atoi(getenv("SC_B200_G3W")) : 64;
+    const bool g3_wide = g3w_env == 64 && pick_bn(B) == 256;
     for (int rep = 0; rep < (dup_k == 3 ? 2 : 1); ++rep) {   // G3 (transposed)
         Seg s{kmajor_h(w.D_h, N, d, M, Nd), kmajor_h(w.r_h, B, d, M, Bd)};
-        EpiBackCodeH::Params ep{};
-        SC_TRY(io_map_h(&ep.c_map, c_h, N, B, M, NB, ldb));
-        SC_TRY(io_map_h(&ep.dz_map, w.dz_h, N, B, M, NB, ldb));
-        ep.l1 = a.l1_alpha; ep.bias = a.bias; ep.db_part = w.db_part; ep.s_part = w.s_part;
-        ep.l1_scale = 0.5f * (float)d; ep.tied = a.tied; ep.feats = N;
-        ep.fold_inv = fold_inv;
-        SC_TRY((run_gemm_short_k<EpiBackCodeH>(N, B, M, &s, ep, st, 2)));
+        auto fill = [&](auto& ep) {
+            ep.l1 = a.l1_alpha; ep.bias = a.bias; ep.db_part = w.db_part; ep.s_part = w.s_part;
+            ep.l1_scale = 0.5f * (float)d; ep.tied = a.tied; ep.feats = N;
+            ep.fold_inv = fold_inv;
+        };
+        if (g3_wide) {
+            EpiBackCodeH64::Params ep{};
+            const char* err = nullptr;
+            int rc = make_io_map_h64(&ep.c_map, c_h, N, B, M, NB, &err, ldb);
+            if (rc == 0) rc = make_io_map_h64(&ep.dz_map, w.dz_h, N, B, M, NB, &err, ldb);
+            if (rc != 0) return fail(rc, "%s", err ? err : "io tensor map creation failed");
+            fill(ep);
+            SC_TRY((run_gemm<false, false, EpiBackCodeH64, true>(N, B, M, &s, 1, ep, st)));
+        } else {
+            EpiBackCodeH::Params ep{};
+            SC_TRY(io_map_h(&ep.c_map, c_h, N, B, M, NB, ldb));
+            SC_TRY(io_map_h(&ep.dz_map, w.dz_h, N, B, M, NB, ldb));
+            fill(ep);
+            SC_TRY((run_gemm_short_k<EpiBackCodeH>(N, B, M, &s, ep, st, 2)));
+        }
     }
     prof_mark(st, "G3_back_code");
     {

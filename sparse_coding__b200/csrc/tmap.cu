@@ -125,11 +125,12 @@ int make_io_map_h(CUtensorMap* out, const void* base, int64_t rows, int64_t cols
 }
 
 int make_io_map_h64(CUtensorMap* out, const void* base, int64_t rows, int64_t cols, int64_t g, int64_t gstride,
-                    const char** err) {
+                    const char** err, int64_t ld) {
     if (g < 1) g = 1;
-    const int64_t gs = (g > 1 && gstride > 0) ? gstride : cols * rows;
+    if (ld <= 0) ld = cols;
+    const int64_t gs = (g > 1 && gstride > 0) ? gstride : ld * rows;
     cuuint64_t dims[3] = {(cuuint64_t)cols, (cuuint64_t)rows, (cuuint64_t)g};
-    cuuint64_t strides[2] = {(cuuint64_t)cols * 2, (cuuint64_t)gs * 2};
+    cuuint64_t strides[2] = {(cuuint64_t)ld * 2, (cuuint64_t)gs * 2};
     cuuint32_t box[3] = {64, 32, 1};
     return encode(out, base, 3, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B, err, CU_TENSOR_MAP_DATA_TYPE_FLOAT16);
 }

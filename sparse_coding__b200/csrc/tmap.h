@@ -44,7 +44,7 @@ int make_io_map_h(CUtensorMap* out, const void* base, int64_t rows, int64_t cols
 
 // fp16 [G][rows][cols] map with box {64 cols, 32 rows} = 128-byte rows, 128-byte swizzle (two 32-column chunks per store)
 int make_io_map_h64(CUtensorMap* out, const void* base, int64_t rows, int64_t cols, int64_t g, int64_t gstride,
-                    const char** err);
+                    const char** err, int64_t ld = 0);
 
 // fp16 [G][rows][cols] map with box {32 cols, 64 rows} = 64-byte rows, 64-byte swizzle: the TRANSPOSED copy of a
 // [32 x 64] register tile (rows of the map = columns of the accumulator)

@@ -627,8 +627,8 @@ def run_ours(args):
     by_batch = {str(B): {"ms_per_step": ms_step, "member_act_per_s": value, "step_tflops": roofline["step_tflops"],
                          "frac_of_tensor_peak": roofline["step_frac_of_tensor_peak"]}}
     if world == 1:
-        for b2 in (4096, 8192):
-            if b2 <= B or b2 * 4 > chunk.shape[0]:
+        for b2 in (1024, 4096, 8192):
+            if b2 == B or b2 * 4 > chunk.shape[0]:
                 continue
             n2 = chunk.shape[0] // b2
             for i in range(10):

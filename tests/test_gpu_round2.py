@@ -221,3 +221,58 @@ def test_fista_large_magnitudes_take_the_tf32_pairs():
     a, _ = sc.FunctionalFista.fista(x.cuda(), D.cuda(), 1e-2, a0.cuda(), 20, "cuda")
     assert torch.isfinite(a).all()
     assert float((a.cpu().double() - a_ref).abs().max()) < 1e-6 * float(a_ref.abs().max()) + 1e-4
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("kind", ["untied", "tied"])
+def test_cached_step_record_is_invisible(kind):
+    """step_batch reuses the previous step's argument record while only the batch changes (ensemble._run_cached).  Two
+    identical ensembles see the same sequence of steps and interventions - a replaced parameter tensor, an in-place
+    edit of a buffer, another batch size, a gradient-only call, another operand format - one of them with the record
+    thrown away before every step: every loss and the final state must be bit-identical."""
+    import sparse_coding__b200 as sc
+    M, d, N = 3, 128, 256
+    sig = sc.FunctionalTiedSAE if kind == "tied" else sc.FunctionalSAE
+
+    def build():
+        torch.manual_seed(7)
+        models = [sig.init(d, N, float(l1), device="cuda") for l1 in np.logspace(-3, -2, M)]
+        return sc.FunctionalEnsemble(models, sig, sc.torchopt_compat.adam, {"lr": 1e-3}, device="cuda")
+
+    a, b = build(), build()
+    x = make_sparse_data(1024, d, 2 * d, 6, seed=11).cuda()
+    log = {id(a): [], id(b): []}
+
+    def step(ens, batch, cached):
+        if not cached:
+            ens._step_ctx = None
+        losses, aux = ens.step_batch(batch)
+        log[id(ens)].append(torch.stack([losses[k] for k in sorted(losses)]).clone())
+        return aux
+
+    def both(fn):
+        fn(a, True)
+        fn(b, False)
+
+    for i in range(3):
+        both(lambda e, c: step(e, x[i * 256:(i + 1) * 256], c))
+    assert a._step_ctx is not None                                   # the record exists and was used
+    both(lambda e, c: e.params.__setitem__("encoder", e.params["encoder"].clone() * 1.01))   # replaced tensor
+    both(lambda e, c: step(e, x[0:256], c))
+    both(lambda e, c: e.buffers["l1_alpha"].mul_(2.0))               # buffer edited in place
+    both(lambda e, c: step(e, x[256:512], c))
+    both(lambda e, c: step(e, x[0:384], c))                          # another batch size
+    both(lambda e, c: e.compute_grads(x[0:256]))                     # a gradient-only call in between
+    both(lambda e, c: step(e, x[256:512], c))
+    both(lambda e, c: setattr(e, "operand_format", "tf32"))          # another operand format
+    both(lambda e, c: step(e, x[512:768], c))
+    both(lambda e, c: step(e, x[768:1024], c))
+    aux_a = step(a, x[0:256], True)
+    aux_b = step(b, x[0:256], False)
+    assert torch.equal(aux_a["c"], aux_b["c"])
+    for la, lb in zip(log[id(a)], log[id(b)]):
+        assert torch.equal(la, lb)
+    for k in a.params:
+        assert torch.equal(a.params[k], b.params[k]), k
+        assert torch.equal(a.optim_states[0].mu[k], b.optim_states[0].mu[k]), k
+        assert torch.equal(a.optim_states[0].nu[k], b.optim_states[0].nu[k]), k

@@ -101,12 +101,12 @@ struct EpiFistaStep {
         tma_load_3d(&p.a_map, io.bar + set, b + 2 * kIoTileBytes, col, row0, 0);
     }
     SC_DEVICE void prefetch(int co) {  // only the warp's very first chunk; later ones are requested one chunk ahead
-        if (c.first && (threadIdx.x & 31) == 0) request((co >> 5) & 1, c.row, c.col0 + co);
+        if (c.first && (threadIdx.x & 31) == 0) request((co >> 5) & 1, c.row0, c.col0 + co);
     }
     SC_DEVICE void chunk(int co, float (&v)[32], int next_co) {
         const int lane = threadIdx.x & 31;
         const int set = (co >> 5) & 1;
-        const int col = c.col0 + co, row0 = c.row - lane;
+        const int col = c.col0 + co, row0 = c.row0;
         uint8_t* b = io.buf + set * (3 * kIoTileBytes);
         io_wait_loads(io, set);
         float yh[32], yl[32], av[32];
@@ -243,12 +243,12 @@ struct EpiFistaStepH {
         tma_load_3d(&p.a_map, io.bar + set, b + 4096, col, row0, 0);
     }
     SC_DEVICE void prefetch(int co) {
-        if (c.first && (threadIdx.x & 31) == 0) request((co >> 5) & 1, c.row, c.col0 + co);
+        if (c.first && (threadIdx.x & 31) == 0) request((co >> 5) & 1, c.row0, c.col0 + co);
     }
     SC_DEVICE void chunk(int co, float (&v)[32], int next_co) {
         const int lane = threadIdx.x & 31;
         const int set = (co >> 5) & 1;
-        const int col = c.col0 + co, row0 = c.row - lane;
+        const int col = c.col0 + co, row0 = c.row0;
         uint8_t* b = io.buf + set * 8192;
         io_wait_loads(io, set);
         const uint32_t rh = smem_u32(b) + lane * 64, rl = rh + 2048;

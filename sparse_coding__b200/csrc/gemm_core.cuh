@@ -108,6 +108,7 @@ SC_DEVICE void run_side_job(const typename E::Params&, int, int, long) {}
 struct RowCtx {
     int g;       // group / ensemble member
     int row;     // global accumulator row (may be >= M on the ragged last tile)
+    int row0;    // row of lane 0 = first row of this warp's 32-row slice (a warp-uniform value: TMA coordinates come from it)
     int col0;    // first global column of the tile
     int M, N;    // logical extents
     int tile_m, tile_n;
@@ -203,7 +204,7 @@ gemm_tf32_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
     uint64_t* io_bar = tmem_empty + 2;
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(io_bar + kIoBars * Cfg::kWarpsEpi);
 
-    const int warp = threadIdx.x >> 5;
+    const int warp = warp_id_uniform();
     const int lane = threadIdx.x & 31;
 
     pdl_launch_dependents();
@@ -232,7 +233,7 @@ gemm_tf32_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    const uint32_t tmem_base = *tmem_ptr;
+    const uint32_t tmem_base = uniform_u32(*tmem_ptr);
     pdl_wait();  // everything above touched only shared memory / TMEM; global memory from here on
 
     const int tiles_per_group = shape.tiles_m * shape.tiles_n;
@@ -347,7 +348,7 @@ gemm_tf32_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shape,
             const int as = it & 1;
             const uint32_t aph = (it >> 1) & 1;
             RowCtx ctx;
-            ctx.g = g; ctx.row = tm * kBlockM + q * 32 + lane; ctx.col0 = tn * BN;
+            ctx.g = g; ctx.row0 = tm * kBlockM + q * 32; ctx.row = ctx.row0 + lane; ctx.col0 = tn * BN;
             ctx.M = shape.M; ctx.N = shape.N; ctx.tile_m = tm; ctx.tile_n = tn; ctx.tiles_m = shape.tiles_m; ctx.tiles_n = shape.tiles_n; ctx.warp_q = q; ctx.prob = prob; ctx.half = half; ctx.halves = kH; ctx.part = q + 4 * half;
             ctx.split = 0; ctx.bn = BN; ctx.first = it == 0;
             ctx.next_g = -1; ctx.next_prob = 0; ctx.next_row0 = 0; ctx.next_col0 = 0;

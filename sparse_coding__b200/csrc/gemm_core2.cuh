@@ -61,7 +61,7 @@ gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape sha
     uint64_t* io_bar = tmem_empty + 2;
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(io_bar + kIoBars * Cfg::kWarpsEpi);
 
-    const int warp = threadIdx.x >> 5;
+    const int warp = warp_id_uniform();
     const int lane = threadIdx.x & 31;
     const uint32_t rank = cluster_ctarank();
     const bool leader = rank == 0;
@@ -93,7 +93,7 @@ gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape sha
     tc_fence_before();
     cluster_sync_all();
     tc_fence_after();
-    const uint32_t tmem_base = *tmem_ptr;
+    const uint32_t tmem_base = uniform_u32(*tmem_ptr);
     pdl_wait();  // everything above touched only shared memory / TMEM; global memory from here on
 
     const int nprob = shape.nprob > 1 ? shape.nprob : 1;
@@ -105,7 +105,7 @@ gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape sha
 
     if (warp == 0) {
         // ------------------------------------------------------------------ TMA producer (both CTAs)
-        if (lane == 0) {
+        {   // the whole (converged) warp walks the loops; one elected lane issues the copies
             int stage = 0;
             uint32_t phase = 0;
             for (int ptile = cluster_id; ptile < total_tiles; ptile += num_clusters) {
@@ -129,6 +129,7 @@ gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape sha
                         uint8_t* sa = smem + stage * Cfg::kStageBytes;
                         uint8_t* sb = sa + kATileBytes;
                         const int k0 = kb * kKElems;
+                        if (elect_one()) {
                         if (!A_MN) {
                             tma_load_3d_2cta(&maps.a[seg], &full_bar[stage], sa, k0, m0, ga);
                         } else if (shape.a_one_box[seg]) {
@@ -149,6 +150,8 @@ gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape sha
                         }
                         if (leader) mbar_arrive_expect_tx(&full_bar[stage], 2 * Cfg::kStageBytes);
                         else mbar_arrive_remote(&full_bar[stage], 0);
+                        }
+                        __syncwarp();
                         if (++stage == kStages) { stage = 0; phase ^= 1; }
                     }
                 }
@@ -156,7 +159,7 @@ gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape sha
         }
     } else if (warp == 1) {
         // ------------------------------------------------------------------ MMA issuer (leader CTA only)
-        if (leader && lane == 0) {
+        if (leader) {  // the whole (converged) warp walks the loops; one elected lane issues
             constexpr uint32_t idesc = EB == 4 ? make_idesc_tf32(2 * kBlockM, BN, A_MN, B_MN) : make_idesc_f16(2 * kBlockM, BN, A_MN, B_MN);
             int stage = 0;
             uint32_t phase = 0;
@@ -180,31 +183,36 @@ gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape sha
                         tc_fence_after();
                         const uint32_t a_base = smem_u32(smem + stage * Cfg::kStageBytes);
                         const uint32_t b_base = a_base + kATileBytes;
+                        if (elect_one()) {
 #pragma unroll
                         for (int k = 0; k < kBlockK / kUmmaK; ++k) {
                             // one MMA consumes 32 bytes of K: 8 tf32 or 16 fp16 elements
                             uint64_t da, db;
+                            const uint32_t acc = k > 0 ? 1u : accumulate;  // only a tile's very first MMA overwrites
                             if (EB == 4) {
                                 da = A_MN ? make_smem_desc(a_base + k * 1024, 4096, 512, kLayoutSw128Base32)
                                           : make_smem_desc(a_base + k * 32, 16, 1024, kLayoutSw128);
                                 db = B_MN ? make_smem_desc(b_base + k * 1024, 4096, 512, kLayoutSw128Base32)
                                           : make_smem_desc(b_base + k * 32, 16, 1024, kLayoutSw128);
-                                umma_tf32_2cta(d_tmem, da, db, idesc, accumulate);
+                                umma_tf32_2cta(d_tmem, da, db, idesc, acc);
                             } else {
                                 // MN-major fp16: 16 k-rows per MMA = two 8-row groups (SBO 1024); 64-wide chunks 8 KB apart (LBO)
                                 da = A_MN ? make_smem_desc(a_base + k * 2048, 8192, 1024, kLayoutSw128)
                                           : make_smem_desc(a_base + k * 32, 16, 1024, kLayoutSw128);
                                 db = B_MN ? make_smem_desc(b_base + k * 2048, 8192, 1024, kLayoutSw128)
                                           : make_smem_desc(b_base + k * 32, 16, 1024, kLayoutSw128);
-                                umma_f16_2cta(d_tmem, da, db, idesc, accumulate);
+                                umma_f16_2cta(d_tmem, da, db, idesc, acc);
                             }
-                            accumulate = 1;
                         }
                         umma_commit_2cta(&empty_bar[stage]);
+                        }
+                        __syncwarp();
+                        accumulate = 1;
                         if (++stage == kStages) { stage = 0; phase ^= 1; }
                     }
                 }
-                umma_commit_2cta(&tmem_full[as]);
+                if (elect_one()) umma_commit_2cta(&tmem_full[as]);
+                __syncwarp();
             }
         }
     } else if (warp == 3) {
@@ -228,7 +236,7 @@ gemm_tf32_2cta_kernel(const __grid_constant__ GemmMaps maps, const GemmShape sha
             const int as = it & 1;
             const uint32_t aph = (it >> 1) & 1;
             RowCtx ctx;
-            ctx.g = g; ctx.row = tm * (2 * kBlockM) + rank * kBlockM + q * 32 + lane; ctx.col0 = tn * BN;
+            ctx.g = g; ctx.row0 = tm * (2 * kBlockM) + rank * kBlockM + q * 32; ctx.row = ctx.row0 + lane; ctx.col0 = tn * BN;
             ctx.M = shape.M; ctx.N = shape.N;
             // partial-sum slots are indexed by 128-row tile: report this CTA's half as its own row tile
             ctx.tile_m = tm * 2 + rank; ctx.tile_n = tn; ctx.tiles_m = shape.tiles_m * 2; ctx.tiles_n = shape.tiles_n;

@@ -72,7 +72,7 @@ gemm_f16_resa_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shap
     uint64_t* io_bar = tmem_empty + 2;
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(io_bar + kIoBars * Cfg::kWarpsEpi);
 
-    const int warp = threadIdx.x >> 5;
+    const int warp = warp_id_uniform();
     const int lane = threadIdx.x & 31;
     const uint32_t rank = cluster_ctarank();
     const bool leader = rank == 0;
@@ -104,7 +104,7 @@ gemm_f16_resa_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shap
     tc_fence_before();
     cluster_sync_all();
     tc_fence_after();
-    const uint32_t tmem_base = *tmem_ptr;
+    const uint32_t tmem_base = uniform_u32(*tmem_ptr);
     pdl_wait();
 
     // contiguous range of tiles for this CTA pair; tile t = (g * tiles_m + tm) * tiles_n + tn
@@ -116,7 +116,7 @@ gemm_f16_resa_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shap
 
     if (warp == 0) {
         // ------------------------------------------------------------------ TMA producer (both CTAs)
-        if (lane == 0) {
+        {   // the whole (converged) warp walks the loops; one elected lane issues the copies
             int stage = 0;
             uint32_t phase = 0;
             int a_gen = 0, cur_group = -1;
@@ -130,14 +130,20 @@ gemm_f16_resa_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shap
                 for (int kb = 0; kb < kblocks; ++kb) {
                     if (new_a) {
                         if (a_gen > 0) mbar_wait(&a_free[kb], (a_gen - 1) & 1);  // the old row tile's MMAs on this k-block are done
-                        tma_load_3d_2cta(&maps.a[0], &a_full[kb], a_res + kb * kATileBytes, kb * 64, m0, ga);
-                        if (leader) mbar_arrive_expect_tx(&a_full[kb], 2 * kATileBytes);
-                        else mbar_arrive_remote(&a_full[kb], 0);
+                        if (elect_one()) {
+                            tma_load_3d_2cta(&maps.a[0], &a_full[kb], a_res + kb * kATileBytes, kb * 64, m0, ga);
+                            if (leader) mbar_arrive_expect_tx(&a_full[kb], 2 * kATileBytes);
+                            else mbar_arrive_remote(&a_full[kb], 0);
+                        }
+                        __syncwarp();
                     }
                     mbar_wait(&empty_bar[stage], phase ^ 1);
-                    tma_load_3d_2cta(&maps.b[0], &full_bar[stage], b_ring + stage * Cfg::kBTileBytes, kb * 64, n0, gb);
-                    if (leader) mbar_arrive_expect_tx(&full_bar[stage], 2 * Cfg::kBTileBytes);
-                    else mbar_arrive_remote(&full_bar[stage], 0);
+                    if (elect_one()) {
+                        tma_load_3d_2cta(&maps.b[0], &full_bar[stage], b_ring + stage * Cfg::kBTileBytes, kb * 64, n0, gb);
+                        if (leader) mbar_arrive_expect_tx(&full_bar[stage], 2 * Cfg::kBTileBytes);
+                        else mbar_arrive_remote(&full_bar[stage], 0);
+                    }
+                    __syncwarp();
                     if (++stage == stages) { stage = 0; phase ^= 1; }
                 }
                 if (new_a) { ++a_gen; cur_group = group; }
@@ -145,7 +151,7 @@ gemm_f16_resa_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shap
         }
     } else if (warp == 1) {
         // ------------------------------------------------------------------ MMA issuer (leader CTA only)
-        if (leader && lane == 0) {
+        if (leader) {  // whole warp, one elected lane issues
             constexpr uint32_t idesc = make_idesc_f16(2 * kBlockM, BN, false, false);
             int stage = 0;
             uint32_t phase = 0;
@@ -167,18 +173,22 @@ gemm_f16_resa_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shap
                     tc_fence_after();
                     const uint32_t a_base = smem_u32(a_res + kb * kATileBytes);
                     const uint32_t b_base = smem_u32(b_ring + stage * Cfg::kBTileBytes);
+                    if (elect_one()) {
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) {  // 16 fp16 of K per MMA, 32 bytes inside the 128-byte swizzle span
-                        const uint64_t da = make_smem_desc(a_base + k * 32, 16, 1024, kLayoutSw128);
-                        const uint64_t db = make_smem_desc(b_base + k * 32, 16, 1024, kLayoutSw128);
-                        umma_f16_2cta(d_tmem, da, db, idesc, accumulate);
-                        accumulate = 1;
+                        for (int k = 0; k < 4; ++k) {  // 16 fp16 of K per MMA, 32 bytes inside the 128-byte swizzle span
+                            const uint64_t da = make_smem_desc(a_base + k * 32, 16, 1024, kLayoutSw128);
+                            const uint64_t db = make_smem_desc(b_base + k * 32, 16, 1024, kLayoutSw128);
+                            umma_f16_2cta(d_tmem, da, db, idesc, k > 0 ? 1u : accumulate);
+                        }
+                        umma_commit_2cta(&empty_bar[stage]);
+                        if (last_of_group) umma_commit_2cta(&a_free[kb]);
                     }
-                    umma_commit_2cta(&empty_bar[stage]);
-                    if (last_of_group) umma_commit_2cta(&a_free[kb]);
+                    __syncwarp();
+                    accumulate = 1;
                     if (++stage == stages) { stage = 0; phase ^= 1; }
                 }
-                umma_commit_2cta(&tmem_full[as]);
+                if (elect_one()) umma_commit_2cta(&tmem_full[as]);
+                __syncwarp();
                 if (new_a) { ++a_gen; cur_group = group; }
             }
         }
@@ -198,7 +208,7 @@ gemm_f16_resa_kernel(const __grid_constant__ GemmMaps maps, const GemmShape shap
             const int as = it & 1;
             const uint32_t aph = (it >> 1) & 1;
             RowCtx ctx;
-            ctx.g = g; ctx.row = tm * (2 * kBlockM) + rank * kBlockM + q * 32 + lane; ctx.col0 = tn * BN;
+            ctx.g = g; ctx.row0 = tm * (2 * kBlockM) + rank * kBlockM + q * 32; ctx.row = ctx.row0 + lane; ctx.col0 = tn * BN;
             ctx.M = shape.M; ctx.N = shape.N;
             ctx.tile_m = tm * 2 + rank; ctx.tile_n = tn; ctx.tiles_m = tiles_m * 2; ctx.tiles_n = tiles_n;
             ctx.warp_q = q; ctx.prob = 0; ctx.half = half; ctx.halves = kH; ctx.part = q + 4 * half;

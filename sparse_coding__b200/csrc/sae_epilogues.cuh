@@ -91,7 +91,7 @@ struct EpiEncode {
         }
         io_wait_stores_read();  // the previous chunk's store has read the staging tile
         io_write_row(io.buf, lane, v);
-        io_store_tile(&p.c_map, io.buf, col, c.row - lane, c.g);
+        io_store_tile(&p.c_map, io.buf, col, c.row0, c.g);
         io_commit();
     }
     SC_DEVICE void finish() {
@@ -448,7 +448,7 @@ struct EpiAdamT {
     // Called by the core before it waits for the accumulator.  Only the warp's very first tile needs it: every
     // later first chunk was requested by the last chunk of the tile before.
     SC_DEVICE void prefetch(int co) {
-        if (c.first && owner && (threadIdx.x & 31) == 0) request((co >> 5) & 1, u, c.g, c.row, c.col0 + co);
+        if (c.first && owner && (threadIdx.x & 31) == 0) request((co >> 5) & 1, u, c.g, c.row0, c.col0 + co);
     }
     // every thread of the quarter has written its part of the staging rows: make them visible to the async proxy
     // and let the owner's lane 0 go on to the tile stores
@@ -461,7 +461,7 @@ struct EpiAdamT {
         const int lane = threadIdx.x & 31;
         const int h = SPLIT == 1 ? 0 : c.half;
         const int set = (co >> 5) & 1;  // consecutive chunks alternate between the two sets
-        const int col = c.col0 + co, row0 = c.row - lane;
+        const int col = c.col0 + co, row0 = c.row0;
         uint8_t* b = io.buf + set * (3 * kIoTileBytes);
         io_wait_loads(io, set);
         float pv[W], mv[W], nv[W];

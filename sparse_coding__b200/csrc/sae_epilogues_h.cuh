@@ -68,7 +68,7 @@ struct EpiEncodeH {
         uint8_t* tile = io.buf + (((co >> 5) / kEpiHalves) & 1) * 2048;  // this warp's chunks alternate between the two tiles
         io_wait_stores_read_n<1>();  // the store issued two chunks ago has read this staging tile
         io_write_row_h(tile, lane, v);
-        io_store_tile(&p.c_map, tile, col, c.row - lane, c.g);
+        io_store_tile(&p.c_map, tile, col, c.row0, c.g);
         io_commit();
     }
     SC_DEVICE void finish() {
@@ -153,7 +153,7 @@ struct EpiReduceTile {
         io_write_row(io.buf, lane, v);
         fence_proxy_async_smem();
         __syncwarp();
-        if (lane == 0) tma_reduce_add_3d(&p.out_map, io.buf, c.col0 + co, c.row, c.g);  // clipped at the tensor's edge
+        if (lane == 0) tma_reduce_add_3d(&p.out_map, io.buf, c.col0 + co, c.row0, c.g);  // clipped at the tensor's edge
         io_commit();
     }
     SC_DEVICE void finish() {}
@@ -214,11 +214,11 @@ struct EpiEncodeTHT {
         }
         // the two staging tiles alternate per stored chunk (bit 8 of the warp's persistent phase word: a tile can have an
         // odd number of chunks per warp), so the one used now is the one whose store is two bulk groups back
-        uint8_t* tile = io.buf + ((*io.phase >> 8) & 1u) * 2048;
+        uint8_t* tile = io.buf + ((uniform_u32(*io.phase) >> 8) & 1u) * 2048;  // a warp-uniform address for the TMA store
         *io.phase ^= 1u << 8;
         io_wait_stores_read_n<1>();
         io_write_row_h(tile, lane, v);
-        io_store_tile(&p.c_map, tile, col, c.row - lane, c.g);
+        io_store_tile(&p.c_map, tile, col, c.row0, c.g);
         io_commit();
     }
     SC_DEVICE void finish() {
@@ -294,7 +294,7 @@ struct EpiBackCodeHT {
     // the k-th (1..kAhead) live chunk after chunk i of the current tile, in processing order
     SC_DEVICE bool nth_next(int i, int k, int& g, int& row0, int& bcol) const {
         for (int j = i + 1; live(c.col0, j); ++j)
-            if (--k == 0) { g = c.g; row0 = c.row - (threadIdx.x & 31); bcol = c.col0 + (c.half + j * H) * W; return true; }
+            if (--k == 0) { g = c.g; row0 = c.row0; bcol = c.col0 + (c.half + j * H) * W; return true; }
         if (c.next_g < 0) return false;
         for (int j = 0; live(c.next_col0, j); ++j)
             if (--k == 0) { g = c.next_g; row0 = c.next_row0; bcol = c.next_col0 + (c.half + j * H) * W; return true; }
@@ -339,8 +339,9 @@ struct EpiBackCodeHT {
         const int i = (co / W) / H;  // index of this chunk among the warp's chunks of the tile
         const int bcol = c.col0 + co;
         if (bcol >= c.N) return;      // the whole chunk lies beyond the batch (warp-uniform): nothing was requested
-        const int row0 = c.row - lane;
-        int cons = (*io.phase >> 8) & 7, ahead = (*io.phase >> 12) & 7;
+        const int row0 = c.row0;
+        const uint32_t ph = uniform_u32(*io.phase);  // the warp's state word, as a value known to be warp-uniform
+        int cons = (ph >> 8) & 7, ahead = (ph >> 12) & 7;
         if (ahead == 0) {  // nothing in flight for this chunk (first chunk of the kernel, or the look-ahead could not see it)
             io_wait_stores_read_n<1>();
             if (lane == 0) request(cons, c.g, row0, bcol);

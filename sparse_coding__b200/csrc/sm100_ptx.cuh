@@ -15,6 +15,22 @@ namespace sc {
 
 SC_DEVICE uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
 SC_DEVICE uint32_t lane_id() { return threadIdx.x & 31; }
+// Warp index as a value the compiler KNOWS to be warp-uniform (a shuffle from lane 0): branches on it are uniform
+// branches, so loop counters, shared-memory addresses and descriptors computed inside stay in uniform registers and the
+// instructions that take uniform operands (UTMALDG, UTCHMMA, UTCBAR) need no per-lane "waterfall" (ELECT + R2UR.BROADCAST
+// + BRA.U.ANY) around them - that was 2/3 of the instructions of the MMA issue loop.
+SC_DEVICE int warp_id_uniform() { return __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0); }
+SC_DEVICE uint32_t uniform_u32(uint32_t v) { return __shfl_sync(0xffffffffu, v, 0); }
+// one lane of a converged warp
+SC_DEVICE bool elect_one() {
+    uint32_t pred;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "elect.sync _|p, 0xffffffff;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(pred));
+    return pred != 0;
+}
 
 // ----------------------------------------------------------------------------- mbarrier
 SC_DEVICE void mbar_init(uint64_t* bar, uint32_t count) {

@@ -408,9 +408,13 @@ int sae_step_f16_impl(const ScStepArgs& a) {
     const bool g45_split = w.g45_split > 1 && !grad_mode;
     const bool fold = !a.tied && !grad_mode && !g45_split && fold_enabled(B);
     const float* fold_inv = fold ? w.inv_norm : nullptr;
-    // the decode GEMM reads the dictionary K-major from a transposed fp16 copy, made by the prologue when it rebuilds the
-    // operand copies and kept current by the Adam epilogue in fold mode (SC_B200_DICT_T=0: MN-major from the plain copy)
-    static const bool dict_t_env = !(getenv("SC_B200_DICT_T") && getenv("SC_B200_DICT_T")[0] == '0');
+    // SC_B200_DICT_T=1: the decode GEMM reads the dictionary K-major from a transposed fp16 copy (made by the prologue
+    // when it rebuilds the operand copies, kept current by the Adam epilogue in fold mode) instead of MN-major from the
+    // plain copy.  That was worth 12 % of the decode mainloop while the MMA issue loop was the bottleneck (its MN-major
+    // descriptors cost more to build); with the converged issue loops the two read the same (0.790 / 0.787 ms at 4096
+    // rows, 1.402 / 1.403 at 8192), and in fold mode the extra 33 MB of epilogue stores cost 1.6 % of the step
+    // (0.4497 / 0.4423 ms at 2048 rows), so it is off by default.
+    static const bool dict_t_env = getenv("SC_B200_DICT_T") && getenv("SC_B200_DICT_T")[0] == '1';
     const bool dict_t = dict_t_env && (size_t)d * 16 <= 48 * 1024;  // the prologue's transposing tile: 16 d bytes of shared memory
     const bool params_ready = fold && a.operands_valid != 0 && handover_intact(a.workspace, M, d, N);
     handover_record(a.workspace, M, d, N, fold);

@@ -136,6 +136,15 @@ SC_DEVICE void epilogue_tile(const typename Epi::Params& ep, const RowCtx& ctx, 
                              uint32_t parity, uint32_t taddr, Release release) {
     Epi epi(ep, ctx, io);
     constexpr int kH = EpiHalvesOf<Epi>::v;
+    // The accumulator stage goes back to the MMA warp as soon as this warp has READ its last chunk of the tile (the values
+    // are in registers then), not after it has processed it: the stage is held for one chunk's arithmetic and stores
+    // less per tile, which matters where a warp has few chunks per tile (two in the dL/dz epilogue).
+    bool released = false;
+    auto give_back = [&] {
+        tc_fence_before();
+        release();
+        released = true;
+    };
     if constexpr (EpiColSplitOf<Epi>::v == 2) {
         static_assert(kH == 2, "column split pairs the two warps of a row quarter");
         epi.prefetch(0);
@@ -146,6 +155,7 @@ SC_DEVICE void epilogue_tile(const typename Epi::Params& ep, const RowCtx& ctx, 
             float v[16];
             tmem_ld16(taddr + c * 32 + ctx.half * 16, v);
             tmem_ld_wait();
+            if (c + 1 == BN / 32) give_back();
             epi.chunk(c * 32, v, (c + 1 < BN / 32) ? (c + 1) * 32 : -1);
         }
     } else if constexpr (EpiChunkWOf<Epi>::v == 64) {
@@ -161,6 +171,7 @@ SC_DEVICE void epilogue_tile(const typename Epi::Params& ep, const RowCtx& ctx, 
                 tmem_ld32(taddr + c * 64, *reinterpret_cast<float(*)[32]>(&v[0]));
                 tmem_ld32(taddr + c * 64 + 32, *reinterpret_cast<float(*)[32]>(&v[32]));
                 tmem_ld_wait();
+                if (c + kH >= kUnits) give_back();
                 epi.chunk(c * 64, v, (c + kH < kUnits) ? (c + kH) * 64 : -1);
             }
         }
@@ -178,12 +189,12 @@ SC_DEVICE void epilogue_tile(const typename Epi::Params& ep, const RowCtx& ctx, 
                 float v[32];
                 tmem_ld32(taddr + c * 32, v);
                 tmem_ld_wait();
+                if (c + kH >= BN / 32) give_back();
                 epi.chunk(c * 32, v, (c + kH < BN / 32) ? (c + kH) * 32 : -1);
             }
         }
     }
-    tc_fence_before();
-    release();
+    if (!released) give_back();  // a warp without a chunk in this tile
     epi.finish();
 }
 

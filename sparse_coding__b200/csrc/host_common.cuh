@@ -15,6 +15,8 @@
 namespace sc {
 
 extern thread_local char g_last_error[512];
+extern thread_local int g_dbg_sm_limit;   // probe: > 0 caps the number of CTAs of the GEMM launches of this thread
+extern thread_local int g_dbg_phase;      // probe: bit 0 = prologue..G3, bit 1 = weight gradients + Adam (default 3)
 
 inline int fail(int code, const char* fmt, ...) {
     va_list ap;
@@ -159,6 +161,7 @@ inline int plan_gemm(GemmPlan* pl, int M, int N, int G, const Seg* segs, int nse
                      bool segs_are_problems = false, int bn = 0, int ksplit = 0) {
     memset(pl, 0, sizeof *pl);
     SC_TRY(device_sm_count(&pl->sms));
+    if (g_dbg_sm_limit > 0 && g_dbg_sm_limit < pl->sms) pl->sms = g_dbg_sm_limit & ~1;
     pl->bn = bn > 0 ? bn : pick_bn(N);
     if (ksplit > 1 && segs[0].a.elem_bytes != 2) return fail(-3, "split-K needs fp16 operands (CTA-pair kernel)");
     pl->sh.ksplit = ksplit > 1 ? ksplit : 1;

@@ -11,6 +11,8 @@
 namespace sc {
 
 thread_local char g_last_error[512] = "";
+thread_local int g_dbg_sm_limit = 0;
+thread_local int g_dbg_phase = 3;
 Profiler g_prof;
 
 // ------------------------------------------------------------------------------------------------
@@ -440,3 +442,6 @@ int sc_sae_step(const ScStepArgs* args) {
 }
 
 }  // extern "C"
+
+extern "C" void sc_debug_set_sm_limit(int n) { sc::g_dbg_sm_limit = n; }
+extern "C" void sc_debug_set_phase(int mask) { sc::g_dbg_phase = mask; }

@@ -423,6 +423,7 @@ int sae_step_f16_impl(const ScStepArgs& a) {
     // difference in step time is that kernel's marginal cost inside the real launch chain
     static const int dup_k = getenv("SC_B200_DUP") ? atoi(getenv("SC_B200_DUP")) : -1;
     prof_mark(st, "begin");
+    if (g_dbg_phase & 1) {
     for (int rep = 0; rep < (dup_k == 0 ? 2 : 1); ++rep) {
         const long long x_n4 = xg * Bd / 4;
         const int x_blocks = static_cast<int>(x_n4 / 1024 + 1 < 1024 ? x_n4 / 1024 + 1 : 1024);
@@ -505,7 +506,9 @@ int sae_step_f16_impl(const ScStepArgs& a) {
             SC_TRY((run_gemm_short_k<EpiBackCodeH>(N, B, M, &s, ep, st, 2)));
         }
     }
+    }  // phase 1
     prof_mark(st, "G3_back_code");
+    if (!(g_dbg_phase & 2)) return 0;
     {
         AdamParams e{};
         e.tiles_b = w.tiles_b; e.a = ad; e.g_scale = sc_;
